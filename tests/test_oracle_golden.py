@@ -113,7 +113,7 @@ def test_oracle_known_answers(oracle, c):
 def test_oracle_special_functions_vs_scipy(oracle):
     rng = np.random.default_rng(0)
     for df in [1, 2, 3, 5, 10, 44, 98, 146, 183, 1000, 100000]:
-        for t in np.concatenate([rng.uniform(0, 6, 20), [1e-8, 0.5, 12.0, 40.0, 300.0]]):
+        for t in np.concatenate([rng.uniform(0, 6, 20), [1e-3, 0.5, 12.0, 40.0, 300.0]]):
             want = 2 * stats.t.sf(t, df)
             got = oracle.t_two_sided_p(t, df)
             assert abs(got - want) <= 1e-11 * want + 1e-300, (t, df, got, want)
@@ -126,6 +126,14 @@ def test_oracle_special_functions_vs_scipy(oracle):
             want = stats.f.sf(f, d1, d2)
             got = oracle.f_upper_p(f, d1, d2)
             assert abs(got - want) <= 1e-10 * want + 1e-300, (f, d1, d2, got, want)
+    # tiny |t| (scipy's t.sf loses digits there): closed form for df = 1, mpmath otherwise
+    assert abs(oracle.t_two_sided_p(1e-8, 1) - (1 - 2 / math.pi * math.atan(1e-8))) < 1e-15
+    import mpmath
+    mpmath.mp.dps = 40
+    for t, df in [(1e-8, 7), (1e-5, 44), (60.0, 44), (25.0, 3)]:
+        x = mpmath.mpf(df) / (df + mpmath.mpf(t) ** 2)
+        want = float(mpmath.betainc(mpmath.mpf(df) / 2, 0.5, 0, x, regularized=True))
+        assert abs(oracle.t_two_sided_p(t, df) - want) <= 1e-13 * want
     assert math.isnan(oracle.t_critical(0.95, 0))  # lib.rs:2218-2220
     assert math.isnan(oracle.t_critical(1.0, 5)) and math.isnan(oracle.t_critical(0.0, 5))
 
