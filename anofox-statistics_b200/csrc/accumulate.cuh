@@ -1,0 +1,627 @@
+// accumulate.cuh -- segmented, group-sorted streaming accumulation of the per-group moment records.
+//
+// Replaces the reference's raw-row aggregate state (src/aggregate_functions/ols_aggregate.cpp:19-42
+// state, :120-186 Update, :189-234 Combine) and the design-matrix build of fit_ols
+// (crates/anofox-stats-core/src/models/ols.rs:59-66 finite-row filter, :76-87 constant-column
+// scan, :149-152 Mat::from_fn): instead of buffering rows and decomposing them, every row is
+// read from HBM exactly once and folded into X'WX, X'Wy, y'Wy, n, sum w and the column sums.
+//
+// Shape of the kernel (one persistent CTA per SM):
+//   * warp 0 = producer. It walks the CTA's windows of the group-sorted row range, packs as many
+//     consecutive whole groups as fit into a shared-memory stage and fetches their rows with ONE
+//     bulk copy per array (cp.async.bulk -> SASS UBLKCP, the TMA engine; the 16-byte alignment
+//     head/tail elements are patched with plain stores). Completion is signalled through an
+//     mbarrier transaction count; a ring of stages keeps several copies in flight per SM.
+//   * warps 1.. = consumers, one group per warp at a time. A step covers 4 rows: lane l holds the
+//     element (row l%4, column 8t + l/4) of each 8-column tile t, which is simultaneously the A
+//     fragment (scaled by the weight) and the B fragment of an FP64 tensor-core MMA
+//     (mma.m8n8k4.f64 -> SASS DMMA): the reduction over rows happens inside the MMA, so no
+//     cross-lane reduction of the Gram matrix is needed. y and the constant-1 column ride in the
+//     spare columns of the last tile when p % 8 leaves room, otherwise they are accumulated by
+//     a few scalar FMAs per step (SIDE mode).
+//   * rows are differenced against the group's first valid row before squaring (exact
+//     constant-column statistic, and a shift that removes the cancellation of raw moments).
+//   * the fast path assumes finite features and checks the result: a non-finite accumulator
+//     re-runs the group with the per-element finite filter of ols.rs:59-66 (CHECKX).
+//   * a group too large for a stage is appended to a list and left to the streaming kernel.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+struct AccArgs {
+	const int64_t *offsets; // [G+1]
+	const double *y;        // [N]
+	const double *x;        // [N*p]
+	const double *w;        // [N] or null
+	const uint8_t *train;   // [N] or null
+	int64_t n_groups;
+	int p;
+	const int64_t *tile_g0; // [n_tiles+1] first group starting in each row window
+	int64_t n_tiles;
+	double *records;        // [G][rec_len(p)]
+	int64_t *big_list;      // groups that do not fit a stage
+	int *big_count;
+	int cap_rows;           // rows per stage
+	int stage_bytes;        // bytes per stage (all regions)
+	int xcap, ycap, wcap;   // region sizes in bytes (16-byte multiples)
+	int n_stages;
+};
+
+struct StageHeader {
+	int64_t g_first;
+	int count; // groups in the stage; -1 = producer finished
+	int lead_x, lead_y, lead_w, lead_t; // byte offset of element 0 inside each region
+	uint32_t rowstart[kMaxStageGroups + 1];
+};
+
+// Copy `bytes` bytes from global `src` into the shared region `dst` (16-byte aligned) so that
+// byte e lands at dst + lead + e, lead = src & 15. The 16-byte aligned interior goes through one
+// bulk copy; the unaligned head / tail are moved with ELEM-sized plain loads by the warp.
+// Returns the number of bytes the bulk copy will deliver (for the mbarrier transaction count).
+template <int ELEM>
+__device__ __forceinline__ uint32_t stage_fetch(unsigned char *dst, const unsigned char *src, int64_t bytes, int lane,
+                                                uint64_t *bar, int *lead_out) {
+	const uint32_t lead = (uint32_t)((uintptr_t)src & 15);
+	*lead_out = (int)lead;
+	if (bytes <= 0) return 0;
+	int64_t head = lead ? (int64_t)(16 - lead) : 0;
+	if (head > bytes) head = bytes;
+	int64_t mid = (bytes - head) & ~(int64_t)15;
+	int64_t tail = bytes - head - mid;
+	for (int64_t e = (int64_t)lane * ELEM; e < head; e += 32 * ELEM) {
+		if (ELEM == 8)
+			*(double *)(dst + lead + e) = *(const double *)(src + e);
+		else
+			dst[lead + e] = src[e];
+	}
+	for (int64_t e = (int64_t)lane * ELEM; e < tail; e += 32 * ELEM) {
+		if (ELEM == 8)
+			*(double *)(dst + lead + head + mid + e) = *(const double *)(src + head + mid + e);
+		else
+			dst[lead + head + mid + e] = src[head + mid + e];
+	}
+	if (mid > 0 && lane == 0) bulk_g2s(dst + lead + head, src + head, (uint32_t)mid, bar);
+	return (uint32_t)mid;
+}
+
+__device__ __forceinline__ double xor_sum4(double v) { // sum over the 4 lanes that share lane/4
+	v += __shfl_xor_sync(0xffffffffu, v, 1);
+	v += __shfl_xor_sync(0xffffffffu, v, 2);
+	return v;
+}
+__device__ __forceinline__ double xor_max4(double v) {
+	v = fmax(v, __shfl_xor_sync(0xffffffffu, v, 1));
+	v = fmax(v, __shfl_xor_sync(0xffffffffu, v, 2));
+	return v;
+}
+
+// Running state of one warp for one group (or one row shard of a big group).
+template <int NT, bool SIDE> struct WarpAcc {
+	static constexpr int NTP = NT * (NT + 1) / 2;
+	double c0[NTP], c1[NTP]; // DMMA accumulators, tile pairs (ta <= tb) in row-major order
+	double cd[NT];           // max |d| per owned column
+	double sxy[SIDE ? NT : 1], s1[SIDE ? NT : 1];
+	double syy, sy, sw;
+	int nv, ns;
+	__device__ __forceinline__ void clear() {
+#pragma unroll
+		for (int i = 0; i < NTP; ++i) c0[i] = c1[i] = 0.0;
+#pragma unroll
+		for (int t = 0; t < NT; ++t) cd[t] = 0.0;
+#pragma unroll
+		for (int t = 0; t < (SIDE ? NT : 1); ++t) sxy[t] = s1[t] = 0.0;
+		syy = sy = sw = 0.0;
+		nv = ns = 0;
+	}
+};
+
+// Row validity from y / w / train only (the part every lane can evaluate alone).
+__device__ __forceinline__ bool row_ok_yw(double yv, double wv, int tr, bool has_w) {
+	bool ok = finite_f64(yv) && tr != 0;
+	if (has_w) ok = ok && (wv > 0.0) && finite_f64(wv);
+	return ok;
+}
+
+// Accumulate rows [r_begin, r_end) of a row-major block into `A`, differencing against sh/shy.
+// xs/ys/ws/ts point at row 0 of the block; n_clamp = last addressable row.
+template <int NT, bool SIDE, bool CHECKX>
+__device__ __forceinline__ void acc_rows(WarpAcc<NT, SIDE> &A, const double *__restrict__ xs,
+                                         const double *__restrict__ ys, const double *__restrict__ ws,
+                                         const uint8_t *__restrict__ ts, int r_begin, int r_end, int p, int lane,
+                                         const double (&sh)[NT], double shy) {
+	const int rl = lane & 3, cl = lane >> 2;
+	const bool has_w = ws != nullptr;
+	for (int base = r_begin; base < r_end; base += 4) {
+		const int r = base + rl;
+		const int rc = r < r_end ? r : r_end - 1;
+		const double yv = ys[rc];
+		const double wv = has_w ? ws[rc] : 1.0;
+		const int tr = ts ? (int)ts[rc] : 1;
+		double xv[NT];
+#pragma unroll
+		for (int t = 0; t < NT; ++t) {
+			const int c = 8 * t + cl;
+			xv[t] = (c < p) ? xs[(int64_t)rc * p + c] : 0.0;
+		}
+		bool ok = (r < r_end) && row_ok_yw(yv, wv, tr, has_w);
+		if (CHECKX) {
+			bool bad = false;
+#pragma unroll
+			for (int t = 0; t < NT; ++t) bad = bad || !finite_f64(xv[t]);
+			const unsigned mb = __ballot_sync(0xffffffffu, bad);
+			ok = ok && ((mb & (0x11111111u << rl)) == 0u);
+		}
+		A.ns += (r < r_end && tr != 0) ? 1 : 0;
+		A.nv += ok ? 1 : 0;
+		const double weff = ok ? wv : 0.0;
+		const double dy = ok ? yv - shy : 0.0;
+		double d[NT], a[NT];
+#pragma unroll
+		for (int t = 0; t < NT; ++t) {
+			const int c = 8 * t + cl;
+			double dv = ok ? xv[t] - sh[t] : 0.0; // feature column (or zero padding: xv = sh = 0)
+			if (!SIDE && t == NT - 1) {
+				if (c == p) dv = dy;
+				if (c == p + 1) dv = ok ? 1.0 : 0.0;
+			}
+			d[t] = dv;
+			A.cd[t] = fmax(A.cd[t], fabs(dv));
+			a[t] = has_w ? weff * dv : dv;
+		}
+		int pair = 0;
+#pragma unroll
+		for (int ta = 0; ta < NT; ++ta)
+#pragma unroll
+			for (int tb = ta; tb < NT; ++tb) {
+				dmma_884(A.c0[pair], A.c1[pair], a[ta], d[tb]);
+				++pair;
+			}
+		if (SIDE) {
+			const double wdy = weff * dy;
+#pragma unroll
+			for (int t = 0; t < NT; ++t) {
+				A.sxy[t] = fma(d[t], wdy, A.sxy[t]);
+				A.s1[t] += a[t];
+			}
+			A.syy = fma(wdy, dy, A.syy);
+			A.sy += wdy;
+			A.sw += weff;
+		}
+	}
+}
+
+// First valid row of [0,n) -> index, or -1. Also loads the shift vector.
+template <int NT, bool SIDE, bool CHECKX>
+__device__ __forceinline__ int find_first_valid(const double *__restrict__ xs, const double *__restrict__ ys,
+                                                const double *__restrict__ ws, const uint8_t *__restrict__ ts, int n,
+                                                int p, int lane) {
+	const int rl = lane & 3, cl = lane >> 2;
+	const bool has_w = ws != nullptr;
+	for (int base = 0; base < n; base += 4) {
+		const int r = base + rl;
+		const int rc = r < n ? r : n - 1;
+		bool ok = (r < n) && row_ok_yw(ys[rc], has_w ? ws[rc] : 1.0, ts ? (int)ts[rc] : 1, has_w);
+		if (CHECKX) {
+			bool bad = false;
+#pragma unroll
+			for (int t = 0; t < NT; ++t) {
+				const int c = 8 * t + cl;
+				if (c < p) bad = bad || !finite_f64(xs[(int64_t)rc * p + c]);
+			}
+			const unsigned mb = __ballot_sync(0xffffffffu, bad);
+			ok = ok && ((mb & (0x11111111u << rl)) == 0u);
+		}
+		const unsigned m4 = __ballot_sync(0xffffffffu, ok) & 0xFu;
+		if (m4) return base + __ffs(m4) - 1;
+	}
+	return -1;
+}
+
+template <int NT, bool SIDE>
+__device__ __forceinline__ void load_shift(const double *__restrict__ xs, const double *__restrict__ ys, int f, int p,
+                                           int lane, double (&sh)[NT], double &shy) {
+	const int cl = lane >> 2;
+#pragma unroll
+	for (int t = 0; t < NT; ++t) {
+		const int c = 8 * t + cl;
+		sh[t] = (c < p) ? xs[(int64_t)f * p + c] : 0.0;
+	}
+	shy = ys[f];
+}
+
+template <int NT, bool SIDE> __device__ __forceinline__ bool acc_poisoned(const WarpAcc<NT, SIDE> &A) {
+	bool bad = false;
+#pragma unroll
+	for (int i = 0; i < WarpAcc<NT, SIDE>::NTP; ++i) bad = bad || !finite_f64(A.c0[i]) || !finite_f64(A.c1[i]);
+	if (SIDE) {
+#pragma unroll
+		for (int t = 0; t < NT; ++t) bad = bad || !finite_f64(A.sxy[t]) || !finite_f64(A.s1[t]);
+		bad = bad || !finite_f64(A.syy) || !finite_f64(A.sy);
+	}
+	return __any_sync(0xffffffffu, bad);
+}
+
+// Scatter the warp's accumulators into a record (global or shared memory, element stride 1).
+// add = false: plain stores of a complete group; add = true is not used here (partials are
+// written whole and reduced by a separate kernel, which keeps the summation order fixed).
+template <int NT, bool SIDE>
+__device__ __forceinline__ void store_record(WarpAcc<NT, SIDE> &A, double *__restrict__ rec, int p, int lane,
+                                             const double (&sh)[NT], double shy, int n_state) {
+	const int rl = lane & 3, cl = lane >> 2, k = p + 1;
+	double *S1 = rec + rec_off_s1(p), *S2 = rec + rec_off_s2(p);
+	int pair = 0;
+#pragma unroll
+	for (int ta = 0; ta < NT; ++ta)
+#pragma unroll
+		for (int tb = ta; tb < NT; ++tb) {
+			const int i = 8 * ta + cl;
+#pragma unroll
+			for (int h = 0; h < 2; ++h) {
+				const int j = 8 * tb + 2 * rl + h;
+				const double v = h ? A.c1[pair] : A.c0[pair];
+				if (i <= j) {
+					if (SIDE) {
+						if (j < p) S2[tri_idx(i, j, k)] = v;
+					} else {
+						if (j <= p)
+							S2[tri_idx(i, j, k)] = v;
+						else if (j == p + 1) {
+							if (i <= p)
+								S1[i] = v;
+							else if (i == p + 1)
+								rec[1] = v; // sum of weights
+						}
+					}
+				}
+			}
+			++pair;
+		}
+	// per-column statistics live replicated over the 4 row lanes
+#pragma unroll
+	for (int t = 0; t < NT; ++t) {
+		const int c = 8 * t + cl;
+		const double cdm = xor_max4(A.cd[t]);
+		if (SIDE) {
+			const double vxy = xor_sum4(A.sxy[t]);
+			const double v1 = xor_sum4(A.s1[t]);
+			if (rl == 0 && c < p) {
+				S2[tri_idx(c, p, k)] = vxy;
+				S1[c] = v1;
+			}
+		}
+		if (rl == 0 && c < p) {
+			rec[rec_off_cdev(p) + c] = cdm;
+			rec[rec_off_shift(p) + c] = sh[t];
+		}
+	}
+	const int nv = A.nv + __shfl_xor_sync(0xffffffffu, A.nv, 1);
+	const int nvt = nv + __shfl_xor_sync(0xffffffffu, nv, 2);
+	const int ns = A.ns + __shfl_xor_sync(0xffffffffu, A.ns, 1);
+	const int nst = ns + __shfl_xor_sync(0xffffffffu, ns, 2);
+	if (SIDE) {
+		const double vyy = xor_sum4(A.syy), vy = xor_sum4(A.sy), vw = xor_sum4(A.sw);
+		if (lane == 0) {
+			S2[tri_idx(p, p, k)] = vyy;
+			S1[p] = vy;
+			rec[1] = vw;
+		}
+	}
+	if (lane == 0) {
+		rec[0] = (double)nvt;
+		rec[2] = (double)(n_state >= 0 ? n_state : nst);
+		rec[3] = 0.0;
+		rec[rec_off_shift(p) + p] = shy;
+	}
+}
+
+// A record that says "no valid rows" (n_valid = 0): the solve stage turns it into the right status.
+__device__ __forceinline__ void store_empty_record(double *__restrict__ rec, int p, int lane, int n_state) {
+	const int L = rec_len(p);
+	for (int i = lane; i < L; i += 32) rec[i] = (i == 2) ? (double)n_state : 0.0;
+}
+
+// One whole group resident in shared memory -> its record.
+template <int NT, bool SIDE>
+__device__ __forceinline__ void accumulate_group(const double *xs, const double *ys, const double *ws,
+                                                 const uint8_t *ts, int n, int p, int lane, double *rec) {
+	// rows that entered the aggregate state: all of them, or the flagged training rows
+	int n_state = n;
+	if (ts) {
+		int c = 0;
+		for (int r = lane; r < n; r += 32) c += ts[r] ? 1 : 0;
+		for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+		n_state = c;
+	}
+	if (n <= 0) {
+		store_empty_record(rec, p, lane, 0);
+		return;
+	}
+	WarpAcc<NT, SIDE> A;
+	double sh[NT], shy;
+	// fast path: features assumed finite
+	int f = find_first_valid<NT, SIDE, false>(xs, ys, ws, ts, n, p, lane);
+	if (f < 0) {
+		store_empty_record(rec, p, lane, n_state);
+		return;
+	}
+	load_shift<NT, SIDE>(xs, ys, f, p, lane, sh, shy);
+	A.clear();
+	acc_rows<NT, SIDE, false>(A, xs, ys, ws, ts, 0, n, p, lane, sh, shy);
+	if (acc_poisoned<NT, SIDE>(A)) {
+		// some feature was NaN/Inf: redo with the full finite-row filter
+		f = find_first_valid<NT, SIDE, true>(xs, ys, ws, ts, n, p, lane);
+		if (f < 0) {
+			store_empty_record(rec, p, lane, n_state);
+			return;
+		}
+		load_shift<NT, SIDE>(xs, ys, f, p, lane, sh, shy);
+		A.clear();
+		acc_rows<NT, SIDE, true>(A, xs, ys, ws, ts, 0, n, p, lane, sh, shy);
+	}
+	store_record<NT, SIDE>(A, rec, p, lane, sh, shy, n_state);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Resident kernel: groups that fit a stage.
+// ---------------------------------------------------------------------------------------------
+template <int NT, bool SIDE, int NCW>
+__global__ void __launch_bounds__(32 * (NCW + 1), 1) acc_resident_kernel(const AccArgs a) {
+	extern __shared__ __align__(128) unsigned char smem[];
+	__shared__ uint64_t full_bar[8], empty_bar[8];
+	__shared__ StageHeader hdr[8];
+	const int NS = a.n_stages;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	if (threadIdx.x == 0) {
+		for (int s = 0; s < NS; ++s) {
+			mbar_init(&full_bar[s], 1);
+			mbar_init(&empty_bar[s], NCW);
+		}
+		mbar_fence_init();
+	}
+	__syncthreads();
+	const int p = a.p;
+	const int L = rec_len(p);
+	if (warp == 0) {
+		// ------------------------------ producer ------------------------------
+		int it = 0;
+		for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+			int64_t g = a.tile_g0[t];
+			const int64_t gend = a.tile_g0[t + 1];
+			while (g < gend) {
+				const int s = it % NS;
+				const uint32_t ph = (uint32_t)((it / NS) & 1);
+				mbar_wait(&empty_bar[s], ph ^ 1u);
+				const int64_t row0 = a.offsets[g];
+				int cnt = 0;
+				int64_t row_end = row0;
+				bool closed = false;
+				while (!closed && g + cnt < gend && cnt < kMaxStageGroups) {
+					const int64_t gi = g + cnt + lane;
+					const bool in = gi < gend && (cnt + lane) < kMaxStageGroups;
+					const int64_t oe = in ? a.offsets[gi + 1] : row0;
+					const bool fits = in && (oe - row0) <= (int64_t)a.cap_rows;
+					const unsigned m = __ballot_sync(0xffffffffu, fits);
+					const int nfit = (m == 0xffffffffu) ? 32 : (__ffs(~m) - 1);
+					if (lane < nfit) hdr[s].rowstart[cnt + lane + 1] = (uint32_t)(oe - row0);
+					if (nfit > 0) row_end = __shfl_sync(0xffffffffu, oe, nfit - 1);
+					cnt += nfit;
+					if (nfit < 32) closed = true;
+				}
+				if (cnt == 0) {
+					// group g alone exceeds a stage: hand it to the streaming kernel
+					if (lane == 0) {
+						const int slot = atomicAdd(a.big_count, 1);
+						a.big_list[slot] = g;
+					}
+					g += 1;
+					continue;
+				}
+				const int64_t rows = row_end - row0;
+				unsigned char *base = smem + (size_t)s * a.stage_bytes;
+				int lx = 0, ly = 0, lw = 0, lt = 0;
+				uint32_t tx = 0;
+				tx += stage_fetch<8>(base, (const unsigned char *)(a.x + row0 * p), rows * p * 8, lane, &full_bar[s], &lx);
+				tx += stage_fetch<8>(base + a.xcap, (const unsigned char *)(a.y + row0), rows * 8, lane, &full_bar[s], &ly);
+				if (a.w)
+					tx += stage_fetch<8>(base + a.xcap + a.ycap, (const unsigned char *)(a.w + row0), rows * 8, lane,
+					                     &full_bar[s], &lw);
+				if (a.train)
+					tx += stage_fetch<1>(base + a.xcap + a.ycap + a.wcap, a.train + row0, rows, lane, &full_bar[s], &lt);
+				if (lane == 0) {
+					hdr[s].rowstart[0] = 0;
+					hdr[s].g_first = g;
+					hdr[s].count = cnt;
+					hdr[s].lead_x = lx;
+					hdr[s].lead_y = ly;
+					hdr[s].lead_w = lw;
+					hdr[s].lead_t = lt;
+				}
+				__syncwarp();
+				if (lane == 0) {
+					if (tx)
+						mbar_arrive_expect_tx(&full_bar[s], tx);
+					else
+						mbar_arrive(&full_bar[s]);
+				}
+				g += cnt;
+				++it;
+			}
+		}
+		// end marker
+		const int s = it % NS;
+		mbar_wait(&empty_bar[s], (uint32_t)(((it / NS) & 1) ^ 1));
+		if (lane == 0) {
+			hdr[s].count = -1;
+			mbar_arrive(&full_bar[s]);
+		}
+	} else {
+		// ------------------------------ consumers -----------------------------
+		const int cw = warp - 1;
+		for (int it = 0;; ++it) {
+			const int s = it % NS;
+			mbar_wait(&full_bar[s], (uint32_t)((it / NS) & 1));
+			const int cnt = hdr[s].count;
+			if (cnt < 0) break;
+			unsigned char *base = smem + (size_t)s * a.stage_bytes;
+			const double *sx = (const double *)(base + hdr[s].lead_x);
+			const double *sy = (const double *)(base + a.xcap + hdr[s].lead_y);
+			const double *swp = a.w ? (const double *)(base + a.xcap + a.ycap + hdr[s].lead_w) : nullptr;
+			const uint8_t *st = a.train ? (const uint8_t *)(base + a.xcap + a.ycap + a.wcap + hdr[s].lead_t) : nullptr;
+			const int64_t g0 = hdr[s].g_first;
+			for (int i = cw; i < cnt; i += NCW) {
+				const int rb = (int)hdr[s].rowstart[i];
+				const int n = (int)hdr[s].rowstart[i + 1] - rb;
+				accumulate_group<NT, SIDE>(sx + (int64_t)rb * p, sy + rb, swp ? swp + rb : nullptr, st ? st + rb : nullptr,
+				                           n, p, lane, a.records + (g0 + i) * L);
+			}
+			__syncwarp();
+			if (lane == 0) mbar_arrive(&empty_bar[s]);
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// Window bounds: tile_g0[t] = first group whose first row is >= t * window_rows.
+// ---------------------------------------------------------------------------------------------
+__global__ void tile_bounds_kernel(const int64_t *__restrict__ offsets, int64_t n_groups, int64_t window_rows,
+                                   int64_t n_tiles, int64_t *__restrict__ tile_g0) {
+	const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t > n_tiles) return;
+	if (t == n_tiles) {
+		tile_g0[t] = n_groups;
+		return;
+	}
+	const int64_t target = t * window_rows;
+	int64_t lo = 0, hi = n_groups; // first g in [0, G] with offsets[g] >= target
+	while (lo < hi) {
+		const int64_t mid = (lo + hi) >> 1;
+		if (offsets[mid] >= target)
+			hi = mid;
+		else
+			lo = mid + 1;
+	}
+	tile_g0[t] = lo;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Streaming path for groups larger than a stage (and for the row-sharded single group).
+//   step 1  first_valid_kernel : one warp per big group finds its first valid row -> shift
+//   step 2  acc_stream_kernel  : every CTA takes an equal slice of the group's rows; each warp
+//                                accumulates 4-row steps straight from global memory and writes
+//                                one partial record
+//   step 3  reduce_partials_kernel : fixed-order sum of the partial records
+// ---------------------------------------------------------------------------------------------
+struct StreamArgs {
+	const int64_t *offsets; // group mode: rows of big_list[b] are offsets[g] .. offsets[g+1]
+	const int64_t *big_list;
+	const int *big_count;
+	int64_t fixed_rows;     // shard mode (offsets == nullptr): the block is rows [0, fixed_rows)
+	const double *y, *x, *w;
+	const uint8_t *train;
+	int p;
+	double *shift;          // [nbig][p+1]  (shard mode: provided by the caller)
+	int *first_ok;          // [nbig] 1 when a valid row exists
+	double *partials;       // [nbig][n_part][L]
+	int n_part;             // gridDim.x * warps per CTA of acc_stream_kernel
+	double *records;        // group mode: [G][L]; shard mode: [1][L]
+};
+
+__device__ __forceinline__ bool row_valid_full(const StreamArgs &a, int64_t r) {
+	bool ok = row_ok_yw(a.y[r], a.w ? a.w[r] : 1.0, a.train ? (int)a.train[r] : 1, a.w != nullptr);
+	for (int c = 0; ok && c < a.p; ++c) ok = finite_f64(a.x[r * a.p + c]);
+	return ok;
+}
+
+__global__ void first_valid_kernel(const StreamArgs a) {
+	const int b = blockIdx.x;
+	if (b >= *a.big_count) return;
+	const int lane = threadIdx.x;
+	const int64_t g = a.big_list[b];
+	const int64_t r0 = a.offsets[g], r1 = a.offsets[g + 1];
+	int64_t f = -1;
+	for (int64_t base = r0; base < r1 && f < 0; base += 32) {
+		const int64_t r = base + lane;
+		const bool ok = r < r1 && row_valid_full(a, r);
+		const unsigned m = __ballot_sync(0xffffffffu, ok);
+		if (m) f = base + __ffs(m) - 1;
+	}
+	const int k = a.p + 1;
+	if (f >= 0) {
+		for (int c = lane; c < a.p; c += 32) a.shift[(int64_t)b * k + c] = a.x[f * a.p + c];
+		if (lane == 0) a.shift[(int64_t)b * k + a.p] = a.y[f];
+	}
+	if (lane == 0) a.first_ok[b] = f >= 0 ? 1 : 0;
+}
+
+template <int NT, bool SIDE, int NW> __global__ void __launch_bounds__(32 * NW) acc_stream_kernel(const StreamArgs a) {
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cl = lane >> 2;
+	const int p = a.p, k = p + 1, L = rec_len(p);
+	const int nbig = a.offsets ? *a.big_count : 1;
+	for (int b = 0; b < nbig; ++b) {
+		int64_t r0 = 0, r1 = a.fixed_rows;
+		if (a.offsets) {
+			const int64_t g = a.big_list[b];
+			r0 = a.offsets[g];
+			r1 = a.offsets[g + 1];
+		}
+		double *part = a.partials + ((int64_t)b * a.n_part + (int64_t)blockIdx.x * NW + warp) * L;
+		if (a.first_ok && !a.first_ok[b]) {
+			store_empty_record(part, p, lane, 0);
+			continue;
+		}
+		// equal contiguous slices per warp, multiples of 4 rows
+		const int64_t nrows = r1 - r0;
+		const int64_t nw_total = (int64_t)gridDim.x * NW;
+		int64_t per = (nrows + nw_total - 1) / nw_total;
+		per = (per + 3) & ~(int64_t)3;
+		const int64_t wid = (int64_t)blockIdx.x * NW + warp;
+		int64_t wb = r0 + wid * per, we = wb + per;
+		if (wb > r1) wb = r1;
+		if (we > r1) we = r1;
+		double sh[NT], shy;
+#pragma unroll
+		for (int t = 0; t < NT; ++t) {
+			const int c = 8 * t + cl;
+			sh[t] = (c < p) ? a.shift[(int64_t)b * k + c] : 0.0;
+		}
+		shy = a.shift[(int64_t)b * k + p];
+		WarpAcc<NT, SIDE> A;
+		A.clear();
+		// chunks keep the int row index of acc_rows in range
+		for (int64_t cb = wb; cb < we; cb += (1 << 20)) {
+			const int64_t ce = cb + (1 << 20) < we ? cb + (1 << 20) : we;
+			acc_rows<NT, SIDE, true>(A, a.x + cb * p, a.y + cb, a.w ? a.w + cb : nullptr, a.train ? a.train + cb : nullptr,
+			                         0, (int)(ce - cb), p, lane, sh, shy);
+		}
+		store_record<NT, SIDE>(A, part, p, lane, sh, shy, -1);
+	}
+}
+
+// Sum the partial records of each big group in a fixed order: n, sw, n_state, S1, S2 add; cdev
+// takes the max; the shift is common to all partials.
+__global__ void reduce_partials_kernel(const StreamArgs a) {
+	const int b = blockIdx.y;
+	const int nbig = a.offsets ? *a.big_count : 1;
+	if (b >= nbig) return;
+	const int p = a.p, L = rec_len(p);
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= L) return;
+	const int64_t g = a.offsets ? a.big_list[b] : 0;
+	const double *part = a.partials + (int64_t)b * a.n_part * L;
+	double v;
+	if (i >= rec_off_shift(p) && i < rec_off_cdev(p)) {
+		v = a.shift[(int64_t)b * (p + 1) + (i - rec_off_shift(p))];
+	} else if (i >= rec_off_cdev(p) && i < rec_off_s1(p)) {
+		v = 0.0;
+		for (int q = 0; q < a.n_part; ++q) v = fmax(v, part[(int64_t)q * L + i]);
+	} else if (i == 3) {
+		v = 0.0;
+	} else {
+		v = 0.0;
+		for (int q = 0; q < a.n_part; ++q) v += part[(int64_t)q * L + i];
+	}
+	a.records[g * L + i] = v;
+}
+
+} // namespace b200

@@ -1,0 +1,95 @@
+// common.cuh -- shared definitions of the B200 group-fit kernels (sm_100a only).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/anofox_b200.h"
+
+namespace b200 {
+
+// -------------------------------------------------------------------------------------------
+// Moment record: what the accumulation stage hands to the solve stage, one per group.
+// All sums are taken over VALID rows (finite y and x, w > 0 and finite, training flag set)
+// of d = z - shift, z = (x_1 .. x_p, y), shift = the group's first valid row (which is also
+// the row the reference's constant-column test compares against, ols.rs:76-87).
+//   [0] n_valid   [1] sum w   [2] n_state (rows that entered the aggregate state)   [3] spare
+//   shift[k]      k = p + 1
+//   cdev[p]       max |x_j - shift_j| over valid rows
+//   S1[k]         sum w d
+//   S2[k(k+1)/2]  sum w d d^T, packed upper triangle, row-major: (i,j), i <= j
+// n, sw, S1, S2 add across row shards that share a shift; cdev combines with max.
+// -------------------------------------------------------------------------------------------
+__host__ __device__ inline int rec_off_shift(int) { return 4; }
+__host__ __device__ inline int rec_off_cdev(int p) { return 4 + (p + 1); }
+__host__ __device__ inline int rec_off_s1(int p) { return 4 + (p + 1) + p; }
+__host__ __device__ inline int rec_off_s2(int p) { return 4 + (p + 1) + p + (p + 1); }
+__host__ __device__ inline int rec_len(int p) { return rec_off_s2(p) + (p + 1) * (p + 2) / 2; }
+__host__ __device__ inline int tri_idx(int i, int j, int k) { return i * k - (i * (i - 1)) / 2 + (j - i); } // i <= j
+
+constexpr int kMaxFeatures = 64;
+constexpr int kMaxStageGroups = 512; // groups packed into one smem stage at most
+constexpr int kTcritTable = 4096;    // t-critical values precomputed for df = 1 .. kTcritTable
+
+struct FitParams {
+	int p;
+	int method;
+	int fit_intercept;
+	int compute_inference;
+	int lambda_scaling;
+	double level;
+	double alpha;
+	const double *tcrit; // [kTcritTable + 1] device table for `level`, index = df
+	int predict_mode;    // 1: df for t-critical follows anofox_predict_with_interval
+	int min_state_rows;  // 2 = aggregate rule (ols_aggregate.cpp:263-267); 0 = direct anofox_*_fit call
+};
+
+__device__ __forceinline__ bool finite_f64(double v) {
+	return (__double2hiint(v) & 0x7ff00000) != 0x7ff00000;
+}
+
+__device__ __forceinline__ double nan_f64() { return __longlong_as_double(0x7ff8000000000000LL); }
+
+// ---- mbarrier / bulk-copy (TMA) primitives ------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+	asm volatile(
+	    "{\n"
+	    " .reg .pred p;\n"
+	    "WAIT_%=:\n"
+	    " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+	    " @p bra DONE_%=;\n"
+	    " bra WAIT_%=;\n"
+	    "DONE_%=:\n"
+	    "}\n" ::"r"(smem_u32(bar)),
+	    "r"(parity)
+	    : "memory");
+}
+// One contiguous global -> shared bulk copy (SASS: UBLKCP). dst/src 16-byte aligned, bytes % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+	                 smem_u32(dst)),
+	             "l"(src), "r"(bytes), "r"(smem_u32(bar))
+	             : "memory");
+}
+
+// FP64 tensor-core MMA, D(8x8) += A(8x4, row) * B(4x8, col).  SASS: DMMA.8x8x4.
+// Fragment layout (PTX ISA): a = A[lane/4][lane%4], b = B[lane%4][lane/4],
+// c0,c1 = C[lane/4][2*(lane%4) + {0,1}].
+__device__ __forceinline__ void dmma_884(double &c0, double &c1, double a, double b) {
+	asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+	             : "+d"(c0), "+d"(c1)
+	             : "d"(a), "d"(b));
+}
+
+} // namespace b200

@@ -1,0 +1,1311 @@
+// groupfit.cu -- kernels' launch side and the C ABI of libanofox_stats_b200.so (include/anofox_b200.h).
+//
+// Host-side mirror of the reference interface for this path:
+//   anofox_{ols,ridge,wls}_fit ........ crates/anofox-stats-ffi/src/lib.rs:98-265, :984-1155, :1384-1555
+//   anofox_free_result_* .............. lib.rs:272-311
+//   anofox_t_critical / predict ....... lib.rs:2217-2231, :2266-2350
+//   anofox_compute_aic / _bic ......... lib.rs:1932-2010
+// plus the batch layer the DuckDB Finalize (ols_aggregate.cpp:249-338) should call instead of one
+// FFI call per group. There is NO CPU implementation behind these entry points: every fit runs the
+// CUDA kernels below, and a missing / unsuitable device is an error.
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "accumulate.cuh"
+#include "common.cuh"
+#include "solve.cuh"
+#include "specfun.cuh"
+
+namespace b200 {
+
+static std::atomic<long long> g_launches{0};
+#define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
+
+// Optional per-stage timing (bench.py's roofline leg): CUDA events recorded on the caller's stream
+// around the accumulation kernel and around the solve + refine kernels of every batched call.
+struct StageTimer {
+	std::mutex mu;
+	bool enabled = false;
+	std::vector<cudaEvent_t> ev; // triples: before accumulate, after accumulate, after solve/refine
+	void clear() {
+		for (auto e : ev) cudaEventDestroy(e);
+		ev.clear();
+	}
+};
+static StageTimer &stage_timer() {
+	static StageTimer t;
+	return t;
+}
+static cudaEvent_t timer_mark(cudaStream_t st) {
+	StageTimer &t = stage_timer();
+	if (!t.enabled) return nullptr;
+	std::lock_guard<std::mutex> lock(t.mu);
+	cudaEvent_t e = nullptr;
+	if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+	cudaEventRecord(e, st);
+	t.ev.push_back(e);
+	return e;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Small kernels
+// ---------------------------------------------------------------------------------------------
+__global__ void tcrit_table_kernel(double level, double *__restrict__ table) {
+	const int df = blockIdx.x * blockDim.x + threadIdx.x;
+	if (df > kTcritTable) return;
+	table[df] = df == 0 ? nan_f64() : t_critical_dev(level, (double)df);
+}
+
+template <int PMAX>
+__global__ void __launch_bounds__(128) solve_kernel(const double *__restrict__ records, int64_t n_groups, FitParams P,
+                                                    AnofoxB200FitOutputs o, int *refine_count, int64_t *refine_list) {
+	const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= n_groups) return;
+	solve_group<PMAX>(records + g * rec_len(P.p), 1, g, P, o, -1.0, nullptr, refine_count, refine_list);
+}
+
+// Exact residual pass for the groups the solve stage queued (residual sum of squares too small
+// relative to the total for the moment form to keep 1e-9): one warp per queued group re-reads the
+// group's rows, forms sum w (y - b0 - x'b)^2 with the coefficients just written (NaN = aliased,
+// contributes nothing -- lib.rs:2296-2303) and re-runs the statistics with that value.
+struct RefineArgs {
+	const int64_t *offsets;
+	const double *y, *x, *w;
+	const uint8_t *train;
+	const double *records;
+	const int *refine_count;
+	const int64_t *refine_list;
+};
+template <int PMAX>
+__global__ void __launch_bounds__(256) refine_kernel(RefineArgs a, FitParams P, AnofoxB200FitOutputs o) {
+	const int lane = threadIdx.x & 31;
+	const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+	const int count = *a.refine_count;
+	const int p = P.p;
+	for (int q = wid; q < count; q += nw) {
+		const int64_t g = a.refine_list[q];
+		const int64_t r0 = a.offsets[g], r1 = a.offsets[g + 1];
+		const double icpt = o.intercept[g];
+		const double b0 = isnan(icpt) ? 0.0 : icpt;
+		const double *coef = o.coefficients + g * p;
+		double rss = 0.0;
+		for (int64_t r = r0 + lane; r < r1; r += 32) {
+			const double yv = a.y[r];
+			const double wv = a.w ? a.w[r] : 1.0;
+			bool ok = row_ok_yw(yv, wv, a.train ? (int)a.train[r] : 1, a.w != nullptr);
+			double fit = b0;
+			for (int j = 0; j < p; ++j) {
+				const double xv = a.x[r * p + j];
+				ok = ok && finite_f64(xv);
+				const double c = coef[j];
+				if (!isnan(c)) fit = fma(c, xv, fit);
+			}
+			if (ok) {
+				const double e = yv - fit;
+				rss = fma(wv * e, e, rss);
+			}
+		}
+		for (int off = 16; off; off >>= 1) rss += __shfl_xor_sync(0xffffffffu, rss, off);
+		if (lane == 0) solve_group<PMAX>(a.records + g * rec_len(p), 1, g, P, o, rss, nullptr, nullptr, nullptr);
+	}
+}
+
+// mode 0: two-sided t p-value (a = t, b = df); 1: t critical (a = level, b = df); 2: F upper tail (a = f, b = d1, c = d2)
+__global__ void specfun_eval_kernel(int mode, int n, const double *a, const double *b, const double *c, double *out) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	if (mode == 0)
+		out[i] = t_two_sided_p(a[i], b[i]);
+	else if (mode == 1)
+		out[i] = t_critical_dev(a[i], b[i]);
+	else
+		out[i] = f_upper_p(a[i], b[i], c[i]);
+}
+
+// Default training rule of ols_predict_aggregate.cpp:216-239 when the caller passes no flags:
+// y present (NaN stands for NULL) and no missing feature.
+__global__ void default_train_kernel(const double *__restrict__ y, const double *__restrict__ x, int64_t n_rows, int p,
+                                     uint8_t *__restrict__ flag) {
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= n_rows) return;
+	bool tr = !isnan(y[r]);
+	for (int j = 0; tr && j < p; ++j) tr = !isnan(x[r * p + j]);
+	flag[r] = tr ? 1 : 0;
+}
+
+// One warp per group: yhat and the simplified interval of anofox_predict_with_interval
+// (lib.rs:2292-2347) for every row of the group, in input order.
+__global__ void predict_kernel(const int64_t *__restrict__ offsets, int64_t n_groups, const double *__restrict__ x,
+                               int p, FitParams P, AnofoxB200FitOutputs fit, AnofoxB200PredictOutputs out) {
+	const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (g >= n_groups) return;
+	const int64_t r0 = offsets[g], r1 = offsets[g + 1];
+	const double nanv = nan_f64();
+	const bool ok = fit.status[g] == 0;
+	double b0 = 0.0, margin = 0.0;
+	const double *coef = fit.coefficients + g * p;
+	if (ok) {
+		const double icpt = fit.intercept[g];
+		const bool has_i = !isnan(icpt);
+		b0 = has_i ? icpt : 0.0;
+		const double rse = fit.residual_std_error[g];
+		const int64_t n = fit.n_observations[g];
+		if (!(isnan(rse) || rse <= 0.0 || n <= (int64_t)p + 1)) {
+			const int64_t kk = (int64_t)p + (has_i ? 1 : 0);
+			const int64_t df = n > kk ? n - kk : 0;
+			if (df > 0) {
+				const double tc = (P.tcrit && df <= kTcritTable) ? P.tcrit[df] : t_critical_dev(P.level, (double)df);
+				if (!isnan(tc)) margin = tc * (rse * sqrt(1.0 + 1.0 / (double)n));
+			}
+		}
+	}
+	for (int64_t r = r0 + lane; r < r1; r += 32) {
+		double yh = nanv, lo = nanv, hi = nanv;
+		if (ok) {
+			double s = b0;
+			for (int j = 0; j < p; ++j) {
+				const double c = coef[j];
+				if (!isnan(c)) s += c * x[r * p + j];
+			}
+			if (finite_f64(s)) { // ols_predict_aggregate.cpp:409-417
+				yh = s;
+				lo = s - margin;
+				hi = s + margin;
+			}
+		}
+		out.yhat[r] = yh;
+		out.yhat_lower[r] = lo;
+		out.yhat_upper[r] = hi;
+	}
+}
+
+// Shifted moment block of the row-sharded path -> standard record. The block layout is the
+// record without header rewrite: we only need to splice shift and cdev in.
+__global__ void assemble_record_kernel(const double *__restrict__ moments, const double *__restrict__ cdev,
+                                       const double *__restrict__ shift, int p, double *__restrict__ rec) {
+	const int L = rec_len(p);
+	for (int i = threadIdx.x; i < L; i += blockDim.x) {
+		double v;
+		if (i < 4)
+			v = moments[i];
+		else if (i < rec_off_cdev(p))
+			v = shift[i - rec_off_shift(p)];
+		else if (i < rec_off_s1(p))
+			v = cdev[i - rec_off_cdev(p)];
+		else
+			v = moments[4 + (i - rec_off_s1(p))];
+		rec[i] = v;
+	}
+}
+__global__ void split_record_kernel(const double *__restrict__ rec, int p, double *__restrict__ moments,
+                                    double *__restrict__ cdev) {
+	const int L = rec_len(p);
+	for (int i = threadIdx.x; i < L; i += blockDim.x) {
+		const double v = rec[i];
+		if (i < 4)
+			moments[i] = (i == 3) ? 0.0 : v;
+		else if (i < rec_off_cdev(p)) {
+		} else if (i < rec_off_s1(p))
+			cdev[i - rec_off_cdev(p)] = v;
+		else
+			moments[4 + (i - rec_off_s1(p))] = v;
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// Dispatch on the feature count
+// ---------------------------------------------------------------------------------------------
+struct Shape {
+	int nt;
+	bool side;
+};
+static Shape shape_of(int p) {
+	const int r = p % 8;
+	const bool side = (r == 0 || r == 7);
+	const int nt = side ? (p + 7) / 8 : (p + 2 + 7) / 8;
+	return {nt, side};
+}
+
+template <int NT, bool SIDE, int NCW> static cudaError_t launch_resident_t(const AccArgs &a, int grid, cudaStream_t st) {
+	auto kern = acc_resident_kernel<NT, SIDE, NCW>;
+	const size_t dyn = (size_t)a.n_stages * a.stage_bytes;
+	cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+	if (e != cudaSuccess) return e;
+	kern<<<grid, 32 * (NCW + 1), dyn, st>>>(a);
+	LAUNCHED();
+	return cudaGetLastError();
+}
+
+static cudaError_t launch_resident(const AccArgs &a, int grid, cudaStream_t st) {
+	const Shape s = shape_of(a.p);
+#define CASE(NT_, NCW_)                                                                                              \
+	case NT_:                                                                                                        \
+		return s.side ? launch_resident_t<NT_, true, NCW_>(a, grid, st) : launch_resident_t<NT_, false, NCW_>(a, grid, st);
+	switch (s.nt) {
+		CASE(1, 16)
+		CASE(2, 16)
+		CASE(3, 8)
+		CASE(4, 8)
+		CASE(5, 4)
+		CASE(6, 4)
+		CASE(7, 4)
+		CASE(8, 4)
+		CASE(9, 4)
+	}
+#undef CASE
+	return cudaErrorInvalidValue;
+}
+
+constexpr int kStreamWarps = 8;
+
+// Big-group streaming: each warp owns an equal slice of every big group (partials = grid * warps).
+template <int NT, bool SIDE> static cudaError_t launch_stream_t(const StreamArgs &a, int grid, cudaStream_t st) {
+	acc_stream_kernel<NT, SIDE, kStreamWarps><<<grid, 32 * kStreamWarps, 0, st>>>(a);
+	LAUNCHED();
+	return cudaGetLastError();
+}
+static cudaError_t launch_stream(const StreamArgs &a, int grid, cudaStream_t st) {
+	const Shape s = shape_of(a.p);
+#define CASE(NT_)                                                                                                    \
+	case NT_:                                                                                                        \
+		return s.side ? launch_stream_t<NT_, true>(a, grid, st) : launch_stream_t<NT_, false>(a, grid, st);
+	switch (s.nt) {
+		CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8) CASE(9)
+	}
+#undef CASE
+	return cudaErrorInvalidValue;
+}
+
+static cudaError_t launch_solve(const double *records, int64_t G, const FitParams &P, const AnofoxB200FitOutputs &o,
+                                int *refine_count, int64_t *refine_list, cudaStream_t st) {
+	if (G <= 0) return cudaSuccess;
+	const int threads = 128;
+	const unsigned blocks = (unsigned)((G + threads - 1) / threads);
+	if (P.p <= 8)
+		solve_kernel<8><<<blocks, threads, 0, st>>>(records, G, P, o, refine_count, refine_list);
+	else if (P.p <= 16)
+		solve_kernel<16><<<blocks, threads, 0, st>>>(records, G, P, o, refine_count, refine_list);
+	else if (P.p <= 32)
+		solve_kernel<32><<<blocks, threads, 0, st>>>(records, G, P, o, refine_count, refine_list);
+	else
+		solve_kernel<64><<<blocks, threads, 0, st>>>(records, G, P, o, refine_count, refine_list);
+	LAUNCHED();
+	return cudaGetLastError();
+}
+
+static cudaError_t launch_refine(const RefineArgs &a, const FitParams &P, const AnofoxB200FitOutputs &o, int sms,
+                                 cudaStream_t st) {
+	const int blocks = sms * 2;
+	if (P.p <= 8)
+		refine_kernel<8><<<blocks, 256, 0, st>>>(a, P, o);
+	else if (P.p <= 16)
+		refine_kernel<16><<<blocks, 256, 0, st>>>(a, P, o);
+	else if (P.p <= 32)
+		refine_kernel<32><<<blocks, 256, 0, st>>>(a, P, o);
+	else
+		refine_kernel<64><<<blocks, 256, 0, st>>>(a, P, o);
+	LAUNCHED();
+	return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Device properties / stage geometry
+// ---------------------------------------------------------------------------------------------
+struct DeviceInfo {
+	int sms = 0;
+	int cc_major = 0;
+	size_t smem_optin = 0;
+	bool ok = false;
+	char why[200] = {0};
+};
+static DeviceInfo &device_info() {
+	static DeviceInfo info;
+	static std::once_flag once;
+	std::call_once(once, [] {
+		int n = 0;
+		cudaError_t e = cudaGetDeviceCount(&n);
+		if (e != cudaSuccess || n == 0) {
+			snprintf(info.why, sizeof info.why, "no CUDA device: %s", e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
+			return;
+		}
+		int dev = 0;
+		cudaGetDevice(&dev);
+		cudaDeviceProp pr;
+		if ((e = cudaGetDeviceProperties(&pr, dev)) != cudaSuccess) {
+			snprintf(info.why, sizeof info.why, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+			return;
+		}
+		info.sms = pr.multiProcessorCount;
+		info.cc_major = pr.major;
+		info.smem_optin = pr.sharedMemPerBlockOptin;
+		if (pr.major != 10) {
+			snprintf(info.why, sizeof info.why, "device %s is sm_%d%d; this library is built for sm_100a only", pr.name,
+			         pr.major, pr.minor);
+			return;
+		}
+		info.ok = true;
+	});
+	return info;
+}
+
+struct StageGeom {
+	int cap_rows, xcap, ycap, wcap, tcap, stage_bytes, n_stages;
+	int64_t window_rows;
+};
+static inline int align16(int64_t v) { return (int)((v + 15) & ~(int64_t)15); }
+
+// Choose the stage size from the mean group size: a stage should hold several groups, and the ring
+// should keep >= ~96 KB in flight per SM (microbenchmark: 4 x 32 KB stages reach 7.3 TB/s).
+static StageGeom stage_geometry(int p, bool has_w, bool has_t, int64_t n_rows, int64_t n_groups) {
+	const int64_t row_bytes = 8 * (int64_t)(p + 1) + (has_w ? 8 : 0) + (has_t ? 1 : 0);
+	const int64_t budget = 196 * 1024; // dynamic shared memory for the ring
+	const double mean_rows = n_groups > 0 ? (double)n_rows / (double)n_groups : 1.0;
+	int64_t want = (int64_t)(4.0 * mean_rows * (double)row_bytes);
+	int64_t stage = 32 * 1024;
+	while (stage < want && stage < budget / 2) stage += 16 * 1024;
+	if (stage > budget / 2) stage = budget / 2;
+	StageGeom g;
+	g.n_stages = (int)std::min<int64_t>(6, budget / stage);
+	const int64_t overhead = 4 * 32; // alignment slack of the regions
+	g.cap_rows = (int)((stage - overhead) / row_bytes);
+	if (g.cap_rows < 4) g.cap_rows = 4;
+	g.xcap = align16((int64_t)g.cap_rows * p * 8 + 16);
+	g.ycap = align16((int64_t)g.cap_rows * 8 + 16);
+	g.wcap = has_w ? align16((int64_t)g.cap_rows * 8 + 16) : 0;
+	g.tcap = has_t ? align16((int64_t)g.cap_rows + 32) : 0;
+	g.stage_bytes = (g.xcap + g.ycap + g.wcap + g.tcap + 127) & ~127;
+	while ((int64_t)g.n_stages * g.stage_bytes > budget + 8 * 1024 && g.n_stages > 2) --g.n_stages;
+	g.window_rows = (int64_t)g.cap_rows * 8;
+	return g;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Workspace carving
+// ---------------------------------------------------------------------------------------------
+struct Workspace {
+	double *records;
+	int64_t *tile_g0;
+	int64_t *big_list;
+	int *big_count;
+	double *tcrit;
+	double *shift;
+	int *first_ok;
+	double *partials;
+	int64_t *refine_list;
+	int *refine_count;
+	uint8_t *train_tmp;
+	// fit outputs used internally by the predict path when the caller passes none
+	double *f_coef, *f_icpt, *f_r2, *f_adj, *f_rse;
+	int64_t *f_nobs;
+	int32_t *f_status;
+	size_t bytes;
+	int64_t nbig_max;
+	int n_part;
+};
+
+static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int p, int sms) {
+	size_t off = 0;
+	auto take = [&](size_t bytes) {
+		size_t o = off;
+		off += (bytes + 255) & ~(size_t)255;
+		return base ? base + o : (unsigned char *)nullptr;
+	};
+	const int L = rec_len(p);
+	const StageGeom sg = stage_geometry(p, true, true, N, G);
+	const int64_t n_tiles = (N + sg.window_rows - 1) / sg.window_rows + 1;
+	// big groups hold more than cap_rows rows each (cap_rows depends on w/train only mildly: use the
+	// smallest capacity for the bound)
+	w.nbig_max = std::min<int64_t>(G, N / std::max(1, sg.cap_rows) + 1);
+	w.n_part = sms * 2 * kStreamWarps;
+	w.records = (double *)take((size_t)std::max<int64_t>(G, 1) * L * 8);
+	w.tile_g0 = (int64_t *)take((size_t)(n_tiles + 2) * 8);
+	w.big_list = (int64_t *)take((size_t)(w.nbig_max + 1) * 8);
+	w.big_count = (int *)take(256);
+	w.tcrit = (double *)take((size_t)(kTcritTable + 1) * 8);
+	w.shift = (double *)take((size_t)(w.nbig_max + 1) * (p + 1) * 8);
+	w.first_ok = (int *)take((size_t)(w.nbig_max + 1) * 4);
+	// partial records of the streaming path: one per (big group, warp). Bounded by capping how many
+	// big groups one call may hold (see fit_device); sized here for that cap.
+	const int64_t part_groups = std::min<int64_t>(w.nbig_max, 64);
+	w.partials = (double *)take((size_t)part_groups * w.n_part * L * 8);
+	w.refine_list = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
+	w.refine_count = (int *)take(256);
+	w.train_tmp = (uint8_t *)take((size_t)std::max<int64_t>(N, 1));
+	w.f_coef = (double *)take((size_t)std::max<int64_t>(G, 1) * p * 8);
+	w.f_icpt = (double *)take((size_t)std::max<int64_t>(G, 1) * 8);
+	w.f_r2 = (double *)take((size_t)std::max<int64_t>(G, 1) * 8);
+	w.f_adj = (double *)take((size_t)std::max<int64_t>(G, 1) * 8);
+	w.f_rse = (double *)take((size_t)std::max<int64_t>(G, 1) * 8);
+	w.f_nobs = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
+	w.f_status = (int32_t *)take((size_t)std::max<int64_t>(G, 1) * 4);
+	w.bytes = off;
+	return off;
+}
+
+static void set_error(AnofoxError *err, int code, const char *msg) {
+	if (!err) return;
+	err->code = (AnofoxErrorCode)code;
+	strncpy(err->message, msg ? msg : "", 255);
+	err->message[255] = 0;
+}
+static void clear_error(AnofoxError *err) {
+	if (!err) return;
+	err->code = ANOFOX_ERROR_SUCCESS;
+	memset(err->message, 0, sizeof err->message);
+}
+static int cuda_fail(AnofoxError *err, cudaError_t e, const char *where) {
+	char buf[256];
+	snprintf(buf, sizeof buf, "CUDA error in %s: %s", where, cudaGetErrorString(e));
+	set_error(err, ANOFOX_ERROR_INTERNAL, buf);
+	return ANOFOX_ERROR_INTERNAL;
+}
+#define CU(call, where)                                                                                              \
+	do {                                                                                                             \
+		cudaError_t e__ = (call);                                                                                    \
+		if (e__ != cudaSuccess) return cuda_fail(err, e__, where);                                                   \
+	} while (0)
+
+static int validate_common(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w,
+                           int64_t N, int p, const AnofoxB200FitOptions *opt, AnofoxError *err) {
+	clear_error(err);
+	if (!opt) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "options is NULL");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (G < 0 || N < 0 || p <= 0 || !offsets || (N > 0 && (!y || !x))) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "x is NULL or empty"); // lib.rs:120-125
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (p > kMaxFeatures) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "more than 64 features are not supported by the B200 path");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (opt->method < ANOFOX_B200_OLS || opt->method > ANOFOX_B200_WLS) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "unknown method");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (opt->method == ANOFOX_B200_RIDGE && opt->alpha < 0.0) { // ridge.rs:38-40
+		set_error(err, ANOFOX_ERROR_INVALID_ALPHA, "Invalid alpha: must be >= 0");
+		return ANOFOX_ERROR_INVALID_ALPHA;
+	}
+	if (opt->method == ANOFOX_B200_WLS && !w && N > 0) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "weights is NULL");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (opt->hc_type != ANOFOX_HC_NONE) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "hc_type: robust standard errors are outside the B200 path");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	DeviceInfo &di = device_info();
+	if (!di.ok) {
+		set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+		return ANOFOX_ERROR_INTERNAL;
+	}
+	return 0;
+}
+
+// The whole device pipeline for one batch. `train` non-null selects predict semantics.
+static int fit_device(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w,
+                      const uint8_t *train, int64_t N, int p, const AnofoxB200FitOptions *opt,
+                      const AnofoxB200FitOutputs &out, const AnofoxB200PredictOutputs *pred, void *workspace,
+                      size_t workspace_bytes, cudaStream_t st, AnofoxError *err, int min_state_rows = 2) {
+	DeviceInfo &di = device_info();
+	Workspace ws;
+	const size_t need = carve(ws, (unsigned char *)workspace, G, N, p, di.sms);
+	if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 255)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "workspace too small or misaligned (anofox_b200_workspace_bytes)");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (G == 0) return 0;
+	const bool wls = opt->method == ANOFOX_B200_WLS;
+	const double *wuse = wls ? w : nullptr; // weights only matter for WLS (ols.rs / ridge.rs take none)
+
+	FitParams P;
+	P.p = p;
+	P.method = opt->method;
+	P.fit_intercept = opt->fit_intercept != 0;
+	P.compute_inference = pred ? 0 : (opt->compute_inference != 0); // ols_predict_aggregate.cpp:354-364
+	P.lambda_scaling = opt->lambda_scaling;
+	P.level = opt->confidence_level;
+	P.alpha = opt->alpha;
+	P.tcrit = ws.tcrit;
+	P.predict_mode = pred ? 1 : 0;
+	P.min_state_rows = min_state_rows;
+
+	if (P.compute_inference || pred) {
+		tcrit_table_kernel<<<(kTcritTable + 1 + 127) / 128, 128, 0, st>>>(P.level, ws.tcrit);
+		LAUNCHED();
+		CU(cudaGetLastError(), "tcrit_table_kernel");
+	}
+
+	const uint8_t *train_use = nullptr;
+	if (pred) {
+		if (train) {
+			train_use = train;
+			if (pred->is_training) CU(cudaMemcpyAsync(pred->is_training, train, (size_t)N, cudaMemcpyDeviceToDevice, st), "copy train");
+		} else {
+			uint8_t *flags = pred->is_training ? pred->is_training : ws.train_tmp;
+			if (N > 0) {
+				default_train_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(y, x, N, p, flags);
+				LAUNCHED();
+				CU(cudaGetLastError(), "default_train_kernel");
+			}
+			train_use = flags;
+		}
+	}
+
+	const StageGeom sg = stage_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
+	const int64_t n_tiles = (N + sg.window_rows - 1) / sg.window_rows + 1; // +1: groups that start at row N
+	CU(cudaMemsetAsync(ws.big_count, 0, 256, st), "memset");
+	tile_bounds_kernel<<<(unsigned)((n_tiles + 1 + 255) / 256), 256, 0, st>>>(offsets, G, sg.window_rows, n_tiles, ws.tile_g0);
+	LAUNCHED();
+	CU(cudaGetLastError(), "tile_bounds_kernel");
+
+	AccArgs a;
+	a.offsets = offsets;
+	a.y = y;
+	a.x = x;
+	a.w = wuse;
+	a.train = train_use;
+	a.n_groups = G;
+	a.p = p;
+	a.tile_g0 = ws.tile_g0;
+	a.n_tiles = n_tiles;
+	a.records = ws.records;
+	a.big_list = ws.big_list;
+	a.big_count = ws.big_count;
+	a.cap_rows = sg.cap_rows;
+	a.stage_bytes = sg.stage_bytes;
+	a.xcap = sg.xcap;
+	a.ycap = sg.ycap;
+	a.wcap = sg.wcap;
+	a.n_stages = sg.n_stages;
+	const int grid = (int)std::min<int64_t>(di.sms, n_tiles);
+	timer_mark(st);
+	CU(launch_resident(a, grid, st), "acc_resident_kernel");
+	timer_mark(st);
+
+	// Big groups (rare): the count decides whether the streaming kernels run at all.
+	if (N > sg.cap_rows) {
+		int nbig = 0;
+		CU(cudaMemcpyAsync(&nbig, ws.big_count, sizeof(int), cudaMemcpyDeviceToHost, st), "read big_count");
+		CU(cudaStreamSynchronize(st), "sync");
+		for (int b0 = 0; b0 < nbig; b0 += 64) {
+			const int nb = std::min(64, nbig - b0);
+			int *cnt = ws.big_count + 1; // scratch count for this slice
+			CU(cudaMemcpyAsync(cnt, &nb, sizeof(int), cudaMemcpyHostToDevice, st), "slice count");
+			StreamArgs s;
+			s.offsets = offsets;
+			s.big_list = ws.big_list + b0;
+			s.big_count = cnt;
+			s.fixed_rows = 0;
+			s.y = y;
+			s.x = x;
+			s.w = wuse;
+			s.train = train_use;
+			s.p = p;
+			s.shift = ws.shift;
+			s.first_ok = ws.first_ok;
+			s.partials = ws.partials;
+			s.n_part = ws.n_part;
+			s.records = ws.records;
+			first_valid_kernel<<<nb, 32, 0, st>>>(s);
+			LAUNCHED();
+			CU(cudaGetLastError(), "first_valid_kernel");
+			CU(launch_stream(s, ws.n_part / kStreamWarps, st), "acc_stream_kernel");
+			dim3 rg((unsigned)((rec_len(p) + 127) / 128), (unsigned)nb);
+			reduce_partials_kernel<<<rg, 128, 0, st>>>(s);
+			LAUNCHED();
+			CU(cudaGetLastError(), "reduce_partials_kernel");
+			CU(cudaStreamSynchronize(st), "sync"); // nb lives on the host stack
+		}
+	}
+
+	AnofoxB200FitOutputs fo = out;
+	if (!fo.coefficients) { // predict path without fit outputs: use workspace arrays
+		memset(&fo, 0, sizeof fo);
+		fo.coefficients = ws.f_coef;
+		fo.intercept = ws.f_icpt;
+		fo.r_squared = ws.f_r2;
+		fo.adj_r_squared = ws.f_adj;
+		fo.residual_std_error = ws.f_rse;
+		fo.n_observations = ws.f_nobs;
+		fo.status = ws.f_status;
+	}
+	CU(cudaMemsetAsync(ws.refine_count, 0, 256, st), "memset");
+	CU(launch_solve(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_kernel");
+	{
+		RefineArgs ra;
+		ra.offsets = offsets;
+		ra.y = y;
+		ra.x = x;
+		ra.w = wuse;
+		ra.train = train_use;
+		ra.records = ws.records;
+		ra.refine_count = ws.refine_count;
+		ra.refine_list = ws.refine_list;
+		CU(launch_refine(ra, P, fo, di.sms, st), "refine_kernel");
+	}
+	timer_mark(st);
+
+	if (pred && N > 0) {
+		const int threads = 256;
+		const unsigned blocks = (unsigned)((G * 32 + threads - 1) / threads);
+		predict_kernel<<<blocks, threads, 0, st>>>(offsets, G, x, p, P, fo, *pred);
+		LAUNCHED();
+		CU(cudaGetLastError(), "predict_kernel");
+	}
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host-pointer path: library-owned device buffers
+// ---------------------------------------------------------------------------------------------
+struct HostContext {
+	std::mutex mu;
+	cudaStream_t stream = nullptr;
+	unsigned char *dev = nullptr;
+	size_t dev_bytes = 0;
+	int ensure(size_t bytes, AnofoxError *err) {
+		if (!stream) CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "cudaStreamCreate");
+		if (bytes > dev_bytes) {
+			if (dev) cudaFree(dev);
+			dev = nullptr;
+			dev_bytes = 0;
+			size_t want = bytes + bytes / 8;
+			cudaError_t e = cudaMalloc(&dev, want);
+			if (e != cudaSuccess) {
+				set_error(err, ANOFOX_ERROR_ALLOCATION_FAILURE, cudaGetErrorString(e));
+				return ANOFOX_ERROR_ALLOCATION_FAILURE;
+			}
+			dev_bytes = want;
+		}
+		return 0;
+	}
+};
+static HostContext &host_ctx() {
+	static HostContext c;
+	return c;
+}
+
+struct DevLayout { // device mirror of one host batch
+	size_t off = 0;
+	size_t take(size_t bytes) {
+		size_t o = off;
+		off += (bytes + 255) & ~(size_t)255;
+		return o;
+	}
+};
+
+static int fit_host(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w,
+                    const uint8_t *train, int64_t N, int p, const AnofoxB200FitOptions *opt,
+                    const AnofoxB200FitOutputs *out, const AnofoxB200PredictOutputs *pred, AnofoxError *err,
+                    int min_state_rows = 2) {
+	const bool inf = !pred && opt->compute_inference;
+	if (out) {
+		if (!out->coefficients || !out->intercept || !out->r_squared || !out->adj_r_squared || !out->residual_std_error ||
+		    !out->n_observations || !out->status ||
+		    (inf && (!out->std_errors || !out->t_values || !out->p_values || !out->ci_lower || !out->ci_upper ||
+		             !out->f_statistic || !out->f_pvalue))) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "a required output array is NULL");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+	}
+	HostContext &c = host_ctx();
+	std::lock_guard<std::mutex> lock(c.mu);
+	DeviceInfo &di = device_info();
+	Workspace wsz;
+	const size_t ws_bytes = carve(wsz, nullptr, G, N, p, di.sms);
+	DevLayout L;
+	const int64_t G1 = std::max<int64_t>(G, 1), N1 = std::max<int64_t>(N, 1);
+	const size_t o_off = L.take((size_t)(G + 1) * 8), o_y = L.take((size_t)N1 * 8), o_x = L.take((size_t)N1 * p * 8);
+	const size_t o_w = w ? L.take((size_t)N1 * 8) : 0, o_t = train ? L.take((size_t)N1) : 0;
+	const size_t o_gp = L.take((size_t)G1 * p * 8 * (inf ? 6 : 1));
+	const size_t o_g = L.take((size_t)G1 * 8 * 12);
+	const size_t o_pred = pred ? L.take((size_t)N1 * 8 * 3 + (size_t)N1) : 0;
+	const size_t o_ws = L.take(ws_bytes);
+	int rc = c.ensure(L.off, err);
+	if (rc) return rc;
+	unsigned char *d = c.dev;
+	cudaStream_t st = c.stream;
+	CU(cudaMemcpyAsync(d + o_off, offsets, (size_t)(G + 1) * 8, cudaMemcpyHostToDevice, st), "H2D offsets");
+	if (N > 0) {
+		CU(cudaMemcpyAsync(d + o_y, y, (size_t)N * 8, cudaMemcpyHostToDevice, st), "H2D y");
+		CU(cudaMemcpyAsync(d + o_x, x, (size_t)N * p * 8, cudaMemcpyHostToDevice, st), "H2D x");
+		if (w) CU(cudaMemcpyAsync(d + o_w, w, (size_t)N * 8, cudaMemcpyHostToDevice, st), "H2D w");
+		if (train) CU(cudaMemcpyAsync(d + o_t, train, (size_t)N, cudaMemcpyHostToDevice, st), "H2D train");
+	}
+	AnofoxB200FitOutputs dout;
+	memset(&dout, 0, sizeof dout);
+	double *gp = (double *)(d + o_gp), *gs = (double *)(d + o_g);
+	dout.coefficients = gp;
+	if (inf) {
+		dout.std_errors = gp + (size_t)G1 * p * 1;
+		dout.t_values = gp + (size_t)G1 * p * 2;
+		dout.p_values = gp + (size_t)G1 * p * 3;
+		dout.ci_lower = gp + (size_t)G1 * p * 4;
+		dout.ci_upper = gp + (size_t)G1 * p * 5;
+	}
+	dout.intercept = gs + G1 * 0;
+	dout.r_squared = gs + G1 * 1;
+	dout.adj_r_squared = gs + G1 * 2;
+	dout.residual_std_error = gs + G1 * 3;
+	dout.n_observations = (int64_t *)(gs + G1 * 4);
+	dout.status = (int32_t *)(gs + G1 * 5);
+	dout.f_statistic = gs + G1 * 6;
+	dout.f_pvalue = gs + G1 * 7;
+	dout.has_inference = (uint8_t *)(gs + G1 * 8);
+	dout.aic = gs + G1 * 9;
+	dout.bic = gs + G1 * 10;
+	dout.rss = gs + G1 * 11;
+	AnofoxB200PredictOutputs dpred;
+	memset(&dpred, 0, sizeof dpred);
+	if (pred) {
+		double *pp = (double *)(d + o_pred);
+		dpred.yhat = pp;
+		dpred.yhat_lower = pp + N1;
+		dpred.yhat_upper = pp + 2 * N1;
+		dpred.is_training = (uint8_t *)(pp + 3 * N1);
+	}
+	rc = fit_device((const int64_t *)(d + o_off), G, (const double *)(d + o_y), (const double *)(d + o_x),
+	                w ? (const double *)(d + o_w) : nullptr, train ? (const uint8_t *)(d + o_t) : nullptr, N, p, opt, dout,
+	                pred ? &dpred : nullptr, d + o_ws, ws_bytes, st, err, min_state_rows);
+	if (rc) return rc;
+	auto back = [&](void *dst, const void *src, size_t bytes) {
+		return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+	};
+	if (out && G > 0) {
+		CU(back(out->coefficients, dout.coefficients, (size_t)G * p * 8), "D2H");
+		CU(back(out->intercept, dout.intercept, (size_t)G * 8), "D2H");
+		CU(back(out->r_squared, dout.r_squared, (size_t)G * 8), "D2H");
+		CU(back(out->adj_r_squared, dout.adj_r_squared, (size_t)G * 8), "D2H");
+		CU(back(out->residual_std_error, dout.residual_std_error, (size_t)G * 8), "D2H");
+		CU(back(out->n_observations, dout.n_observations, (size_t)G * 8), "D2H");
+		CU(back(out->status, dout.status, (size_t)G * 4), "D2H");
+		if (inf) {
+			CU(back(out->std_errors, dout.std_errors, (size_t)G * p * 8), "D2H");
+			CU(back(out->t_values, dout.t_values, (size_t)G * p * 8), "D2H");
+			CU(back(out->p_values, dout.p_values, (size_t)G * p * 8), "D2H");
+			CU(back(out->ci_lower, dout.ci_lower, (size_t)G * p * 8), "D2H");
+			CU(back(out->ci_upper, dout.ci_upper, (size_t)G * p * 8), "D2H");
+			CU(back(out->f_statistic, dout.f_statistic, (size_t)G * 8), "D2H");
+			CU(back(out->f_pvalue, dout.f_pvalue, (size_t)G * 8), "D2H");
+			CU(back(out->has_inference, dout.has_inference, (size_t)G), "D2H");
+		}
+		CU(back(out->aic, dout.aic, (size_t)G * 8), "D2H");
+		CU(back(out->bic, dout.bic, (size_t)G * 8), "D2H");
+		CU(back(out->rss, dout.rss, (size_t)G * 8), "D2H");
+	}
+	if (pred && N > 0) {
+		CU(back(pred->yhat, dpred.yhat, (size_t)N * 8), "D2H");
+		CU(back(pred->yhat_lower, dpred.yhat_lower, (size_t)N * 8), "D2H");
+		CU(back(pred->yhat_upper, dpred.yhat_upper, (size_t)N * 8), "D2H");
+		CU(back(pred->is_training, dpred.is_training, (size_t)N), "D2H");
+	}
+	CU(cudaStreamSynchronize(st), "sync");
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// One fit through the reference's own signature (drop-in layer)
+// ---------------------------------------------------------------------------------------------
+static bool single_fit(int method, AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count,
+                       const AnofoxDataArray *weights, bool fit_intercept, bool compute_inference, double level,
+                       double alpha, int lambda_scaling, int solver, int hc_type, AnofoxFitResultCore *out_core,
+                       AnofoxFitResultInference *out_inf, AnofoxError *err) {
+	clear_error(err); // lib.rs:108-110
+	if (!out_core) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "out_core is NULL");
+		return false;
+	}
+	if (!x || x_count == 0) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "x is NULL or empty");
+		return false;
+	}
+	if (method == ANOFOX_B200_RIDGE && alpha < 0.0) { // ridge.rs:38-40 comes first
+		set_error(err, ANOFOX_ERROR_INVALID_ALPHA, "Invalid alpha: must be >= 0");
+		return false;
+	}
+	if (y.len == 0 || !y.data) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "Empty input: y"); // ols.rs:38-40
+		return false;
+	}
+	if (weights && weights->len == 0) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "Empty input: weights");
+		return false;
+	}
+	if (weights && weights->len != y.len) {
+		set_error(err, ANOFOX_ERROR_DIMENSION_MISMATCH, "Dimension mismatch: weights");
+		return false;
+	}
+	for (size_t j = 0; j < x_count; ++j)
+		if (x[j].len != y.len) { // ols.rs:49-56
+			set_error(err, ANOFOX_ERROR_DIMENSION_MISMATCH, "Dimension mismatch: x column length differs from y");
+			return false;
+		}
+	const size_t n = y.len, p = x_count;
+	auto valid = [](const uint8_t *v, size_t i) { return v == nullptr || ((v[i >> 3] >> (i & 7)) & 1); };
+	// column arrays -> one group of row-major rows; NULL -> NaN (types.rs:79-89)
+	std::vector<double> xr(n * p), yv(n), wv;
+	for (size_t i = 0; i < n; ++i) yv[i] = valid(y.validity, i) ? y.data[i] : NAN;
+	for (size_t j = 0; j < p; ++j)
+		for (size_t i = 0; i < n; ++i) xr[i * p + j] = valid(x[j].validity, i) ? x[j].data[i] : NAN;
+	if (weights) {
+		wv.resize(n);
+		for (size_t i = 0; i < n; ++i) wv[i] = valid(weights->validity, i) ? weights->data[i] : NAN;
+	}
+	AnofoxB200FitOptions o;
+	o.method = method;
+	o.fit_intercept = fit_intercept;
+	o.compute_inference = compute_inference;
+	o.solver = solver;
+	o.lambda_scaling = lambda_scaling;
+	o.hc_type = hc_type;
+	o.confidence_level = level;
+	o.alpha = alpha;
+	int64_t offsets[2] = {0, (int64_t)n};
+	// The aggregate's "fewer than 2 rows" rule belongs to the caller (ols_aggregate.cpp:263-267), not
+	// to anofox_*_fit: a one-row fit must reach the core rules, hence min_state_rows = 0 below.
+	std::vector<double> coef(p), se(p), tv(p), pv(p), lo(p), hi(p);
+	double icpt, r2, adj, rse, fs, fp;
+	int64_t nobs;
+	int32_t status;
+	uint8_t has_inf = 0;
+	AnofoxB200FitOutputs out;
+	memset(&out, 0, sizeof out);
+	out.coefficients = coef.data();
+	out.intercept = &icpt;
+	out.r_squared = &r2;
+	out.adj_r_squared = &adj;
+	out.residual_std_error = &rse;
+	out.n_observations = &nobs;
+	out.status = &status;
+	out.std_errors = se.data();
+	out.t_values = tv.data();
+	out.p_values = pv.data();
+	out.ci_lower = lo.data();
+	out.ci_upper = hi.data();
+	out.f_statistic = &fs;
+	out.f_pvalue = &fp;
+	out.has_inference = &has_inf;
+	int rc = validate_common(offsets, 1, yv.data(), xr.data(), weights ? wv.data() : nullptr, (int64_t)n, (int)p, &o, err);
+	if (rc) return false;
+	rc = fit_host(offsets, 1, yv.data(), xr.data(), weights ? wv.data() : nullptr, nullptr, (int64_t)n, (int)p, &o, &out,
+	              nullptr, err, 0);
+	if (rc) return false;
+	if (status != 0) {
+		const char *msg = status == ANOFOX_ERROR_NO_VALID_DATA        ? "No valid data"
+		                  : status == ANOFOX_ERROR_INSUFFICIENT_DATA ? "Insufficient data"
+		                                                             : "fit failed";
+		set_error(err, status, msg);
+		return false;
+	}
+	double *c = (double *)malloc(std::max<size_t>(p, 1) * sizeof(double));
+	if (!c) {
+		set_error(err, ANOFOX_ERROR_ALLOCATION_FAILURE, "Failed to allocate coefficients");
+		return false;
+	}
+	memcpy(c, coef.data(), p * sizeof(double));
+	out_core->coefficients = c;
+	out_core->coefficients_len = p;
+	out_core->intercept = icpt;
+	out_core->r_squared = r2;
+	out_core->adj_r_squared = adj;
+	out_core->residual_std_error = rse;
+	out_core->n_observations = (size_t)nobs;
+	out_core->n_features = p;
+	if (out_inf) {
+		if (compute_inference && has_inf) {
+			double *arrs[5];
+			const std::vector<double> *src[5] = {&se, &tv, &pv, &lo, &hi};
+			bool okm = true;
+			for (int i = 0; i < 5; ++i) {
+				arrs[i] = (double *)malloc(std::max<size_t>(p, 1) * sizeof(double));
+				okm = okm && arrs[i];
+			}
+			if (!okm) {
+				for (int i = 0; i < 5; ++i) free(arrs[i]);
+				free(c);
+				out_core->coefficients = nullptr;
+				set_error(err, ANOFOX_ERROR_ALLOCATION_FAILURE, "Failed to allocate inference arrays");
+				return false;
+			}
+			for (int i = 0; i < 5; ++i) memcpy(arrs[i], src[i]->data(), p * sizeof(double));
+			out_inf->std_errors = arrs[0];
+			out_inf->t_values = arrs[1];
+			out_inf->p_values = arrs[2];
+			out_inf->ci_lower = arrs[3];
+			out_inf->ci_upper = arrs[4];
+			out_inf->len = p;
+			out_inf->confidence_level = level;
+			out_inf->f_statistic = fs;
+			out_inf->f_pvalue = fp;
+		} else { // lib.rs:251-253
+			out_inf->std_errors = out_inf->t_values = out_inf->p_values = out_inf->ci_lower = out_inf->ci_upper = nullptr;
+			out_inf->len = 0;
+			out_inf->confidence_level = 0.95;
+			out_inf->f_statistic = NAN;
+			out_inf->f_pvalue = NAN;
+		}
+	}
+	return true;
+}
+
+static int eval_specfun_host(int mode, int n, const double *a, const double *b, const double *c, double *out,
+                             AnofoxError *err) {
+	clear_error(err);
+	DeviceInfo &di = device_info();
+	if (!di.ok) {
+		set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+		return ANOFOX_ERROR_INTERNAL;
+	}
+	if (n <= 0) return 0;
+	HostContext &ctx = host_ctx();
+	std::lock_guard<std::mutex> lock(ctx.mu);
+	const size_t bytes = (size_t)n * 8;
+	int rc = ctx.ensure(4 * ((bytes + 255) & ~(size_t)255), err);
+	if (rc) return rc;
+	const size_t step = (bytes + 255) & ~(size_t)255;
+	double *da = (double *)ctx.dev, *db = (double *)(ctx.dev + step), *dc = (double *)(ctx.dev + 2 * step),
+	       *dout = (double *)(ctx.dev + 3 * step);
+	cudaStream_t st = ctx.stream;
+	CU(cudaMemcpyAsync(da, a, bytes, cudaMemcpyHostToDevice, st), "H2D");
+	CU(cudaMemcpyAsync(db, b, bytes, cudaMemcpyHostToDevice, st), "H2D");
+	if (c) CU(cudaMemcpyAsync(dc, c, bytes, cudaMemcpyHostToDevice, st), "H2D");
+	specfun_eval_kernel<<<(n + 127) / 128, 128, 0, st>>>(mode, n, da, db, dc, dout);
+	LAUNCHED();
+	CU(cudaGetLastError(), "specfun_eval_kernel");
+	CU(cudaMemcpyAsync(out, dout, bytes, cudaMemcpyDeviceToHost, st), "D2H");
+	CU(cudaStreamSynchronize(st), "sync");
+	return 0;
+}
+
+} // namespace b200
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+using namespace b200;
+
+extern "C" {
+
+bool anofox_ols_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxOlsOptions options,
+                    AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference, AnofoxError *out_error) {
+	return single_fit(ANOFOX_B200_OLS, y, x, x_count, nullptr, options.fit_intercept, options.compute_inference,
+	                  options.confidence_level, 0.0, 0, (int)options.solver, (int)options.hc_type, out_core,
+	                  out_inference, out_error);
+}
+
+bool anofox_ridge_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxRidgeOptions options,
+                      AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference, AnofoxError *out_error) {
+	return single_fit(ANOFOX_B200_RIDGE, y, x, x_count, nullptr, options.fit_intercept, options.compute_inference,
+	                  options.confidence_level, options.alpha, (int)options.lambda_scaling, (int)options.solver,
+	                  ANOFOX_HC_NONE, out_core, out_inference, out_error);
+}
+
+bool anofox_wls_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxDataArray weights,
+                    AnofoxWlsOptions options, AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference,
+                    AnofoxError *out_error) {
+	return single_fit(ANOFOX_B200_WLS, y, x, x_count, &weights, options.fit_intercept, options.compute_inference,
+	                  options.confidence_level, 0.0, 0, (int)options.solver, (int)options.hc_type, out_core,
+	                  out_inference, out_error);
+}
+
+void anofox_free_result_core(AnofoxFitResultCore *result) {
+	if (!result) return;
+	free(result->coefficients);
+	result->coefficients = nullptr;
+}
+
+void anofox_free_result_inference(AnofoxFitResultInference *result) {
+	if (!result) return;
+	free(result->std_errors);
+	free(result->t_values);
+	free(result->p_values);
+	free(result->ci_lower);
+	free(result->ci_upper);
+	result->std_errors = result->t_values = result->p_values = result->ci_lower = result->ci_upper = nullptr;
+}
+
+double anofox_t_critical(double confidence_level, size_t df) {
+	if (df == 0 || !(confidence_level > 0.0) || !(confidence_level < 1.0)) return NAN; // lib.rs:2218-2220
+	double a = confidence_level, b = (double)df, out = NAN;
+	AnofoxError err;
+	if (eval_specfun_host(1, 1, &a, &b, nullptr, &out, &err) != 0) return NAN;
+	return out;
+}
+
+bool anofox_predict_with_interval(const double *coefficients, size_t coefficients_len, double intercept,
+                                  const double *x_new, size_t x_len, double residual_std_error,
+                                  size_t n_observations, double confidence_level, AnofoxPredictionResult *out) {
+	if (!out) return false;
+	out->yhat = out->yhat_lower = out->yhat_upper = NAN;
+	if (!coefficients || coefficients_len == 0) return false;
+	if (!x_new || x_len != coefficients_len) return false;
+	// lib.rs:2292-2347. The dot product of one row is scalar host work; the t quantile is the
+	// device routine (anofox_t_critical above), as in the batched predict kernel.
+	double yhat = std::isnan(intercept) ? 0.0 : intercept;
+	for (size_t j = 0; j < coefficients_len; ++j)
+		if (!std::isnan(coefficients[j])) yhat += coefficients[j] * x_new[j];
+	out->yhat = out->yhat_lower = out->yhat_upper = yhat;
+	if (std::isnan(residual_std_error) || residual_std_error <= 0.0 || n_observations <= coefficients_len + 1) return true;
+	const size_t k = coefficients_len + (std::isnan(intercept) ? 0 : 1);
+	const size_t df = n_observations > k ? n_observations - k : 0;
+	if (df == 0) return true;
+	const double tc = anofox_t_critical(confidence_level, df);
+	if (std::isnan(tc)) return true;
+	const double margin = tc * (residual_std_error * std::sqrt(1.0 + 1.0 / (double)n_observations));
+	out->yhat_lower = yhat - margin;
+	out->yhat_upper = yhat + margin;
+	return true;
+}
+
+static bool info_crit(double rss, size_t n, size_t k, double *out, bool bic, AnofoxError *err) {
+	clear_error(err);
+	if (!out) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, bic ? "out_bic is NULL" : "out_aic is NULL");
+		return false;
+	}
+	if (n == 0) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "n must be > 0");
+		return false;
+	}
+	if (rss < 0.0) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "RSS must be non-negative");
+		return false;
+	}
+	if (rss == 0.0) {
+		*out = -INFINITY;
+		return true;
+	}
+	const double nf = (double)n, kf = (double)k;
+	*out = nf * std::log(rss / nf) + (bic ? kf * std::log(nf) : 2.0 * kf);
+	return true;
+}
+bool anofox_compute_aic(double rss, size_t n, size_t k, double *out_aic, AnofoxError *err) {
+	return info_crit(rss, n, k, out_aic, false, err);
+}
+bool anofox_compute_bic(double rss, size_t n, size_t k, double *out_bic, AnofoxError *err) {
+	return info_crit(rss, n, k, out_bic, true, err);
+}
+
+size_t anofox_b200_workspace_bytes(int64_t n_groups, int64_t n_rows, int32_t n_features) {
+	if (n_groups < 0 || n_rows < 0 || n_features <= 0 || n_features > kMaxFeatures) return 0;
+	DeviceInfo &di = device_info();
+	Workspace w;
+	return carve(w, nullptr, n_groups, n_rows, n_features, di.sms > 0 ? di.sms : 148);
+}
+
+int32_t anofox_b200_fit_batch_device(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
+                                     const double *w, int64_t n_rows, int32_t n_features,
+                                     const AnofoxB200FitOptions *options, const AnofoxB200FitOutputs *out,
+                                     void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err) {
+	int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+	if (rc) return rc;
+	if (!out || !out->coefficients || !out->status) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "outputs is NULL");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (options->compute_inference && !out->std_errors) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "compute_inference needs the inference arrays");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	return fit_device(offsets, n_groups, y, x, w, nullptr, n_rows, n_features, options, *out, nullptr, workspace,
+	                  workspace_bytes, (cudaStream_t)stream, err);
+}
+
+int32_t anofox_b200_fit_batch_host(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
+                                   const double *w, int64_t n_rows, int32_t n_features,
+                                   const AnofoxB200FitOptions *options, const AnofoxB200FitOutputs *out,
+                                   AnofoxError *err) {
+	int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+	if (rc) return rc;
+	if (!out) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "outputs is NULL");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	return fit_host(offsets, n_groups, y, x, w, nullptr, n_rows, n_features, options, out, nullptr, err);
+}
+
+int32_t anofox_b200_fit_predict_batch_device(const int64_t *offsets, int64_t n_groups, const double *y,
+                                             const double *x, const double *w, const uint8_t *train,
+                                             int64_t n_rows, int32_t n_features,
+                                             const AnofoxB200FitOptions *options,
+                                             const AnofoxB200PredictOutputs *pred, const AnofoxB200FitOutputs *fit,
+                                             void *workspace, size_t workspace_bytes, void *stream,
+                                             AnofoxError *err) {
+	int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+	if (rc) return rc;
+	if (!pred || !pred->yhat || !pred->yhat_lower || !pred->yhat_upper) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "prediction outputs are NULL");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	AnofoxB200FitOutputs none;
+	memset(&none, 0, sizeof none);
+	return fit_device(offsets, n_groups, y, x, w, train, n_rows, n_features, options, fit ? *fit : none, pred,
+	                  workspace, workspace_bytes, (cudaStream_t)stream, err);
+}
+
+int32_t anofox_b200_fit_predict_batch_host(const int64_t *offsets, int64_t n_groups, const double *y,
+                                           const double *x, const double *w, const uint8_t *train, int64_t n_rows,
+                                           int32_t n_features, const AnofoxB200FitOptions *options,
+                                           const AnofoxB200PredictOutputs *pred, const AnofoxB200FitOutputs *fit,
+                                           AnofoxError *err) {
+	int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+	if (rc) return rc;
+	if (!pred || !pred->yhat || !pred->yhat_lower || !pred->yhat_upper || !pred->is_training) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "prediction outputs are NULL");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	return fit_host(offsets, n_groups, y, x, w, train, n_rows, n_features, options, fit, pred, err);
+}
+
+size_t anofox_b200_moment_block_len(int32_t n_features) {
+	if (n_features <= 0 || n_features > kMaxFeatures) return 0;
+	const int k = n_features + 1;
+	return (size_t)(4 + k + k * (k + 1) / 2);
+}
+
+int32_t anofox_b200_moments_device(const double *y, const double *x, const double *w, int64_t n_rows,
+                                   int32_t n_features, const double *shift, double *moments, double *cdev,
+                                   void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err) {
+	clear_error(err);
+	DeviceInfo &di = device_info();
+	if (!di.ok) {
+		set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+		return ANOFOX_ERROR_INTERNAL;
+	}
+	const int p = n_features;
+	if (p <= 0 || p > kMaxFeatures || n_rows < 0 || !shift || !moments || !cdev || (n_rows > 0 && (!x || !y))) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "invalid argument");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	Workspace ws;
+	const size_t need = carve(ws, (unsigned char *)workspace, 1, n_rows, p, di.sms);
+	if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 255)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "workspace too small or misaligned");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	cudaStream_t st = (cudaStream_t)stream;
+	StreamArgs s;
+	s.offsets = nullptr;
+	s.big_list = nullptr;
+	s.big_count = nullptr;
+	s.fixed_rows = n_rows;
+	s.y = y;
+	s.x = x;
+	s.w = w;
+	s.train = nullptr;
+	s.p = p;
+	s.shift = const_cast<double *>(shift);
+	s.first_ok = nullptr;
+	s.partials = ws.partials;
+	s.n_part = ws.n_part;
+	s.records = ws.records;
+	CU(launch_stream(s, ws.n_part / kStreamWarps, st), "acc_stream_kernel");
+	dim3 rg((unsigned)((rec_len(p) + 127) / 128), 1);
+	reduce_partials_kernel<<<rg, 128, 0, st>>>(s);
+	LAUNCHED();
+	CU(cudaGetLastError(), "reduce_partials_kernel");
+	split_record_kernel<<<1, 256, 0, st>>>(ws.records, p, moments, cdev);
+	LAUNCHED();
+	CU(cudaGetLastError(), "split_record_kernel");
+	return 0;
+}
+
+int32_t anofox_b200_solve_moments_device(const double *moments, const double *cdev, const double *shift,
+                                         int32_t n_features, const AnofoxB200FitOptions *options,
+                                         const AnofoxB200FitOutputs *out, void *stream, AnofoxError *err) {
+	clear_error(err);
+	DeviceInfo &di = device_info();
+	if (!di.ok) {
+		set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+		return ANOFOX_ERROR_INTERNAL;
+	}
+	const int p = n_features;
+	if (p <= 0 || p > kMaxFeatures || !moments || !cdev || !shift || !options || !out || !out->coefficients) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "invalid argument");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (options->method == ANOFOX_B200_RIDGE && options->alpha < 0.0) {
+		set_error(err, ANOFOX_ERROR_INVALID_ALPHA, "Invalid alpha: must be >= 0");
+		return ANOFOX_ERROR_INVALID_ALPHA;
+	}
+	cudaStream_t st = (cudaStream_t)stream;
+	double *rec = nullptr;
+	CU(cudaMallocAsync(&rec, (size_t)rec_len(p) * 8, st), "cudaMallocAsync");
+	assemble_record_kernel<<<1, 256, 0, st>>>(moments, cdev, shift, p, rec);
+	LAUNCHED();
+	FitParams P;
+	P.p = p;
+	P.method = options->method;
+	P.fit_intercept = options->fit_intercept != 0;
+	P.compute_inference = options->compute_inference != 0;
+	P.lambda_scaling = options->lambda_scaling;
+	P.level = options->confidence_level;
+	P.alpha = options->alpha;
+	P.tcrit = nullptr; // one group: evaluate the quantile directly
+	P.predict_mode = 0;
+	P.min_state_rows = 2;
+	CU(launch_solve(rec, 1, P, *out, nullptr, nullptr, st), "solve_kernel");
+	CU(cudaFreeAsync(rec, st), "cudaFreeAsync");
+	return 0;
+}
+
+int32_t anofox_b200_device_check(AnofoxError *err) {
+	clear_error(err);
+	DeviceInfo &di = device_info();
+	if (!di.ok) {
+		set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+		return ANOFOX_ERROR_INTERNAL;
+	}
+	return 0;
+}
+
+int64_t anofox_b200_launch_count(void) { return (int64_t)g_launches.load(); }
+
+const char *anofox_b200_version(void) { return "anofox-statistics_b200 0.1 (sm_100a)"; }
+
+// Bench hooks: per-stage device times of the batched calls made while enabled.
+void anofox_b200_stage_timing_enable(int32_t on) {
+	StageTimer &t = stage_timer();
+	std::lock_guard<std::mutex> lock(t.mu);
+	t.clear();
+	t.enabled = on != 0;
+}
+// Sums over all recorded calls (synchronises the device). Returns the number of calls.
+int64_t anofox_b200_stage_timing_read(double *accumulate_ms, double *solve_ms) {
+	StageTimer &t = stage_timer();
+	std::lock_guard<std::mutex> lock(t.mu);
+	cudaDeviceSynchronize();
+	double a = 0.0, b = 0.0;
+	int64_t n = 0;
+	for (size_t i = 0; i + 3 <= t.ev.size(); i += 3) {
+		float m1 = 0.f, m2 = 0.f;
+		if (cudaEventElapsedTime(&m1, t.ev[i], t.ev[i + 1]) == cudaSuccess &&
+		    cudaEventElapsedTime(&m2, t.ev[i + 1], t.ev[i + 2]) == cudaSuccess) {
+			a += m1;
+			b += m2;
+			++n;
+		}
+	}
+	if (accumulate_ms) *accumulate_ms = a;
+	if (solve_ms) *solve_ms = b;
+	t.clear();
+	return n;
+}
+
+// Test hook: evaluate the device special functions on arrays (host pointers).
+int32_t anofox_b200_eval_specfun(int32_t mode, int32_t n, const double *a, const double *b, const double *c,
+                                 double *out, AnofoxError *err) {
+	return eval_specfun_host(mode, n, a, b, c, out, err);
+}
+
+} // extern "C"

@@ -1,0 +1,126 @@
+// specfun.cuh -- Student-t and F distribution functions on the device (f64).
+//
+// Replaces what the reference obtains from statrs 0.18 (crates/anofox-stats-ffi/src/lib.rs:26,
+// :2223-2230 StudentsT::inverse_cdf) and from anofox-regression's p-value code. Written from
+// the standard formulas: regularised incomplete beta by a Lentz continued fraction, log-beta
+// with the Stirling-correction form (as in R's lbeta) so that large degrees of freedom do not
+// cancel, and a safeguarded Newton iteration for the quantile.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+// Stirling correction  lgamma(x) - [(x - 1/2) ln x - x + ln sqrt(2 pi)],  x >= 10.
+__device__ inline double lgamma_corr(double x) {
+	double r = 1.0 / x, r2 = r * r;
+	return r * (8.3333333333333333e-2 +
+	            r2 * (-2.7777777777777778e-3 +
+	                  r2 * (7.9365079365079365e-4 +
+	                        r2 * (-5.9523809523809524e-4 + r2 * (8.4175084175084175e-4 + r2 * (-1.9175269175269175e-3))))));
+}
+
+__device__ inline double lbeta_dev(double a, double b) {
+	double p = fmin(a, b), q = fmax(a, b);
+	const double ln_sqrt_2pi = 0.91893853320467274178;
+	if (p >= 10.0) {
+		double corr = lgamma_corr(p) + lgamma_corr(q) - lgamma_corr(p + q);
+		return -0.5 * log(q) + ln_sqrt_2pi + corr + (p - 0.5) * log(p / (p + q)) + q * log1p(-p / (p + q));
+	}
+	if (q >= 10.0) {
+		double corr = lgamma_corr(q) - lgamma_corr(p + q);
+		return lgamma(p) + corr + p - p * log(p + q) + (q - 0.5) * log1p(-p / (p + q));
+	}
+	return lgamma(p) + lgamma(q) - lgamma(p + q);
+}
+
+// Continued fraction for I_x(a,b) (modified Lentz); converges in O(sqrt(max(a,b))) steps for
+// x < (a+1)/(a+b+2).
+__device__ inline double beta_cf(double a, double b, double x) {
+	const double tiny = 1e-300;
+	double qab = a + b, qap = a + 1.0, qam = a - 1.0;
+	double c = 1.0, d = 1.0 - qab * x / qap;
+	if (fabs(d) < tiny) d = tiny;
+	d = 1.0 / d;
+	double h = d;
+	for (int m = 1; m <= 5000; ++m) {
+		double m2 = 2.0 * m;
+		double aa = m * (b - m) * x / ((qam + m2) * (a + m2));
+		d = 1.0 + aa * d;
+		if (fabs(d) < tiny) d = tiny;
+		c = 1.0 + aa / c;
+		if (fabs(c) < tiny) c = tiny;
+		d = 1.0 / d;
+		h *= d * c;
+		aa = -(a + m) * (qab + m) * x / ((a + m2) * (qap + m2));
+		d = 1.0 + aa * d;
+		if (fabs(d) < tiny) d = tiny;
+		c = 1.0 + aa / c;
+		if (fabs(c) < tiny) c = tiny;
+		d = 1.0 / d;
+		double del = d * c;
+		h *= del;
+		if (fabs(del - 1.0) < 3e-16) break;
+	}
+	return h;
+}
+
+// I_x(a,b) with xc = 1 - x given by the caller (no cancellation near x = 1).
+__device__ inline double beta_inc(double a, double b, double x, double xc) {
+	if (!(x > 0.0)) return 0.0;
+	if (!(xc > 0.0)) return 1.0;
+	double lnpre = a * log(x) + b * log(xc) - lbeta_dev(a, b);
+	if (x < (a + 1.0) / (a + b + 2.0)) return exp(lnpre) * beta_cf(a, b, x) / a;
+	return 1.0 - exp(lnpre) * beta_cf(b, a, xc) / b;
+}
+
+// 2 * (1 - T_df(|t|)) = I_{df/(df+t^2)}(df/2, 1/2)
+__device__ inline double t_two_sided_p(double t, double df) {
+	if (isnan(t) || !(df > 0.0)) return nan_f64();
+	if (isinf(t)) return 0.0;
+	double t2 = t * t;
+	return beta_inc(0.5 * df, 0.5, df / (df + t2), t2 / (df + t2));
+}
+
+// Upper tail of F(d1,d2)
+__device__ inline double f_upper_p(double f, double d1, double d2) {
+	if (isnan(f) || !(d1 > 0.0) || !(d2 > 0.0)) return nan_f64();
+	if (f <= 0.0) return 1.0;
+	if (isinf(f)) return 0.0;
+	double den = d2 + d1 * f;
+	return beta_inc(0.5 * d2, 0.5 * d1, d2 / den, d1 * f / den);
+}
+
+// t such that P(|T_df| <= t) = level  (anofox_t_critical, lib.rs:2217-2231).
+__device__ inline double t_critical_dev(double level, double df) {
+	if (!(df > 0.0) || !(level > 0.0) || !(level < 1.0)) return nan_f64();
+	const double alpha = 1.0 - level; // two-sided tail mass
+	if (df == 1.0) return tan(1.5707963267948966 * level);
+	if (df == 2.0) return level * sqrt(2.0 / ((1.0 - level) * (1.0 + level)));
+	// Cornish-Fisher start from the normal quantile
+	double z = normcdfinv(1.0 - 0.5 * alpha);
+	double z2 = z * z;
+	double t = z + z * (z2 + 1.0) / (4.0 * df) + z * (5.0 * z2 * z2 + 16.0 * z2 + 3.0) / (96.0 * df * df) +
+	           z * (3.0 * z2 * z2 * z2 + 19.0 * z2 * z2 + 17.0 * z2 - 15.0) / (384.0 * df * df * df);
+	if (!(t > 0.0) || isinf(t)) t = z > 0.0 ? z : 1.0;
+	const double lnc = -lbeta_dev(0.5, 0.5 * df) - 0.5 * log(df); // log of the pdf normaliser
+	double lo = 0.0, hi = -1.0;                                   // bracket: f(lo) > 0 > f(hi)
+	for (int it = 0; it < 100; ++it) {
+		double f = t_two_sided_p(t, df) - alpha;
+		if (f > 0.0)
+			lo = t;
+		else
+			hi = t;
+		double pdf = exp(lnc - 0.5 * (df + 1.0) * log1p(t * t / df));
+		double step = f / (2.0 * pdf); // Newton: t_new = t + f / (2 pdf)  (f' = -2 pdf)
+		double tn = t + step;
+		if (!(tn > lo) || (hi > 0.0 && !(tn < hi)) || isnan(tn)) tn = hi > 0.0 ? 0.5 * (lo + hi) : 2.0 * t + 1.0;
+		if (fabs(tn - t) <= 4e-16 * tn) {
+			t = tn;
+			break;
+		}
+		t = tn;
+	}
+	return t;
+}
+
+} // namespace b200

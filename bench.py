@@ -1,0 +1,319 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the B200 group-fit path (contract: task prompt, section 4).
+
+Workload (BASELINE.json configs[1], "C2"): ols_fit_agg over 1 M groups x 50 rows x 5 features, f64,
+full inference, synthetic. One "step" = one pass of the hot path (accumulate + solve/inference)
+over the whole batch. `value` = fits/s with inputs resident in HBM; `e2e` = the same through the
+host-pointer C-ABI call (pinned host buffers, H2D + D2H inside the timed region).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C1|C2|C3r|C3w|C5]
+  torchrun --nproc-per-node N bench.py --gpus N ...      (weak scaling: every rank fits its own C2)
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (G, n, p, method, inference, options)
+    "C1": (10_000, 100, 3, "ols", False, {}),
+    "C2": (1_000_000, 50, 5, "ols", True, {}),
+    "C3r": (1_000_000, 200, 16, "ridge", False, {"alpha": 1.0, "rank_deficient": True}),
+    "C3w": (1_000_000, 200, 16, "wls", False, {"weights": True, "rank_deficient": True}),
+    "C5": (100_000, 1_000, 8, "ols", False, {"holdout": 0.2, "predict": True}),
+}
+
+
+def algorithmic_bytes(G, N, p, method, inference, predict=False):
+    """compulsory traffic, each input element once, results once."""
+    per_row = 8 * (p + 1) + (8 if method == "wls" else 0)
+    inp = N * per_row + 8 * (G + 1)
+    out = G * (8 * p + 48 + ((40 * p + 16) if inference else 0))
+    if predict:
+        out += N * 25
+    return inp, out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [s.strip() for s in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = float(f[2])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_reference_run(wl, host, steps, warmup, threads, budget_s=12.0):
+    """Time the CPU oracle (port of the reference path; the Rust crates are unavailable) on a bounded sample."""
+    import numpy as np
+    import oracle  # test infrastructure, allowed here as the timed CPU baseline only
+    G, n, p, method, inference, extra = wl
+    opt = dict(method=method, compute_inference=inference, alpha=extra.get("alpha", 0.0))
+    threads = threads or oracle.max_threads()
+    # pilot to size the sample
+    gs = min(G, 2000)
+    t0 = time.perf_counter()
+    oracle.fit_batch(host["offsets"][:gs + 1], host["y"][:gs * n], host["x"][:gs * n], host["w"][:gs * n] if host["w"] is not None else None,
+                     precision=1, threads=threads, **opt)
+    rate = gs / max(time.perf_counter() - t0, 1e-6)
+    per_step = budget_s / max(steps + warmup, 1)
+    gs = int(max(1000, min(G, rate * per_step)))
+    sub = (host["offsets"][:gs + 1], host["y"][:gs * n], host["x"][:gs * n],
+           host["w"][:gs * n] if host["w"] is not None else None)
+    for _ in range(warmup):
+        oracle.fit_batch(*sub, precision=1, threads=threads, **opt)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oracle.fit_batch(*sub, precision=1, threads=threads, **opt)
+    dt = (time.perf_counter() - t0) / steps
+    return gs / dt, dt, gs, threads
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the groups (smoke runs only)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    G, n, p, method, inference, extra = WORKLOADS[args.workload]
+    G = max(64, int(G * args.scale))
+    wl = (G, n, p, method, inference, extra)
+    N = G * n
+    name = {"C1": "ols_fit_agg 10k groups x 100 rows x 3 features",
+            "C2": "ols_fit_agg 1M groups x 50 rows x 5 features, full inference",
+            "C3r": "ridge_fit_agg(lambda=1) 1M groups x 200 rows x 16 features incl. rank-deficient groups",
+            "C3w": "wls_fit_agg 1M groups x 200 rows x 16 features incl. rank-deficient groups",
+            "C5": "ols_fit_predict_by 100k groups x 1k rows x 8 features, 20% held-out"}[args.workload]
+    config = {"workload": name, "groups_per_gpu": G, "rows_per_group": n, "features": p, "method": method,
+              "inference": inference, "sharding": "group-range per rank, no collective",
+              "l2_policy": "inputs (%.2f GB/step) exceed the 126 MB L2" % (N * 8 * (p + 1) / 1e9)}
+
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        from __graft_entry__ import load_package
+        synth = __import__("importlib").import_module("anofox_statistics_b200.synth") if False else None
+        pkg = load_package()
+        from importlib import import_module
+        synth = import_module("anofox_statistics_b200.synth")
+        gs = min(G, 200_000)
+        d = synth.make_numpy(gs, n, p, seed=2, weights=extra.get("weights", False),
+                             rank_deficient=extra.get("rank_deficient", False))
+        wl_s = (gs, n, p, method, inference, extra)
+        v, dt, used, threads = cpu_reference_run(wl_s, d, max(args.steps, 1), args.warmup, 0,
+                                                 budget_s=60.0)
+        line = {"impl": "reference", "metric": "fits_per_sec", "value": v, "unit": "fits/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "rows_per_sec": v * n,
+                "cpu_baseline": {"value": v, "unit": "fits/s", "cores": threads, "kind": "port",
+                                 "sample": f"{used} groups x {n} rows per step (oracle f64, OpenMP over groups; "
+                                           "the reference's Rust crates cannot be built here)"},
+                "e2e": {"value": v, "unit": "fits/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    # ------------------------------------------------------------------ our arm (GPU)
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from importlib import import_module
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    pkg.device_check()
+    synth = import_module("anofox_statistics_b200.synth")
+    predict = bool(extra.get("predict"))
+    d = synth.make_torch(G, n, p, seed=2 + rank, weights=extra.get("weights", False),
+                         rank_deficient=extra.get("rank_deficient", False), holdout=extra.get("holdout", 0.0))
+    fit = pkg.DeviceFit(G, N, p, inference=inference, predict=predict)
+    opt = dict(method=method, compute_inference=inference, alpha=extra.get("alpha", 0.0))
+
+    def step():
+        if predict:
+            fit.fit_predict(d["offsets"], d["y"], d["x"], d["w"], None, **opt)
+        else:
+            fit.fit(d["offsets"], d["y"], d["x"], d["w"], **opt)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    pkg.stage_timing(True)
+    l0 = pkg.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = pkg.launch_count() - l0
+    calls, acc_ms, solve_ms = pkg.stage_timing_read()
+    pkg.stage_timing(False)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    ms_per_step = ms_max / args.steps
+    value = world * G / (ms_per_step * 1e-3)
+
+    # sanity of what was timed: every group fitted
+    st = fit.out["status"]
+    n_ok = int((st == 0).sum().item())
+
+    # ------------------------------------------------------------------ e2e through the host-pointer C ABI
+    e2e = None
+    if not args.no_e2e and not predict:
+        import ctypes as C
+        abi = pkg.abi
+        pin = lambda tt: tt.cpu().pin_memory()  # noqa: E731
+        h = {k: (pin(d[k]) if d[k] is not None else None) for k in ("offsets", "y", "x", "w")}
+        ho = {}
+        for k, v in fit.out.items():
+            ho[k] = torch.empty(v.shape, dtype=v.dtype).pin_memory()
+        hs = abi.B200FitOutputs()
+        for nm, ctype in abi.B200FitOutputs._fields_:
+            setattr(hs, nm, None if nm not in ho else C.cast(ho[nm].data_ptr(), ctype))
+        ptr = lambda tt: None if tt is None else tt.data_ptr()  # noqa: E731
+        e2e_steps = max(1, min(args.steps, 5))
+
+        def e2e_step():
+            pkg.fit_batch_host_into(ptr(h["offsets"]), ptr(h["y"]), ptr(h["x"]), ptr(h["w"]), hs, G, N, p, **opt)
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        barrier()
+        dt = (time.perf_counter() - t0) / e2e_steps
+        tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        h2d = sum(v.numel() * v.element_size() for v in h.values() if v is not None)
+        d2h = sum(v.numel() * v.element_size() for v in ho.values())
+        same = bool(torch.equal(ho["status"], fit.out["status"].cpu()))
+        e2e = {"value": world * G / dt, "unit": "fits/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": dt * 1e3, "steps": e2e_steps, "matches_device_path": same}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak_gbs()
+    inp, outb = algorithmic_bytes(G, N, p, method, inference, predict)
+    acc_launch_ms = acc_ms / max(calls, 1)
+    acc_bytes = N * (8 * (p + 1) + (8 if method == "wls" else 0)) + 8 * (G + 1)
+    achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
+    roofline = {"bound": "hbm", "kernel": "acc_resident_kernel (segmented moment accumulation)",
+                "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "algorithmic_bytes_per_launch": acc_bytes, "avg_launch_ms": acc_launch_ms,
+                "solve_stage_ms": solve_ms / max(calls, 1), "solve_share_of_step": (solve_ms / max(calls, 1)) / ms_per_step,
+                "step_algorithmic_gbs": (inp + outb) / (ms_per_step * 1e-3) / 1e9}
+
+    cpu = None
+    if not args.no_cpu:
+        gs = min(G, 200_000)
+        host = {"offsets": d["offsets"][:gs + 1].cpu().numpy(), "y": d["y"][:gs * n].cpu().numpy(),
+                "x": d["x"][:gs * n].cpu().numpy(), "w": d["w"][:gs * n].cpu().numpy() if d["w"] is not None else None}
+        v, dt, used, threads = cpu_reference_run((gs, n, p, method, inference, extra), host, 3, 1, 0, budget_s=12.0)
+        cpu = {"value": v, "unit": "fits/s", "cores": threads, "kind": "port",
+               "sample": f"{used} groups x {n} rows per step, 3 steps (oracle f64 build, OpenMP over groups)"}
+
+    line = {"metric": "fits_per_sec", "value": value, "unit": "fits/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+            "rows_per_sec": value * n, "groups_fitted_ok": n_ok, "clocks": clocks, "e2e": e2e,
+            "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

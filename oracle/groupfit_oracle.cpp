@@ -255,7 +255,24 @@ void qr_limited(std::vector<R> &a, std::vector<R> &b, size_t rows, size_t m, R t
 	rank = std::min(lup, lmax);
 }
 
-template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &out) {
+// per-thread memo of t quantiles: the level is fixed within a batch, df repeats across groups
+template <class R> struct TcritMemo {
+	double level = -1;
+	std::vector<std::pair<double, R>> items;
+	R get(double lvl, double df) {
+		if (lvl != level) {
+			items.clear();
+			level = lvl;
+		}
+		for (auto &it : items)
+			if (it.first == df) return it.second;
+		R v = t_quantile_upper<R>(((R)1 + (R)lvl) / 2, (R)df);
+		if (items.size() < 4096) items.emplace_back(df, v);
+		return v;
+	}
+};
+
+template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &out, TcritMemo<R> *memo = nullptr) {
 	const size_t n = d.n, p = d.p;
 	out = GroupResult();
 	// ridge.rs:38-40: alpha is validated before anything else
@@ -486,7 +503,8 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 		out.lo.assign(p, kNaN);
 		out.hi.assign(p, kNaN);
 		R tcrit = std::numeric_limits<R>::quiet_NaN();
-		if (dfr > 0 && o.level > 0.0 && o.level < 1.0) tcrit = t_quantile_upper<R>(((R)1 + (R)o.level) / 2, (R)dfr);
+		if (dfr > 0 && o.level > 0.0 && o.level < 1.0)
+			tcrit = memo ? memo->get(o.level, dfr) : t_quantile_upper<R>(((R)1 + (R)o.level) / 2, (R)dfr);
 		for (size_t c = 0; c < pe; ++c) {
 			if (aliased[c]) continue;
 			R se = std::sqrt(sigma2 * vdiag[c]);
@@ -640,7 +658,12 @@ void fit_batch(const int64_t *offsets, int64_t G, const double *y, const double 
 	if (pred) o.compute_inference = false; // ols_predict_aggregate.cpp:354-364
 #ifdef _OPENMP
 	if (threads > 0) omp_set_num_threads(threads);
-#pragma omp parallel for schedule(dynamic, 64)
+#pragma omp parallel
+#endif
+	{
+	TcritMemo<R> memo;
+#ifdef _OPENMP
+#pragma omp for schedule(dynamic, 64)
 #endif
 	for (int64_t g = 0; g < G; ++g) {
 		int64_t r0 = offsets[g], r1 = offsets[g + 1];
@@ -685,7 +708,7 @@ void fit_batch(const int64_t *offsets, int64_t G, const double *y, const double 
 			r.coef.assign((size_t)p, kNaN);
 			// alpha < 0 still wins: the whole call is rejected upstream; keep per-group rule simple
 		} else {
-			fit_group<R>(o, d, r);
+			fit_group<R>(o, d, r, &memo);
 		}
 		if (out) {
 			out->status[g] = r.code;
@@ -732,6 +755,7 @@ void fit_batch(const int64_t *offsets, int64_t G, const double *y, const double 
 				pred->yhat_upper[row] = pr.yhat_upper;
 			}
 		}
+	}
 	}
 }
 

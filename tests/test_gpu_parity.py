@@ -1,0 +1,451 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on identical inputs.
+
+Bit-exact: per-group status (NULL-struct pattern), n_observations, NaN/NULL positions.
+Values: relative 1e-9 (north star: "1e-9 for well-conditioned f64"); p-values relative 1e-8.
+Run on a B200 with:  python -m pytest tests -m gpu
+"""
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+from parity import assert_fit_parity, max_rel_err
+from test_oracle_golden import KAT, R_FIX, check_against_r, check_kat, fit_kwargs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib(b200):
+    b200.device_check()  # fails loudly without an sm_100 device: there is no fallback
+    return b200
+
+
+# ------------------------------------------------------------------ drop-in symbols vs goldens
+@pytest.mark.parametrize("c", R_FIX, ids=[c["name"] for c in R_FIX])
+def test_single_fit_matches_r_golden(lib, c):
+    r = lib.single_fit(c["method"], c["y"], c["x"], c["w"], **fit_kwargs(c))
+    check_against_r(r, c)
+
+
+@pytest.mark.parametrize("c", KAT, ids=[c["name"] for c in KAT])
+def test_single_fit_known_answers(lib, c):
+    r = lib.single_fit(c["method"], c["y"], c["x"], None, fit_intercept=c["fit_intercept"], alpha=c.get("alpha", 0.0))
+    check_kat(r, c)
+
+
+def test_single_fit_error_taxonomy(lib, oracle):
+    """Same calls as test_oracle_error_taxonomy: identical ok / error code from both implementations."""
+    nan, inf = float("nan"), float("inf")
+    y = [1.0, 2.0, 3.5, 4.0]
+    x = [[1.0, 2.0, 3.0, 4.5]]
+    yy = np.arange(10.0) * 2 + 1 + np.sin(np.arange(10.0))
+    xx = [np.arange(10.0)]
+    w = [1.0] * 10
+    w[3], w[7] = 0.0, -2.0
+    cases = [
+        ("ridge", y, x, None, dict(alpha=-1.0)),
+        ("ols", y, [], None, {}),
+        ("ols", [], [[]], None, {}),
+        ("ols", y, [[1.0, 2.0]], None, {}),
+        ("ols", [nan] * 4, x, None, {}),
+        ("wls", y, x, [0.0, -1.0, nan, inf], {}),
+        ("ols", [1.0, 2.0], [[1.0, 2.0], [2.0, 5.0], [1.0, 7.0]], None, {}),
+        ("ols", [1.0, 2.0, 4.0], [[1.0, 2.0, 3.0], [1.0, 0.0, 2.0]], None, {}),
+        ("ols", y, [[5.0] * 4], None, dict(compute_inference=True)),
+        ("ols", y, [[5.0] * 4], None, dict(fit_intercept=False)),
+        ("wls", yy, xx, w, {}),
+        ("ols", yy, xx, None, dict(y_validity=[1] * 9 + [0])),
+        ("ols", [3.0], [[1.0]], None, {}),
+        ("ols", [3.0], [[1.0]], None, dict(fit_intercept=False)),
+        ("wls", [3.0], [[1.0]], [2.0], {}),
+    ]
+    for method, yv, xv, wv, kw in cases:
+        a = lib.single_fit(method, yv, xv, wv, **kw)
+        b = oracle.single_fit(method, yv, xv, wv, **kw)
+        assert a.ok == b.ok and a.error_code == b.error_code, (method, kw, a.error_code, b.error_code, a.error_message)
+        if a.ok:
+            assert a.n_observations == b.n_observations
+            assert np.array_equal(np.isnan(a.coefficients), np.isnan(b.coefficients))
+            assert max_rel_err(a.coefficients, b.coefficients) < 1e-9
+            for k in ("intercept", "r_squared", "adj_r_squared", "residual_std_error"):
+                va, vb = getattr(a, k), getattr(b, k)
+                assert (math.isnan(va) and math.isnan(vb)) or abs(va - vb) <= 1e-9 * max(1, abs(vb)), (k, va, vb)
+            if kw.get("compute_inference"):
+                assert a.inference_len == b.inference_len
+
+
+def test_free_functions_null_the_pointers(lib):
+    import ctypes as C
+    A = lib.abi
+    l = lib.load_library()
+    y = np.array([1.0, 2.0, 2.5, 4.1, 5.0])
+    x = np.array([1.0, 2.0, 3.0, 4.0, 5.0])
+    xs = (A.DataArray * 1)(A.DataArray(x.ctypes.data_as(A.c_double_p), None, 5))
+    core, inf, err = A.FitResultCore(), A.FitResultInference(), A.AnofoxError()
+    ok = l.anofox_ols_fit(A.DataArray(y.ctypes.data_as(A.c_double_p), None, 5), xs, 1,
+                          A.OlsOptions(True, True, 0.95, 1, 0), C.byref(core), C.byref(inf), C.byref(err))
+    assert ok and bool(core.coefficients) and bool(inf.p_values) and inf.len == 1
+    l.anofox_free_result_core(C.byref(core))
+    l.anofox_free_result_inference(C.byref(inf))
+    assert not core.coefficients and not inf.std_errors and not inf.ci_upper  # lib.rs:272-311
+    l.anofox_free_result_core(None)  # NULL-safe
+    l.anofox_free_result_inference(None)
+    # hc_type is outside the path
+    ok = l.anofox_ols_fit(A.DataArray(y.ctypes.data_as(A.c_double_p), None, 5), xs, 1,
+                          A.OlsOptions(True, True, 0.95, 1, 2), C.byref(core), C.byref(inf), C.byref(err))
+    assert not ok and err.code == A.INVALID_INPUT
+
+
+# ------------------------------------------------------------------ special functions
+def test_device_special_functions(lib, oracle):
+    rng = np.random.default_rng(1)
+    ts, dfs = [], []
+    for df in [1, 2, 3, 4, 5, 7, 10, 25, 44, 98, 146, 183, 991, 5000, 100000]:
+        for t in np.concatenate([rng.uniform(0, 8, 25), [1e-6, 0.3, 15.0, 45.0, 400.0]]):
+            ts.append(t)
+            dfs.append(df)
+    got = lib.eval_specfun(0, ts, dfs)
+    want = np.array([oracle.t_two_sided_p(t, d) for t, d in zip(ts, dfs)])
+    rel = np.abs(got - want) / np.maximum(want, 1e-300)
+    assert rel.max() < 1e-10, (rel.max(), ts[int(rel.argmax())], dfs[int(rel.argmax())])
+    lv, dd = [], []
+    for df in [1, 2, 3, 4, 5, 8, 13, 44, 98, 183, 991, 4096, 4097, 100000]:
+        for level in [0.5, 0.8, 0.9, 0.95, 0.99, 0.999, 0.999999]:
+            lv.append(level)
+            dd.append(df)
+    got = lib.eval_specfun(1, lv, dd)
+    want = np.array([oracle.t_critical(l, d) for l, d in zip(lv, dd)])
+    rel = np.abs(got - want) / want
+    assert rel.max() < 1e-11, (rel.max(), lv[int(rel.argmax())], dd[int(rel.argmax())])
+    fs, d1, d2 = [], [], []
+    for a, b in [(1, 5), (3, 146), (5, 44), (16, 183), (8, 991), (2, 2), (64, 100000), (1, 1)]:
+        for f in [1e-3, 0.5, 1.0, 3.0, 25.0, 1e3, 1e5]:
+            fs.append(f)
+            d1.append(a)
+            d2.append(b)
+    got = lib.eval_specfun(2, fs, d1, d2)
+    want = np.array([oracle.f_upper_p(f, a, b) for f, a, b in zip(fs, d1, d2)])
+    rel = np.abs(got - want) / np.maximum(want, 1e-300)
+    assert rel.max() < 1e-10, rel.max()
+    # drop-in scalar symbols
+    assert math.isnan(lib.t_critical(0.95, 0)) and math.isnan(lib.t_critical(1.0, 3))
+    assert abs(lib.t_critical(0.95, 98) - oracle.t_critical(0.95, 98)) < 1e-12
+    coef, x = [2.0, float("nan"), -1.0], [1.5, 100.0, 2.0]
+    for icpt in (0.5, float("nan")):
+        for rse, n in [(0.7, 40), (float("nan"), 40), (0.7, 4), (0.0, 40), (0.7, 5)]:
+            a = lib.predict_with_interval(coef, icpt, x, rse, n, 0.9)
+            b = oracle.predict_with_interval(coef, icpt, x, rse, n, 0.9)
+            assert a[0] == b[0] and np.allclose(a[1], b[1], rtol=1e-12, atol=0), (icpt, rse, n, a, b)
+    assert lib.predict_with_interval(coef, 0.0, [1.0], 1.0, 10, 0.9)[0] is False  # length mismatch
+
+
+# ------------------------------------------------------------------ batch layer vs oracle
+def make_case(rng, G, n_lo, n_hi, p, dirty=True, weights=False, collinear=True):
+    sizes = rng.integers(n_lo, n_hi + 1, size=G)
+    if dirty and G >= 8:
+        sizes[1], sizes[3], sizes[5] = 0, 1, 2  # empty / single-row / two-row groups
+    offsets = np.zeros(G + 1, dtype=np.int64)
+    np.cumsum(sizes, out=offsets[1:])
+    N = int(offsets[-1])
+    x = rng.uniform(-10, 10, size=(N, p))
+    gid = np.repeat(np.arange(G), sizes)
+    beta = rng.uniform(-5, 5, size=(G, p))
+    y = rng.uniform(-10, 10, size=G)[gid] + np.einsum("ij,ij->i", x, beta[gid]) + rng.normal(0, 2.0, size=N)
+    w = rng.uniform(0.5, 1.5, size=N) if weights else None
+    if dirty:
+        u = rng.uniform(size=G)
+        for g in np.flatnonzero(u < 0.15):  # a constant column
+            x[offsets[g]:offsets[g + 1], rng.integers(0, p)] = 3.25
+        if collinear and p >= 2:
+            for g in np.flatnonzero((u >= 0.15) & (u < 0.30)):  # duplicated / affine-dependent column
+                a, b = rng.choice(p, size=2, replace=False)
+                x[offsets[g]:offsets[g + 1], max(a, b)] = 2.0 * x[offsets[g]:offsets[g + 1], min(a, b)] + 3.0
+        for g in np.flatnonzero((u >= 0.30) & (u < 0.33)):  # every column constant
+            x[offsets[g]:offsets[g + 1], :] = 1.5
+        rows = rng.integers(0, max(N, 1), size=max(N // 40, 1))
+        x[rows, rng.integers(0, p, size=rows.size)] = np.nan  # NULL elements -> NaN -> row dropped
+        rows = rng.integers(0, max(N, 1), size=max(N // 60, 1))
+        y[rows] = np.where(rng.uniform(size=rows.size) < 0.5, np.nan, np.inf)
+        if G >= 8 and sizes[7] > 0:
+            x[offsets[7], 0] = np.nan  # the first row of a group is invalid: shift row = a later one
+            y[offsets[7]:offsets[8]][:1] = np.nan
+        if G >= 10:
+            y[offsets[9]:offsets[10]] = np.nan  # a group with no valid row at all
+        if weights:
+            rows = rng.integers(0, max(N, 1), size=max(N // 30, 1))
+            w[rows] = rng.choice([0.0, -1.0, np.nan, np.inf], size=rows.size)
+    return dict(offsets=offsets, y=y, x=x, w=w)
+
+
+CASES = [
+    # method, p, intercept, inference, (n_lo, n_hi), G
+    ("ols", 1, True, True, (3, 40), 300),
+    ("ols", 3, True, True, (5, 120), 400),
+    ("ols", 5, True, True, (30, 70), 600),
+    ("ols", 5, False, True, (30, 70), 300),
+    ("ols", 6, True, False, (10, 90), 300),
+    ("ols", 7, True, True, (10, 90), 300),   # SIDE mode (p % 8 == 7)
+    ("ols", 8, True, True, (12, 300), 300),  # SIDE mode (p % 8 == 0)
+    ("ols", 9, True, True, (12, 100), 200),
+    ("ols", 13, False, True, (20, 100), 200),
+    ("wls", 5, True, True, (30, 70), 400),
+    ("wls", 16, True, True, (40, 260), 200),
+    ("wls", 8, False, False, (12, 100), 200),
+    ("ridge", 5, True, True, (30, 70), 400),
+    ("ridge", 16, True, True, (40, 260), 200),
+    ("ridge", 16, False, False, (40, 260), 100),
+    ("ols", 17, True, True, (40, 200), 100),
+    ("ols", 24, True, False, (60, 200), 60),
+    ("ols", 32, True, True, (80, 200), 40),
+    ("ols", 40, True, False, (100, 200), 20),
+    ("ols", 64, True, True, (150, 260), 12),
+]
+
+
+@pytest.mark.parametrize("method,p,icpt,inf,nr,G", CASES,
+                         ids=[f"{c[0]}-p{c[1]}-{'i' if c[2] else 'noi'}-{'inf' if c[3] else 'core'}" for c in CASES])
+def test_batch_parity_vs_oracle(lib, oracle, method, p, icpt, inf, nr, G):
+    rng = np.random.default_rng(1000 + p * 7 + len(method))
+    c = make_case(rng, G, nr[0], nr[1], p, dirty=True, weights=(method == "wls"))
+    opt = dict(method=method, fit_intercept=icpt, compute_inference=inf, confidence_level=0.9,
+               alpha=1.0 if method == "ridge" else 0.0)
+    dev = lib.fit_batch_host(c["offsets"], c["y"], c["x"], c["w"], **opt)
+    ora = oracle.fit_batch(c["offsets"], c["y"], c["x"], c["w"], **opt)
+    assert ora["rc"] == 0
+    st = ora["status"]
+    # the case generator must actually exercise the NULL patterns it claims to
+    assert (st == 1000).sum() >= 2 and (st == 10).sum() >= 1 and (st == 0).sum() > G // 2
+    assert_fit_parity(dev, ora, rtol=1e-9, inference=inf, label=f"{method} p={p}")
+
+
+def test_batch_ridge_glmnet_scaling(lib, oracle):
+    rng = np.random.default_rng(5)
+    c = make_case(rng, 100, 30, 80, 4, dirty=False)
+    opt = dict(method="ridge", alpha=0.3, lambda_scaling="glmnet", compute_inference=True)
+    dev = lib.fit_batch_host(c["offsets"], c["y"], c["x"], None, **opt)
+    ora = oracle.fit_batch(c["offsets"], c["y"], c["x"], None, **opt)
+    assert_fit_parity(dev, ora, rtol=1e-9, inference=True)
+    with pytest.raises(lib.B200Error) as e:
+        lib.fit_batch_host(c["offsets"], c["y"], c["x"], None, method="ridge", alpha=-0.5)
+    assert e.value.code == lib.abi.INVALID_ALPHA  # ridge.rs:38-40: before anything else
+
+
+def test_batch_solver_option_is_result_neutral(lib):
+    """test_map_options.test: svd / qr / cholesky agree to 1e-10 on r_squared."""
+    rng = np.random.default_rng(6)
+    c = make_case(rng, 50, 20, 60, 3, dirty=False)
+    r = [lib.fit_batch_host(c["offsets"], c["y"], c["x"], None, solver=s)["r_squared"] for s in ("svd", "qr", "cholesky")]
+    assert np.abs(r[0] - r[1]).max() < 1e-10 and np.abs(r[0] - r[2]).max() < 1e-10
+
+
+def test_batch_empty_and_degenerate_inputs(lib, oracle):
+    # no groups at all
+    out = lib.fit_batch_host(np.zeros(1, dtype=np.int64), np.zeros(0), np.zeros((0, 3)), None)
+    assert out["status"].shape == (0,)
+    # only empty groups
+    out = lib.fit_batch_host(np.zeros(6, dtype=np.int64), np.zeros(0), np.zeros((0, 2)), None)
+    assert (out["status"] == 1000).all() and np.isnan(out["coefficients"]).all()
+    # error_handling.test:102-131: a group with n < p + 1 is NULL, its neighbour is fine
+    y = np.array([1.0, 2.0, 1.0, 2.2, 2.9, 4.1, 5.2])
+    x = np.array([[1.0, 2.0], [2.0, 1.0], [1.0, 5.0], [2.0, 3.0], [3.0, 4.5], [4.0, 1.0], [5.0, 2.0]])
+    off = np.array([0, 2, 7], dtype=np.int64)
+    dev = lib.fit_batch_host(off, y, x, None)
+    ora = oracle.fit_batch(off, y, x, None)
+    assert dev["status"].tolist() == ora["status"].tolist() == [6, 0]
+    assert_fit_parity(dev, ora)
+    # many tiny groups (more groups than a stage header holds) and offsets with repeats
+    rng = np.random.default_rng(7)
+    c = make_case(rng, 5000, 0, 4, 2, dirty=False)
+    dev = lib.fit_batch_host(c["offsets"], c["y"], c["x"], None, compute_inference=True)
+    ora = oracle.fit_batch(c["offsets"], c["y"], c["x"], None, compute_inference=True)
+    assert_fit_parity(dev, ora, rtol=1e-8, inference=True, ptol=1e-6, check_ic=False)
+
+
+def test_batch_large_groups_take_the_streaming_path(lib, oracle):
+    """Groups larger than a shared-memory stage are accumulated by the streaming kernel."""
+    rng = np.random.default_rng(8)
+    sizes = np.array([30, 40000, 25, 0, 9000, 60, 30000, 17])
+    offsets = np.zeros(len(sizes) + 1, dtype=np.int64)
+    np.cumsum(sizes, out=offsets[1:])
+    N, p = int(offsets[-1]), 5
+    x = rng.uniform(-10, 10, size=(N, p))
+    y = 3.0 + x @ rng.uniform(-5, 5, size=p) + rng.normal(0, 2.0, size=N)
+    w = rng.uniform(0.5, 1.5, size=N)
+    x[offsets[1], 2] = np.nan  # first row of a big group invalid
+    x[offsets[4]:offsets[5], 3] = -7.0  # constant column inside a big group
+    y[rng.integers(0, N, size=50)] = np.nan
+    for method in ("ols", "wls"):
+        opt = dict(method=method, compute_inference=True)
+        dev = lib.fit_batch_host(offsets, y, x, w, **opt)
+        ora = oracle.fit_batch(offsets, y, x, w, **opt)
+        assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label=method)
+    # one very wide big group
+    N, p = 6000, 64
+    x = rng.normal(size=(N, p))
+    y = x @ rng.uniform(-1, 1, size=p) + rng.normal(0, 0.5, size=N)
+    off = np.array([0, N], dtype=np.int64)
+    dev = lib.fit_batch_host(off, y, x, None, compute_inference=True)
+    ora = oracle.fit_batch(off, y, x, None, compute_inference=True)
+    assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label="p64")
+
+
+def test_exact_fit_groups_use_the_residual_pass(lib, oracle):
+    """Noise-free groups: the moment form of RSS cancels completely, the queued residual pass must restore
+    r_squared == 1 to the last digits and a residual standard error at rounding level (anofox_stats.test:12-15,
+    ols_validation.test:121-133)."""
+    rng = np.random.default_rng(12)
+    c = make_case(rng, 300, 10, 60, 4, dirty=False)
+    gid = np.repeat(np.arange(300), np.diff(c["offsets"]))
+    beta = rng.uniform(-5, 5, size=(300, 4))
+    y = 2.0 + np.einsum("ij,ij->i", c["x"], beta[gid])
+    y[c["offsets"][150]:] += rng.normal(0, 1e-5, size=len(y) - c["offsets"][150])  # half: tiny but real noise
+    for method, w in (("ols", None), ("wls", rng.uniform(0.5, 1.5, size=len(y)))):
+        opt = dict(method=method, compute_inference=True)
+        dev = lib.fit_batch_host(c["offsets"], y, c["x"], w, **opt)
+        ora = oracle.fit_batch(c["offsets"], y, c["x"], w, **opt)
+        assert (dev["status"] == 0).all()
+        assert np.abs(dev["coefficients"] - ora["coefficients"]).max() < 1e-9
+        assert (dev["r_squared"][:150] >= 1 - 1e-14).all()
+        assert (dev["residual_std_error"][:150] < 1e-11).all()  # |y| ~ 100: rounding-level residuals
+        # tiny-noise half: the statistic is well defined and must agree to 1e-9 although RSS/TSS ~ 1e-14
+        e = max_rel_err(dev["residual_std_error"][150:], ora["residual_std_error"][150:])
+        assert e < 1e-6, e  # limited by the coefficients' own 1e-16 * cond rounding, not by cancellation
+        assert np.abs(dev["r_squared"][150:] - ora["r_squared"][150:]).max() < 1e-15
+
+
+def test_fit_predict_parity(lib, oracle):
+    """Engine of ols/ridge/wls_fit_predict_by: every row predicted, held-out rows (y NULL) not trained on."""
+    rng = np.random.default_rng(9)
+    for method, p in [("ols", 3), ("ols", 8), ("ridge", 5), ("wls", 4)]:
+        c = make_case(rng, 120, 8, 90, p, dirty=True, weights=(method == "wls"), collinear=True)
+        N = len(c["y"])
+        hold = rng.uniform(size=N) < 0.2
+        c["y"][hold] = np.nan
+        opt = dict(method=method, confidence_level=0.95, alpha=1.0 if method == "ridge" else 0.0)
+        pd, fd = lib.fit_predict_batch_host(c["offsets"], c["y"], c["x"], c["w"], None, **opt)
+        po, fo = oracle.fit_predict_batch(c["offsets"], c["y"], c["x"], c["w"], None, **opt)
+        assert np.array_equal(pd["is_training"], po["is_training"])
+        assert_fit_parity(fd, fo, rtol=1e-9, label=f"predict/{method}")
+        for k in ("yhat", "yhat_lower", "yhat_upper"):
+            assert np.array_equal(np.isnan(pd[k]), np.isnan(po[k])), k  # NULL triples at the same rows
+            m = np.isfinite(po[k])
+            scale = np.maximum(np.abs(po["yhat"][m]), 1.0)
+            assert (np.abs(pd[k][m] - po[k][m]) / scale).max() < 1e-9, k
+        ok = np.isfinite(po["yhat"])
+        assert (pd["yhat_lower"][ok] <= pd["yhat"][ok]).all() and (pd["yhat"][ok] <= pd["yhat_upper"][ok]).all()
+        # explicit training flags (split column semantics): only flagged rows train
+        train = (rng.uniform(size=N) < 0.7).astype(np.uint8)
+        train[~np.isfinite(c["y"])] = 0
+        pd, fd = lib.fit_predict_batch_host(c["offsets"], c["y"], c["x"], c["w"], train, **opt)
+        po, fo = oracle.fit_predict_batch(c["offsets"], c["y"], c["x"], c["w"], train, **opt)
+        assert np.array_equal(pd["is_training"], train)
+        assert_fit_parity(fd, fo, rtol=1e-9, label=f"predict-flags/{method}")
+        m = np.isfinite(po["yhat_upper"])
+        assert np.array_equal(np.isnan(pd["yhat_upper"]), np.isnan(po["yhat_upper"]))
+        assert (np.abs(pd["yhat_upper"][m] - po["yhat_upper"][m]) / np.maximum(np.abs(po["yhat"][m]), 1)).max() < 1e-9
+
+
+def test_row_sharded_single_group(lib, oracle):
+    """Config-4 path on one GPU: two row shards -> moment blocks -> SUM / MAX combine -> solve."""
+    import ctypes as C
+    import torch
+    A = lib.abi
+    l = lib.load_library()
+    rng = np.random.default_rng(10)
+    for p, N in [(5, 20000), (64, 30000), (16, 9001)]:
+        x = rng.normal(size=(N, p))
+        for j in range(1, p):
+            x[:, j] = 0.3 * x[:, j - 1] + math.sqrt(1 - 0.09) * x[:, j]  # AR(1) correlation across features
+        y = 1.5 + x @ rng.uniform(-1, 1, size=p) + rng.normal(0, 0.7, size=N)
+        y[5] = np.nan
+        x[17, p - 1] = np.inf
+        off = np.array([0, N], dtype=np.int64)
+        ora = oracle.fit_batch(off, y, x, None, compute_inference=True)
+        xd, yd = torch.tensor(x, device="cuda"), torch.tensor(y, device="cuda")
+        shift = torch.cat([xd[0], yd[:1]]).contiguous()  # rank 0's first valid row, "broadcast"
+        L = lib.moment_block_len(p)
+        cut = N // 3
+        blocks, cdevs = [], []
+        wb = l.anofox_b200_workspace_bytes(1, N, p)
+        ws = torch.empty(wb + 256, dtype=torch.uint8, device="cuda")
+        wp = (ws.data_ptr() + 255) & ~255
+        err = A.AnofoxError()
+        for a, b in [(0, cut), (cut, N)]:
+            m = torch.zeros(L, dtype=torch.float64, device="cuda")
+            cd = torch.zeros(p, dtype=torch.float64, device="cuda")
+            xs, ys = xd[a:b].contiguous(), yd[a:b].contiguous()
+            rc = l.anofox_b200_moments_device(C.c_void_p(ys.data_ptr()), C.c_void_p(xs.data_ptr()), None, b - a, p,
+                                              C.c_void_p(shift.data_ptr()), C.c_void_p(m.data_ptr()),
+                                              C.c_void_p(cd.data_ptr()), C.c_void_p(wp), wb, None, C.byref(err))
+            assert rc == 0, err.message
+            torch.cuda.synchronize()
+            blocks.append(m)
+            cdevs.append(cd)
+        msum = blocks[0] + blocks[1]            # what ncclAllReduce(SUM) produces
+        cmax = torch.maximum(cdevs[0], cdevs[1])  # ncclAllReduce(MAX)
+        fit = lib.DeviceFit(1, N, p, inference=True)
+        o = A.make_fit_options(compute_inference=True)
+        rc = l.anofox_b200_solve_moments_device(C.c_void_p(msum.data_ptr()), C.c_void_p(cmax.data_ptr()),
+                                                C.c_void_p(shift.data_ptr()), p, C.byref(o), C.byref(fit.out_struct),
+                                                None, C.byref(err))
+        assert rc == 0, err.message
+        torch.cuda.synchronize()
+        dev = {k: v.cpu().numpy() for k, v in fit.out.items()}
+        assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label=f"sharded p={p}")
+
+
+def test_device_pointer_api_matches_host_api(lib):
+    import torch
+    rng = np.random.default_rng(11)
+    c = make_case(rng, 700, 20, 80, 5, dirty=True, weights=True)
+    host = lib.fit_batch_host(c["offsets"], c["y"], c["x"], c["w"], method="wls", compute_inference=True)
+    G, N = len(c["offsets"]) - 1, len(c["y"])
+    f = lib.DeviceFit(G, N, 5, inference=True)
+    t = {k: torch.tensor(c[k], device="cuda") for k in ("offsets", "y", "x", "w")}
+    before = lib.launch_count()
+    out = f.fit(t["offsets"], t["y"], t["x"], t["w"], method="wls", compute_inference=True)
+    torch.cuda.synchronize()
+    assert lib.launch_count() - before >= 3  # bounds + accumulate + solve (+ t table)
+    for k, v in out.items():
+        assert np.array_equal(v.cpu().numpy(), host[k], equal_nan=True), k  # same kernels, same bits
+
+
+def test_full_size_properties_config2(lib):
+    """BASELINE config 2 at full size (1 M groups x 50 rows x 5 features, inference on): size-independent
+    properties instead of an oracle run -- scale equivariance, group-permutation invariance of the results,
+    linearity in y and a checksum of checksums against sub-batch runs."""
+    import torch
+    synth = __import__("anofox_statistics_b200.synth", fromlist=["synth"])
+    G, n, p = 1_000_000, 50, 5
+    d = synth.make_torch(G, n, p, seed=2)
+    f = lib.DeviceFit(G, G * n, p, inference=True)
+    opt = dict(method="ols", compute_inference=True)
+    base = {k: v.clone() for k, v in f.fit(d["offsets"], d["y"], d["x"], **opt).items()}
+    torch.cuda.synchronize()
+    assert int((base["status"] != 0).sum()) == 0 and int((base["n_observations"] != n).sum()) == 0
+    assert bool(torch.isfinite(base["coefficients"]).all())
+    assert bool(((base["r_squared"] > 0.0) & (base["r_squared"] <= 1.0)).all())
+    assert bool(((base["p_values"] >= 0) & (base["p_values"] <= 1)).all())
+    # (1) y -> 3 y + 2: slopes x3, intercept 3a+2, r2 / t / p unchanged
+    y2 = d["y"] * 3.0 + 2.0
+    o2 = f.fit(d["offsets"], y2, d["x"], **opt)
+    torch.cuda.synchronize()
+    assert float((o2["coefficients"] - 3 * base["coefficients"]).abs().max()) < 1e-9
+    assert float((o2["intercept"] - (3 * base["intercept"] + 2)).abs().max()) < 1e-8
+    assert float((o2["r_squared"] - base["r_squared"]).abs().max()) < 1e-11
+    assert float(((o2["t_values"] - base["t_values"]).abs() / base["t_values"].abs().clamp_min(1e-3)).max()) < 1e-8
+    # (2) the first 4096 groups fitted alone give bit-identical results (no cross-group leakage)
+    Gs = 4096
+    fs = lib.DeviceFit(Gs, Gs * n, p, inference=True)
+    os_ = fs.fit(d["offsets"][:Gs + 1].contiguous(), d["y"][:Gs * n].contiguous(), d["x"][:Gs * n].contiguous(), **opt)
+    torch.cuda.synchronize()
+    for k in ("coefficients", "intercept", "r_squared", "p_values", "f_pvalue", "residual_std_error"):
+        assert torch.equal(os_[k], base[k][:Gs]), k
+    # (3) checksum of checksums: sum of per-group RSS equals the RSS of the stacked residuals
+    xb = d["x"].view(G, n, p)
+    fitted = (xb * base["coefficients"][:, None, :]).sum(-1) + base["intercept"][:, None]
+    rss = ((d["y"].view(G, n) - fitted) ** 2).sum(-1)
+    assert float(((rss - base["rss"]).abs() / rss).max()) < 1e-9
