@@ -1,0 +1,62 @@
+// acc_launch.h -- host-side launchers of the accumulation kernels, one translation unit per tile count
+// (acc_nt*.cu) so that the template instantiations compile in parallel.
+#pragma once
+#include "accumulate.cuh"
+
+namespace b200 {
+
+constexpr int kStreamWarps = 8;
+
+#define B200_DECLARE_NT(NT_)                                                                                         \
+	cudaError_t launch_resident_nt##NT_(bool side, bool has_w, bool has_t, const AccArgs &a, int grid,               \
+	                                    cudaStream_t st);                                                            \
+	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st);
+B200_DECLARE_NT(1)
+B200_DECLARE_NT(2)
+B200_DECLARE_NT(3)
+B200_DECLARE_NT(4)
+B200_DECLARE_NT(5)
+B200_DECLARE_NT(6)
+B200_DECLARE_NT(7)
+B200_DECLARE_NT(8)
+B200_DECLARE_NT(9)
+#undef B200_DECLARE_NT
+
+// consumer warps per CTA of the resident kernel: register budget of the DMMA accumulators
+constexpr int resident_warps(int nt) { return nt <= 2 ? 16 : (nt <= 4 ? 8 : 4); }
+
+template <int NT, bool SIDE, int NCW, bool HASW, bool HAST>
+cudaError_t launch_resident_t(const AccArgs &a, int grid, cudaStream_t st) {
+	auto kern = acc_resident_kernel<NT, SIDE, NCW, HASW, HAST>;
+	const size_t dyn = (size_t)a.n_stages * a.stage_bytes;
+	cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+	if (e != cudaSuccess) return e;
+	kern<<<grid, 32 * (NCW + 1), dyn, st>>>(a);
+	return cudaGetLastError();
+}
+
+#define B200_DEFINE_NT(NT_)                                                                                          \
+	cudaError_t launch_resident_nt##NT_(bool side, bool has_w, bool has_t, const AccArgs &a, int grid,               \
+	                                    cudaStream_t st) {                                                           \
+		constexpr int W = resident_warps(NT_);                                                                       \
+		const int sel = (side ? 4 : 0) | (has_w ? 2 : 0) | (has_t ? 1 : 0);                                          \
+		switch (sel) {                                                                                               \
+		case 0: return launch_resident_t<NT_, false, W, false, false>(a, grid, st);                                  \
+		case 1: return launch_resident_t<NT_, false, W, false, true>(a, grid, st);                                   \
+		case 2: return launch_resident_t<NT_, false, W, true, false>(a, grid, st);                                   \
+		case 3: return launch_resident_t<NT_, false, W, true, true>(a, grid, st);                                    \
+		case 4: return launch_resident_t<NT_, true, W, false, false>(a, grid, st);                                   \
+		case 5: return launch_resident_t<NT_, true, W, false, true>(a, grid, st);                                    \
+		case 6: return launch_resident_t<NT_, true, W, true, false>(a, grid, st);                                    \
+		default: return launch_resident_t<NT_, true, W, true, true>(a, grid, st);                                    \
+		}                                                                                                            \
+	}                                                                                                                \
+	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st) {                   \
+		if (side)                                                                                                    \
+			acc_stream_kernel<NT_, true, kStreamWarps><<<grid, 32 * kStreamWarps, 0, st>>>(a);                       \
+		else                                                                                                         \
+			acc_stream_kernel<NT_, false, kStreamWarps><<<grid, 32 * kStreamWarps, 0, st>>>(a);                      \
+		return cudaGetLastError();                                                                                   \
+	}
+
+} // namespace b200

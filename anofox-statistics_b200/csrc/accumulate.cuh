@@ -100,7 +100,7 @@ __device__ __forceinline__ double xor_max4(double v) {
 template <int NT, bool SIDE> struct WarpAcc {
 	static constexpr int NTP = NT * (NT + 1) / 2;
 	double c0[NTP], c1[NTP]; // DMMA accumulators, tile pairs (ta <= tb) in row-major order
-	double cd[NT];           // max |d| per owned column
+	bool nc[NT];             // some valid row differs from the shift row by >= 1e-10 (ols.rs:76-87)
 	double sxy[SIDE ? NT : 1], s1[SIDE ? NT : 1];
 	double syy, sy, sw;
 	int nv, ns;
@@ -108,7 +108,7 @@ template <int NT, bool SIDE> struct WarpAcc {
 #pragma unroll
 		for (int i = 0; i < NTP; ++i) c0[i] = c1[i] = 0.0;
 #pragma unroll
-		for (int t = 0; t < NT; ++t) cd[t] = 0.0;
+		for (int t = 0; t < NT; ++t) nc[t] = false;
 #pragma unroll
 		for (int t = 0; t < (SIDE ? NT : 1); ++t) sxy[t] = s1[t] = 0.0;
 		syy = sy = sw = 0.0;
@@ -166,7 +166,7 @@ __device__ __forceinline__ void acc_rows(WarpAcc<NT, SIDE> &A, const double *__r
 				if (c == p + 1) dv = ok ? 1.0 : 0.0;
 			}
 			d[t] = dv;
-			A.cd[t] = fmax(A.cd[t], fabs(dv));
+			A.nc[t] = A.nc[t] || (fabs(dv) >= 1e-10);
 			a[t] = has_w ? weff * dv : dv;
 		}
 		int pair = 0;
@@ -281,7 +281,8 @@ __device__ __forceinline__ void store_record(WarpAcc<NT, SIDE> &A, double *__res
 #pragma unroll
 	for (int t = 0; t < NT; ++t) {
 		const int c = 8 * t + cl;
-		const double cdm = xor_max4(A.cd[t]);
+		const unsigned ncm = __ballot_sync(0xffffffffu, A.nc[t]);
+		const double cdm = ((ncm >> (4 * cl)) & 0xFu) ? 1.0 : 0.0;
 		if (SIDE) {
 			const double vxy = xor_sum4(A.sxy[t]);
 			const double v1 = xor_sum4(A.s1[t]);
@@ -321,13 +322,176 @@ __device__ __forceinline__ void store_empty_record(double *__restrict__ rec, int
 	for (int i = lane; i < L; i += 32) rec[i] = (i == 2) ? (double)n_state : 0.0;
 }
 
-// One whole group resident in shared memory -> its record.
+// ---------------------------------------------------------------------------------------------
+// Fast path of the resident kernel. Every lane owns, per tile, ONE shared-memory address and a
+// per-step stride: feature columns walk the row-major X block, the y column walks the y block,
+// the constant-1 column and the zero padding point at two constants (stride 0). A 4-row step is
+// then: one LDS + one DADD (difference against the shift row) + one DSETP (constant-column flag)
+// per tile, and the DMMAs. Nothing else is checked per element: non-finite inputs poison the
+// accumulators and the group is redone by the checked path above.
+//   HASW: rows with w <= 0 (or NaN) are masked here (they are legitimate input, wls.rs:76-86).
+//   HAST: rows whose training flag is 0 are masked (held-out rows of *_fit_predict_agg).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+	double v;
+	asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+	return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+	uint32_t v;
+	asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+	return v;
+}
+
+struct SmemGroup { // shared-space addresses of one group's rows
+	uint32_t x, y, w, t; // byte addresses (w / t unused unless HASW / HAST)
+	uint32_t kone, kzero; // addresses of the constants 1.0 and 0.0
+};
+
 template <int NT, bool SIDE>
-__device__ __forceinline__ void accumulate_group(const double *xs, const double *ys, const double *ws,
-                                                 const uint8_t *ts, int n, int p, int lane, double *rec) {
+__device__ __forceinline__ void lane_pointers(const SmemGroup &g, int p, int lane, uint32_t (&pa)[NT], uint32_t (&st)[NT]) {
+	const int rl = lane & 3, cl = lane >> 2;
+#pragma unroll
+	for (int t = 0; t < NT; ++t) {
+		const int c = 8 * t + cl;
+		if (c < p) {
+			pa[t] = g.x + (uint32_t)(rl * p + c) * 8u;
+			st[t] = 32u * (uint32_t)p;
+		} else if (!SIDE && c == p) {
+			pa[t] = g.y + (uint32_t)rl * 8u;
+			st[t] = 32u;
+		} else if (!SIDE && c == p + 1) {
+			pa[t] = g.kone;
+			st[t] = 0u;
+		} else {
+			pa[t] = g.kzero;
+			st[t] = 0u;
+		}
+	}
+}
+
+template <int NT, bool SIDE, bool HASW, bool HAST, bool TAIL>
+__device__ __forceinline__ void fast_step(WarpAcc<NT, SIDE> &A, uint32_t (&pa)[NT], const uint32_t (&st)[NT],
+                                          uint32_t &py, uint32_t &pw, uint32_t &pt, const double (&sh)[NT], double shy,
+                                          bool in_range) {
+	double v[NT];
+#pragma unroll
+	for (int t = 0; t < NT; ++t) {
+		v[t] = lds_f64(pa[t]);
+		pa[t] += st[t];
+	}
+	bool ok = true;
+	double wv = 1.0, yv = 0.0;
+	if (SIDE) {
+		yv = lds_f64(py);
+		py += 32u;
+	}
+	if (HASW) {
+		wv = lds_f64(pw);
+		pw += 32u;
+		ok = wv > 0.0;
+	}
+	if (HAST) {
+		const uint32_t tr = lds_u8(pt);
+		pt += 4u;
+		ok = ok && tr != 0u;
+		if (!TAIL || in_range) A.ns += tr != 0u ? 1 : 0;
+	}
+	if (TAIL) ok = ok && in_range;
+	constexpr bool MASK = HASW || HAST || TAIL;
+	if (MASK) A.nv += ok ? 1 : 0;
+	const double weff = MASK ? (ok ? wv : 0.0) : wv;
+	double d[NT], a[NT];
+#pragma unroll
+	for (int t = 0; t < NT; ++t) {
+		double dv = v[t] - sh[t];
+		if (MASK) dv = ok ? dv : 0.0;
+		d[t] = dv;
+		A.nc[t] = A.nc[t] || (fabs(dv) >= 1e-10);
+		a[t] = HASW ? weff * dv : dv;
+	}
+	int pair = 0;
+#pragma unroll
+	for (int ta = 0; ta < NT; ++ta)
+#pragma unroll
+		for (int tb = ta; tb < NT; ++tb) {
+			dmma_884(A.c0[pair], A.c1[pair], a[ta], d[tb]);
+			++pair;
+		}
+	if (SIDE) {
+		double dy = yv - shy;
+		if (MASK) dy = ok ? dy : 0.0;
+		const double wdy = HASW ? weff * dy : dy;
+#pragma unroll
+		for (int t = 0; t < NT; ++t) {
+			A.sxy[t] = fma(d[t], wdy, A.sxy[t]);
+			A.s1[t] += a[t];
+		}
+		A.syy = fma(wdy, dy, A.syy);
+		A.sy += wdy;
+		A.sw += weff;
+	}
+}
+
+// Returns false when the result is poisoned (non-finite input somewhere) or no row passed the
+// w / train mask with a usable shift; the caller then runs the checked path.
+template <int NT, bool SIDE, bool HASW, bool HAST>
+__device__ __forceinline__ bool accumulate_group_fast(WarpAcc<NT, SIDE> &A, const SmemGroup &g, int n, int p, int lane,
+                                                      double (&sh)[NT], double &shy) {
+	const int rl = lane & 3, cl = lane >> 2;
+	// first row that passes the mask (row 0 in the plain case)
+	int f = 0;
+	if (HASW || HAST) {
+		f = -1;
+		for (int base = 0; base < n && f < 0; base += 32) {
+			const int r = base + lane;
+			bool ok = r < n;
+			if (ok && HASW) ok = lds_f64(g.w + (uint32_t)r * 8u) > 0.0;
+			if (ok && HAST) ok = lds_u8(g.t + (uint32_t)r) != 0u;
+			const unsigned m = __ballot_sync(0xffffffffu, ok);
+			if (m) f = base + __ffs(m) - 1;
+		}
+		if (f < 0) return false;
+	}
+	uint32_t pa[NT], st[NT];
+	lane_pointers<NT, SIDE>(g, p, lane, pa, st);
+#pragma unroll
+	for (int t = 0; t < NT; ++t) {
+		const int c = 8 * t + cl;
+		const bool data = (c < p) || (!SIDE && c == p);
+		// row f of this lane's column: undo the lane's own row offset (rl), then add f rows
+		sh[t] = data ? lds_f64(pa[t] + (uint32_t)(f - rl) * (st[t] >> 2)) : 0.0;
+	}
+	shy = lds_f64(g.y + (uint32_t)f * 8u);
+	uint32_t py = g.y + (uint32_t)rl * 8u, pw = g.w + (uint32_t)rl * 8u, pt = g.t + (uint32_t)rl;
+	A.clear();
+	const int nfull = n >> 2;
+#pragma unroll 2
+	for (int s = 0; s < nfull; ++s) fast_step<NT, SIDE, HASW, HAST, false>(A, pa, st, py, pw, pt, sh, shy, true);
+	if (n & 3) {
+		const bool in_range = rl < (n & 3);
+		if (!in_range) { // keep the loads inside the group's rows
+#pragma unroll
+			for (int t = 0; t < NT; ++t) pa[t] -= (uint32_t)rl * (st[t] >> 2);
+			py -= (uint32_t)rl * 8u;
+			pw -= (uint32_t)rl * 8u;
+			pt -= (uint32_t)rl;
+		}
+		fast_step<NT, SIDE, HASW, HAST, true>(A, pa, st, py, pw, pt, sh, shy, in_range);
+	}
+	// unmasked full steps of the plain case did not count their rows
+	if (!(HASW || HAST)) A.nv += nfull;
+	return !acc_poisoned<NT, SIDE>(A);
+}
+
+// One whole group resident in shared memory -> its record.
+template <int NT, bool SIDE, bool HASW, bool HAST>
+__device__ __forceinline__ void accumulate_group(const SmemGroup &sg, const double *xs, const double *ys,
+                                                 const double *ws, const uint8_t *ts, int n, int p, int lane,
+                                                 double *rec) {
 	// rows that entered the aggregate state: all of them, or the flagged training rows
 	int n_state = n;
-	if (ts) {
+	if (HAST) {
 		int c = 0;
 		for (int r = lane; r < n; r += 32) c += ts[r] ? 1 : 0;
 		for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
@@ -339,18 +503,9 @@ __device__ __forceinline__ void accumulate_group(const double *xs, const double 
 	}
 	WarpAcc<NT, SIDE> A;
 	double sh[NT], shy;
-	// fast path: features assumed finite
-	int f = find_first_valid<NT, SIDE, false>(xs, ys, ws, ts, n, p, lane);
-	if (f < 0) {
-		store_empty_record(rec, p, lane, n_state);
-		return;
-	}
-	load_shift<NT, SIDE>(xs, ys, f, p, lane, sh, shy);
-	A.clear();
-	acc_rows<NT, SIDE, false>(A, xs, ys, ws, ts, 0, n, p, lane, sh, shy);
-	if (acc_poisoned<NT, SIDE>(A)) {
-		// some feature was NaN/Inf: redo with the full finite-row filter
-		f = find_first_valid<NT, SIDE, true>(xs, ys, ws, ts, n, p, lane);
+	if (!accumulate_group_fast<NT, SIDE, HASW, HAST>(A, sg, n, p, lane, sh, shy)) {
+		// a non-finite value (or no row passing the mask): the checked path of ols.rs:59-66
+		const int f = find_first_valid<NT, SIDE, true>(xs, ys, ws, ts, n, p, lane);
 		if (f < 0) {
 			store_empty_record(rec, p, lane, n_state);
 			return;
@@ -365,11 +520,12 @@ __device__ __forceinline__ void accumulate_group(const double *xs, const double 
 // ---------------------------------------------------------------------------------------------
 // Resident kernel: groups that fit a stage.
 // ---------------------------------------------------------------------------------------------
-template <int NT, bool SIDE, int NCW>
+template <int NT, bool SIDE, int NCW, bool HASW, bool HAST>
 __global__ void __launch_bounds__(32 * (NCW + 1), 1) acc_resident_kernel(const AccArgs a) {
 	extern __shared__ __align__(128) unsigned char smem[];
 	__shared__ uint64_t full_bar[8], empty_bar[8];
 	__shared__ StageHeader hdr[8];
+	__shared__ double kconst[2];
 	const int NS = a.n_stages;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	if (threadIdx.x == 0) {
@@ -378,6 +534,8 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) acc_resident_kernel(const A
 			mbar_init(&empty_bar[s], NCW);
 		}
 		mbar_fence_init();
+		kconst[0] = 1.0;
+		kconst[1] = 0.0;
 	}
 	__syncthreads();
 	const int p = a.p;
@@ -423,10 +581,10 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) acc_resident_kernel(const A
 				uint32_t tx = 0;
 				tx += stage_fetch<8>(base, (const unsigned char *)(a.x + row0 * p), rows * p * 8, lane, &full_bar[s], &lx);
 				tx += stage_fetch<8>(base + a.xcap, (const unsigned char *)(a.y + row0), rows * 8, lane, &full_bar[s], &ly);
-				if (a.w)
+				if (HASW)
 					tx += stage_fetch<8>(base + a.xcap + a.ycap, (const unsigned char *)(a.w + row0), rows * 8, lane,
 					                     &full_bar[s], &lw);
-				if (a.train)
+				if (HAST)
 					tx += stage_fetch<1>(base + a.xcap + a.ycap + a.wcap, a.train + row0, rows, lane, &full_bar[s], &lt);
 				if (lane == 0) {
 					hdr[s].rowstart[0] = 0;
@@ -466,14 +624,24 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) acc_resident_kernel(const A
 			unsigned char *base = smem + (size_t)s * a.stage_bytes;
 			const double *sx = (const double *)(base + hdr[s].lead_x);
 			const double *sy = (const double *)(base + a.xcap + hdr[s].lead_y);
-			const double *swp = a.w ? (const double *)(base + a.xcap + a.ycap + hdr[s].lead_w) : nullptr;
-			const uint8_t *st = a.train ? (const uint8_t *)(base + a.xcap + a.ycap + a.wcap + hdr[s].lead_t) : nullptr;
+			const double *swp = HASW ? (const double *)(base + a.xcap + a.ycap + hdr[s].lead_w) : nullptr;
+			const uint8_t *st = HAST ? (const uint8_t *)(base + a.xcap + a.ycap + a.wcap + hdr[s].lead_t) : nullptr;
 			const int64_t g0 = hdr[s].g_first;
-			for (int i = cw; i < cnt; i += NCW) {
+			SmemGroup sg;
+			sg.kone = smem_u32(&kconst[0]);
+			sg.kzero = smem_u32(&kconst[1]);
+			const uint32_t ax = smem_u32(sx), ay = smem_u32(sy), aw = HASW ? smem_u32(swp) : 0u, at = HAST ? smem_u32(st) : 0u;
+			// rotate the warp -> group assignment from stage to stage so that a stage holding fewer
+			// groups than there are consumer warps does not always idle the same warps
+			for (int i = (cw + it * 5) % NCW; i < cnt; i += NCW) {
 				const int rb = (int)hdr[s].rowstart[i];
 				const int n = (int)hdr[s].rowstart[i + 1] - rb;
-				accumulate_group<NT, SIDE>(sx + (int64_t)rb * p, sy + rb, swp ? swp + rb : nullptr, st ? st + rb : nullptr,
-				                           n, p, lane, a.records + (g0 + i) * L);
+				sg.x = ax + (uint32_t)rb * (uint32_t)p * 8u;
+				sg.y = ay + (uint32_t)rb * 8u;
+				sg.w = aw + (uint32_t)rb * 8u;
+				sg.t = at + (uint32_t)rb;
+				accumulate_group<NT, SIDE, HASW, HAST>(sg, sx + (int64_t)rb * p, sy + rb, HASW ? swp + rb : nullptr,
+				                                       HAST ? st + rb : nullptr, n, p, lane, a.records + (g0 + i) * L);
 			}
 			__syncwarp();
 			if (lane == 0) mbar_arrive(&empty_bar[s]);
@@ -484,7 +652,7 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) acc_resident_kernel(const A
 // ---------------------------------------------------------------------------------------------
 // Window bounds: tile_g0[t] = first group whose first row is >= t * window_rows.
 // ---------------------------------------------------------------------------------------------
-__global__ void tile_bounds_kernel(const int64_t *__restrict__ offsets, int64_t n_groups, int64_t window_rows,
+static __global__ void tile_bounds_kernel(const int64_t *__restrict__ offsets, int64_t n_groups, int64_t window_rows,
                                    int64_t n_tiles, int64_t *__restrict__ tile_g0) {
 	const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (t > n_tiles) return;
@@ -533,7 +701,7 @@ __device__ __forceinline__ bool row_valid_full(const StreamArgs &a, int64_t r) {
 	return ok;
 }
 
-__global__ void first_valid_kernel(const StreamArgs a) {
+static __global__ void first_valid_kernel(const StreamArgs a) {
 	const int b = blockIdx.x;
 	if (b >= *a.big_count) return;
 	const int lane = threadIdx.x;
@@ -600,7 +768,7 @@ template <int NT, bool SIDE, int NW> __global__ void __launch_bounds__(32 * NW) 
 
 // Sum the partial records of each big group in a fixed order: n, sw, n_state, S1, S2 add; cdev
 // takes the max; the shift is common to all partials.
-__global__ void reduce_partials_kernel(const StreamArgs a) {
+static __global__ void reduce_partials_kernel(const StreamArgs a) {
 	const int b = blockIdx.y;
 	const int nbig = a.offsets ? *a.big_count : 1;
 	if (b >= nbig) return;

@@ -67,12 +67,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 	    "{\n"
 	    " .reg .pred p;\n"
 	    "WAIT_%=:\n"
-	    " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+	    " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
 	    " @p bra DONE_%=;\n"
 	    " bra WAIT_%=;\n"
 	    "DONE_%=:\n"
 	    "}\n" ::"r"(smem_u32(bar)),
-	    "r"(parity)
+	    "r"(parity), "r"(20000u) // suspend-time hint (ns): sleep in hardware instead of spinning
 	    : "memory");
 }
 // One contiguous global -> shared bulk copy (SASS: UBLKCP). dst/src 16-byte aligned, bytes % 16 == 0.

@@ -17,6 +17,7 @@
 #include <mutex>
 #include <vector>
 
+#include "acc_launch.h"
 #include "accumulate.cuh"
 #include "common.cuh"
 #include "solve.cuh"
@@ -233,54 +234,42 @@ static Shape shape_of(int p) {
 	return {nt, side};
 }
 
-template <int NT, bool SIDE, int NCW> static cudaError_t launch_resident_t(const AccArgs &a, int grid, cudaStream_t st) {
-	auto kern = acc_resident_kernel<NT, SIDE, NCW>;
-	const size_t dyn = (size_t)a.n_stages * a.stage_bytes;
-	cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-	if (e != cudaSuccess) return e;
-	kern<<<grid, 32 * (NCW + 1), dyn, st>>>(a);
-	LAUNCHED();
-	return cudaGetLastError();
-}
-
 static cudaError_t launch_resident(const AccArgs &a, int grid, cudaStream_t st) {
 	const Shape s = shape_of(a.p);
-#define CASE(NT_, NCW_)                                                                                              \
-	case NT_:                                                                                                        \
-		return s.side ? launch_resident_t<NT_, true, NCW_>(a, grid, st) : launch_resident_t<NT_, false, NCW_>(a, grid, st);
+	const bool hw = a.w != nullptr, ht = a.train != nullptr;
+	cudaError_t e = cudaErrorInvalidValue;
 	switch (s.nt) {
-		CASE(1, 16)
-		CASE(2, 16)
-		CASE(3, 8)
-		CASE(4, 8)
-		CASE(5, 4)
-		CASE(6, 4)
-		CASE(7, 4)
-		CASE(8, 4)
-		CASE(9, 4)
+	case 1: e = launch_resident_nt1(s.side, hw, ht, a, grid, st); break;
+	case 2: e = launch_resident_nt2(s.side, hw, ht, a, grid, st); break;
+	case 3: e = launch_resident_nt3(s.side, hw, ht, a, grid, st); break;
+	case 4: e = launch_resident_nt4(s.side, hw, ht, a, grid, st); break;
+	case 5: e = launch_resident_nt5(s.side, hw, ht, a, grid, st); break;
+	case 6: e = launch_resident_nt6(s.side, hw, ht, a, grid, st); break;
+	case 7: e = launch_resident_nt7(s.side, hw, ht, a, grid, st); break;
+	case 8: e = launch_resident_nt8(s.side, hw, ht, a, grid, st); break;
+	case 9: e = launch_resident_nt9(s.side, hw, ht, a, grid, st); break;
 	}
-#undef CASE
-	return cudaErrorInvalidValue;
+	LAUNCHED();
+	return e;
 }
-
-constexpr int kStreamWarps = 8;
 
 // Big-group streaming: each warp owns an equal slice of every big group (partials = grid * warps).
-template <int NT, bool SIDE> static cudaError_t launch_stream_t(const StreamArgs &a, int grid, cudaStream_t st) {
-	acc_stream_kernel<NT, SIDE, kStreamWarps><<<grid, 32 * kStreamWarps, 0, st>>>(a);
-	LAUNCHED();
-	return cudaGetLastError();
-}
 static cudaError_t launch_stream(const StreamArgs &a, int grid, cudaStream_t st) {
 	const Shape s = shape_of(a.p);
-#define CASE(NT_)                                                                                                    \
-	case NT_:                                                                                                        \
-		return s.side ? launch_stream_t<NT_, true>(a, grid, st) : launch_stream_t<NT_, false>(a, grid, st);
+	cudaError_t e = cudaErrorInvalidValue;
 	switch (s.nt) {
-		CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8) CASE(9)
+	case 1: e = launch_stream_nt1(s.side, a, grid, st); break;
+	case 2: e = launch_stream_nt2(s.side, a, grid, st); break;
+	case 3: e = launch_stream_nt3(s.side, a, grid, st); break;
+	case 4: e = launch_stream_nt4(s.side, a, grid, st); break;
+	case 5: e = launch_stream_nt5(s.side, a, grid, st); break;
+	case 6: e = launch_stream_nt6(s.side, a, grid, st); break;
+	case 7: e = launch_stream_nt7(s.side, a, grid, st); break;
+	case 8: e = launch_stream_nt8(s.side, a, grid, st); break;
+	case 9: e = launch_stream_nt9(s.side, a, grid, st); break;
 	}
-#undef CASE
-	return cudaErrorInvalidValue;
+	LAUNCHED();
+	return e;
 }
 
 static cudaError_t launch_solve(const double *records, int64_t G, const FitParams &P, const AnofoxB200FitOutputs &o,
