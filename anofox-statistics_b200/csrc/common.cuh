@@ -38,7 +38,9 @@ struct FitParams {
 	int lambda_scaling;
 	double level;
 	double alpha;
-	const double *tcrit; // [kTcritTable + 1] device table for `level`, index = df
+	const double *tcrit;  // [kTcritTable + 1] t_{(1+level)/2, df}, index = df   (may be null: evaluate directly)
+	const double *gratio; // [kTcritTable + 1] Gamma((df+1)/2) / Gamma(df/2)
+	const double *rcp;    // [kRcpTable + 1]  1 / m
 	int predict_mode;    // 1: df for t-critical follows anofox_predict_with_interval
 	int min_state_rows;  // 2 = aggregate rule (ols_aggregate.cpp:263-267); 0 = direct anofox_*_fit call
 };

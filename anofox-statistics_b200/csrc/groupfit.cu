@@ -57,12 +57,6 @@ static cudaEvent_t timer_mark(cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------
 // Small kernels
 // ---------------------------------------------------------------------------------------------
-__global__ void tcrit_table_kernel(double level, double *__restrict__ table) {
-	const int df = blockIdx.x * blockDim.x + threadIdx.x;
-	if (df > kTcritTable) return;
-	table[df] = df == 0 ? nan_f64() : t_critical_dev(level, (double)df);
-}
-
 template <int PMAX>
 __global__ void __launch_bounds__(128) solve_kernel(const double *__restrict__ records, int64_t n_groups, FitParams P,
                                                     AnofoxB200FitOutputs o, int *refine_count, int64_t *refine_list) {
@@ -118,15 +112,21 @@ __global__ void __launch_bounds__(256) refine_kernel(RefineArgs a, FitParams P, 
 }
 
 // mode 0: two-sided t p-value (a = t, b = df); 1: t critical (a = level, b = df); 2: F upper tail (a = f, b = d1, c = d2)
-__global__ void specfun_eval_kernel(int mode, int n, const double *a, const double *b, const double *c, double *out) {
+// 3 / 4: the table-driven fast paths the solve kernel uses.
+__global__ void specfun_eval_kernel(int mode, int n, const double *a, const double *b, const double *c, double *out,
+                                    DfTables T) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
 	if (mode == 0)
 		out[i] = t_two_sided_p(a[i], b[i]);
 	else if (mode == 1)
 		out[i] = t_critical_dev(a[i], b[i]);
-	else
+	else if (mode == 2)
 		out[i] = f_upper_p(a[i], b[i], c[i]);
+	else if (mode == 3)
+		out[i] = t_two_sided_p_fast(a[i], b[i], T);
+	else
+		out[i] = f_upper_p_fast(a[i], b[i], c[i], T);
 }
 
 // Default training rule of ols_predict_aggregate.cpp:216-239 when the caller passes no flags:
@@ -375,6 +375,86 @@ static StageGeom stage_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	return g;
 }
 
+static void set_error(AnofoxError *err, int code, const char *msg) {
+	if (!err) return;
+	err->code = (AnofoxErrorCode)code;
+	strncpy(err->message, msg ? msg : "", 255);
+	err->message[255] = 0;
+}
+static void clear_error(AnofoxError *err) {
+	if (!err) return;
+	err->code = ANOFOX_ERROR_SUCCESS;
+	memset(err->message, 0, sizeof err->message);
+}
+static int cuda_fail(AnofoxError *err, cudaError_t e, const char *where) {
+	char buf[256];
+	snprintf(buf, sizeof buf, "CUDA error in %s: %s", where, cudaGetErrorString(e));
+	set_error(err, ANOFOX_ERROR_INTERNAL, buf);
+	return ANOFOX_ERROR_INTERNAL;
+}
+#define CU(call, where)                                                                                              \
+	do {                                                                                                             \
+		cudaError_t e__ = (call);                                                                                    \
+		if (e__ != cudaSuccess) return cuda_fail(err, e__, where);                                                   \
+	} while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Per-(device, confidence level) distribution tables, built once and kept for the process lifetime.
+// ---------------------------------------------------------------------------------------------
+struct TableEntry {
+	int device;
+	double level;
+	double *buf; // [tcrit | gratio | rcp]
+	cudaEvent_t ready;
+};
+struct TableCache {
+	std::mutex mu;
+	std::vector<TableEntry> entries;
+};
+static TableCache &table_cache() {
+	static TableCache c;
+	return c;
+}
+// Returns the tables for `level` on the current device; work on `st` is ordered after their fill.
+static int get_tables(double level, cudaStream_t st, DfTables &T, AnofoxError *err) {
+	TableCache &c = table_cache();
+	std::lock_guard<std::mutex> lock(c.mu);
+	int dev = 0;
+	cudaGetDevice(&dev);
+	const size_t n1 = kTcritTable + 1, n3 = kRcpTable + 1;
+	for (auto &e : c.entries)
+		if (e.device == dev && (e.level == level || (std::isnan(e.level) && std::isnan(level)))) {
+			CU(cudaStreamWaitEvent(st, e.ready, 0), "cudaStreamWaitEvent");
+			T.tcrit = e.buf;
+			T.gratio = e.buf + n1;
+			T.rcp = e.buf + 2 * n1;
+			return 0;
+		}
+	if (c.entries.size() >= 64) { // unbounded growth guard: drop everything (after the device drains)
+		cudaDeviceSynchronize();
+		for (auto &e : c.entries) {
+			cudaFree(e.buf);
+			cudaEventDestroy(e.ready);
+		}
+		c.entries.clear();
+	}
+	TableEntry e;
+	e.device = dev;
+	e.level = level;
+	e.buf = nullptr;
+	CU(cudaMalloc(&e.buf, (2 * n1 + n3) * sizeof(double)), "cudaMalloc tables");
+	CU(cudaEventCreateWithFlags(&e.ready, cudaEventDisableTiming), "cudaEventCreate");
+	df_tables_kernel<<<(unsigned)((n3 + 127) / 128), 128, 0, st>>>(level, e.buf, e.buf + n1, e.buf + 2 * n1);
+	LAUNCHED();
+	CU(cudaGetLastError(), "df_tables_kernel");
+	CU(cudaEventRecord(e.ready, st), "cudaEventRecord");
+	c.entries.push_back(e);
+	T.tcrit = e.buf;
+	T.gratio = e.buf + n1;
+	T.rcp = e.buf + 2 * n1;
+	return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Workspace carving
 // ---------------------------------------------------------------------------------------------
@@ -383,7 +463,6 @@ struct Workspace {
 	int64_t *tile_g0;
 	int64_t *big_list;
 	int *big_count;
-	double *tcrit;
 	double *shift;
 	int *first_ok;
 	double *partials;
@@ -417,7 +496,6 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 	w.tile_g0 = (int64_t *)take((size_t)(n_tiles + 2) * 8);
 	w.big_list = (int64_t *)take((size_t)(w.nbig_max + 1) * 8);
 	w.big_count = (int *)take(256);
-	w.tcrit = (double *)take((size_t)(kTcritTable + 1) * 8);
 	w.shift = (double *)take((size_t)(w.nbig_max + 1) * (p + 1) * 8);
 	w.first_ok = (int *)take((size_t)(w.nbig_max + 1) * 4);
 	// partial records of the streaming path: one per (big group, warp). Bounded by capping how many
@@ -437,29 +515,6 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 	w.bytes = off;
 	return off;
 }
-
-static void set_error(AnofoxError *err, int code, const char *msg) {
-	if (!err) return;
-	err->code = (AnofoxErrorCode)code;
-	strncpy(err->message, msg ? msg : "", 255);
-	err->message[255] = 0;
-}
-static void clear_error(AnofoxError *err) {
-	if (!err) return;
-	err->code = ANOFOX_ERROR_SUCCESS;
-	memset(err->message, 0, sizeof err->message);
-}
-static int cuda_fail(AnofoxError *err, cudaError_t e, const char *where) {
-	char buf[256];
-	snprintf(buf, sizeof buf, "CUDA error in %s: %s", where, cudaGetErrorString(e));
-	set_error(err, ANOFOX_ERROR_INTERNAL, buf);
-	return ANOFOX_ERROR_INTERNAL;
-}
-#define CU(call, where)                                                                                              \
-	do {                                                                                                             \
-		cudaError_t e__ = (call);                                                                                    \
-		if (e__ != cudaSuccess) return cuda_fail(err, e__, where);                                                   \
-	} while (0)
 
 static int validate_common(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w,
                            int64_t N, int p, const AnofoxB200FitOptions *opt, AnofoxError *err) {
@@ -524,14 +579,17 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	P.lambda_scaling = opt->lambda_scaling;
 	P.level = opt->confidence_level;
 	P.alpha = opt->alpha;
-	P.tcrit = ws.tcrit;
+	P.tcrit = P.gratio = P.rcp = nullptr;
 	P.predict_mode = pred ? 1 : 0;
 	P.min_state_rows = min_state_rows;
 
 	if (P.compute_inference || pred) {
-		tcrit_table_kernel<<<(kTcritTable + 1 + 127) / 128, 128, 0, st>>>(P.level, ws.tcrit);
-		LAUNCHED();
-		CU(cudaGetLastError(), "tcrit_table_kernel");
+		DfTables T;
+		const int trc = get_tables(P.level, st, T, err);
+		if (trc) return trc;
+		P.tcrit = T.tcrit;
+		P.gratio = T.gratio;
+		P.rcp = T.rcp;
 	}
 
 	const uint8_t *train_use = nullptr;
@@ -968,7 +1026,12 @@ static int eval_specfun_host(int mode, int n, const double *a, const double *b, 
 	CU(cudaMemcpyAsync(da, a, bytes, cudaMemcpyHostToDevice, st), "H2D");
 	CU(cudaMemcpyAsync(db, b, bytes, cudaMemcpyHostToDevice, st), "H2D");
 	if (c) CU(cudaMemcpyAsync(dc, c, bytes, cudaMemcpyHostToDevice, st), "H2D");
-	specfun_eval_kernel<<<(n + 127) / 128, 128, 0, st>>>(mode, n, da, db, dc, dout);
+	DfTables T{nullptr, nullptr, nullptr};
+	if (mode >= 3) {
+		rc = get_tables(0.95, st, T, err);
+		if (rc) return rc;
+	}
+	specfun_eval_kernel<<<(n + 127) / 128, 128, 0, st>>>(mode, n, da, db, dc, dout, T);
 	LAUNCHED();
 	CU(cudaGetLastError(), "specfun_eval_kernel");
 	CU(cudaMemcpyAsync(out, dout, bytes, cudaMemcpyDeviceToHost, st), "D2H");
@@ -1240,7 +1303,7 @@ int32_t anofox_b200_solve_moments_device(const double *moments, const double *cd
 	P.lambda_scaling = options->lambda_scaling;
 	P.level = options->confidence_level;
 	P.alpha = options->alpha;
-	P.tcrit = nullptr; // one group: evaluate the quantile directly
+	P.tcrit = P.gratio = P.rcp = nullptr; // one group: evaluate the distribution functions directly
 	P.predict_mode = 0;
 	P.min_state_rows = 2;
 	CU(launch_solve(rec, 1, P, *out, nullptr, nullptr, st), "solve_kernel");

@@ -289,6 +289,7 @@ __device__ void solve_group(const double *__restrict__ rec, int64_t rs, int64_t 
 
 	if (inf_arrays) {
 		if (o.has_inference) o.has_inference[g] = 1;
+		const DfTables T{P.tcrit, P.gratio, P.rcp};
 		double tcrit = nanv;
 		if (dfr > 0.0) {
 			int idf = (int)dfr;
@@ -315,14 +316,14 @@ __device__ void solve_group(const double *__restrict__ rec, int64_t rs, int64_t 
 			int64_t oj = g * p + idx[j];
 			o.std_errors[oj] = se;
 			o.t_values[oj] = t;
-			o.p_values[oj] = dfr > 0.0 ? t_two_sided_p(t, dfr) : nanv;
+			o.p_values[oj] = dfr > 0.0 ? t_two_sided_p_fast(t, dfr, T) : nanv;
 			o.ci_lower[oj] = b[j] - tcrit * se;
 			o.ci_upper[oj] = b[j] + tcrit * se;
 		}
 		if (dfm > 0.0 && dfr > 0.0) {
 			double f = ((tss - rss) / dfm) / sigma2;
 			o.f_statistic[g] = f;
-			o.f_pvalue[g] = f_upper_p(f, dfm, dfr);
+			o.f_pvalue[g] = f_upper_p_fast(f, dfm, dfr, T);
 		}
 	}
 }

@@ -123,4 +123,123 @@ __device__ inline double t_critical_dev(double level, double df) {
 	return t;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fast paths for INTEGER degrees of freedom (every p-value of a fit has df = n - rank).
+// Three per-df tables are built once per confidence level (df_tables_kernel, cached by the host):
+//   tcrit[df]  = t_{(1+level)/2, df}
+//   gratio[df] = Gamma((df+1)/2) / Gamma(df/2)
+//   rcp[m]     = 1 / m
+// With them I_x(df/2, 1/2) is either the classical finite trigonometric sum for the t CDF
+// (Abramowitz & Stegun 26.7.3-4: df/2 terms, used for the body of the distribution) or the
+// hypergeometric tail series x^a (1-x)^b / (a B(a,b)) * sum_n (a+b)_n / (a+1)_n x^n (relative
+// accuracy in the far tail, geometric convergence with ratio x). Every term costs one table load
+// and three multiply-adds instead of the ~6 divisions of a continued-fraction step.
+// ---------------------------------------------------------------------------------------------
+constexpr int kRcpTable = 2 * kTcritTable + 1024;
+
+struct DfTables {
+	const double *tcrit;
+	const double *gratio;
+	const double *rcp;
+};
+
+__device__ inline double betai_half_tail_series(int nu, double x, double y, const DfTables &T) {
+	const double a = 0.5 * (double)nu;
+	const double pref = exp(a * log(x)) * sqrt(y) * T.gratio[nu] * (0.56418958354775628695 / a); // 1/sqrt(pi)
+	double u = 1.0, sum = 1.0;
+	int idx = nu + 2;
+	for (int n = 0; n < 500; ++n) {
+		u *= x * (1.0 - T.rcp[idx]);
+		idx += 2;
+		sum += u;
+		if (u < 1e-17 * sum) break;
+	}
+	return pref * sum;
+}
+
+// I_x(nu/2, 1/2) = P(|T_nu| > t) with x = nu / (nu + t^2), y = 1 - x, nu integer in [1, kTcritTable].
+__device__ inline double betai_half_fast(int nu, double x, double y, const DfTables &T) {
+	if (!(x > 0.0)) return 0.0;
+	if (!(y > 0.0)) return 1.0;
+	if (x <= 0.6) return betai_half_tail_series(nu, x, y, T);
+	if (nu <= 400) {
+		const double s = sqrt(y), c = sqrt(x);
+		double p;
+		if (nu & 1) {
+			double o = 1.0, sum = nu > 1 ? 1.0 : 0.0;
+			const int jmax = (nu - 3) / 2;
+			for (int j = 1; j <= jmax; ++j) {
+				o *= x * (1.0 - T.rcp[2 * j + 1]);
+				sum += o;
+			}
+			p = 0.63661977236758134308 * (atan2(c, s) - s * c * sum); // 2/pi
+		} else {
+			double e = 1.0, sum = 1.0;
+			const int jmax = nu / 2 - 1;
+			for (int j = 1; j <= jmax; ++j) {
+				e *= x * (1.0 - T.rcp[2 * j]);
+				sum += e;
+			}
+			p = 1.0 - s * sum;
+		}
+		if (p > 1e-4) return p; // 1 - A (df/2 rounded terms) keeps >= 11 digits
+	}
+	if (x <= 0.85) return betai_half_tail_series(nu, x, y, T);
+	return beta_inc(0.5 * (double)nu, 0.5, x, y);
+}
+
+__device__ inline double t_two_sided_p_fast(double t, double df, const DfTables &T) {
+	if (isnan(t) || !(df > 0.0)) return nan_f64();
+	if (isinf(t)) return 0.0;
+	const double t2 = t * t, den = df + t2;
+	if (T.rcp == nullptr || df > (double)kTcritTable || df != floor(df)) return beta_inc(0.5 * df, 0.5, df / den, t2 / den);
+	return betai_half_fast((int)df, df / den, t2 / den, T);
+}
+
+// Upper tail of F(d1, d2), integer d1 >= 1 and d2 in [1, kTcritTable]:
+// I_x(a, b) built up from b = 1/2 (or 1) with the recurrence I_x(a, b+1) = I_x(a, b) + T_b,
+// T_b = x^a y^b Gamma(a+b) / (Gamma(a) Gamma(b+1)) -- all terms positive, no cancellation.
+__device__ inline double f_upper_p_fast(double f, double d1, double d2, const DfTables &T) {
+	if (isnan(f) || !(d1 > 0.0) || !(d2 > 0.0)) return nan_f64();
+	if (f <= 0.0) return 1.0;
+	if (isinf(f)) return 0.0;
+	const double den = d2 + d1 * f;
+	const double x = d2 / den, y = d1 * f / den;
+	if (T.rcp == nullptr || d2 > (double)kTcritTable || d2 != floor(d2) || d1 != floor(d1) || d1 > 1024.0)
+		return beta_inc(0.5 * d2, 0.5 * d1, x, y);
+	const int nu = (int)d2, m = (int)d1;
+	const double a = 0.5 * d2;
+	const double xa = exp(a * log(x));
+	double acc, term;
+	int twob; // 2b of the term about to be added
+	if (m & 1) {
+		acc = betai_half_fast(nu, x, y, T);
+		term = xa * sqrt(y) * T.gratio[nu] * 1.12837916709551257390; // 2/sqrt(pi): T_{1/2}
+		twob = 1;
+	} else {
+		acc = xa;
+		term = xa * y * a; // T_1
+		twob = 2;
+	}
+	while (twob < m) {
+		acc += term;
+		// T_{b+1} = T_b * y * (a+b)/(b+1),  (a+b)/(b+1) = (nu + 2b) / (2b + 2)
+		term *= y * (double)(nu + twob) * T.rcp[twob + 2];
+		twob += 2;
+	}
+	return fmin(acc, 1.0);
+}
+
+// One thread per table entry.
+static __global__ void df_tables_kernel(double level, double *__restrict__ tcrit, double *__restrict__ gratio,
+                                 double *__restrict__ rcp) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i <= kRcpTable) rcp[i] = i > 0 ? 1.0 / (double)i : 0.0;
+	if (i <= kTcritTable) {
+		tcrit[i] = i == 0 ? nan_f64() : t_critical_dev(level, (double)i);
+		// Gamma((df+1)/2) / Gamma(df/2) = sqrt(pi) / B(df/2, 1/2)
+		gratio[i] = i == 0 ? 0.0 : 1.7724538509055160273 * exp(-lbeta_dev(0.5 * (double)i, 0.5));
+	}
+}
+
 } // namespace b200

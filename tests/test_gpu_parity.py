@@ -130,6 +130,31 @@ def test_device_special_functions(lib, oracle):
     want = np.array([oracle.f_upper_p(f, a, b) for f, a, b in zip(fs, d1, d2)])
     rel = np.abs(got - want) / np.maximum(want, 1e-300)
     assert rel.max() < 1e-10, rel.max()
+    # table-driven fast paths used by the solve kernel (integer df): body sum, tail series, CF fallback
+    ts, dfs = [], []
+    for df in list(range(1, 41)) + [44, 45, 98, 99, 146, 183, 200, 399, 400, 401, 991, 4096, 4097, 100000]:
+        for t in np.concatenate([rng.uniform(0, 9, 30), [1e-9, 1e-4, 0.05, 12.0, 30.0, 80.0, 500.0, 1e5]]):
+            ts.append(t)
+            dfs.append(df)
+    got = lib.eval_specfun(3, ts, dfs)
+    want = np.array([oracle.t_two_sided_p(t, d) for t, d in zip(ts, dfs)])
+    ok = want > 1e-290
+    rel = np.abs(got[ok] - want[ok]) / want[ok]
+    assert rel.max() < 2e-10, (rel.max(), np.array(ts)[ok][int(rel.argmax())], np.array(dfs)[ok][int(rel.argmax())])
+    assert (got[~ok] < 1e-280).all()
+    fs, d1, d2 = [], [], []
+    for a in [1, 2, 3, 4, 5, 7, 8, 16, 17, 32, 63, 64]:
+        for b in [1, 2, 3, 5, 10, 44, 45, 146, 183, 991, 4096, 5000]:
+            for f in [1e-4, 0.2, 1.0, 2.5, 9.0, 40.0, 300.0, 1e4, 1e7]:
+                fs.append(f)
+                d1.append(a)
+                d2.append(b)
+    got = lib.eval_specfun(4, fs, d1, d2)
+    want = np.array([oracle.f_upper_p(f, a, b) for f, a, b in zip(fs, d1, d2)])
+    ok = want > 1e-290
+    rel = np.abs(got[ok] - want[ok]) / want[ok]
+    i = int(rel.argmax())
+    assert rel.max() < 2e-10, (rel.max(), np.array(fs)[ok][i], np.array(d1)[ok][i], np.array(d2)[ok][i])
     # drop-in scalar symbols
     assert math.isnan(lib.t_critical(0.95, 0)) and math.isnan(lib.t_critical(1.0, 3))
     assert abs(lib.t_critical(0.95, 98) - oracle.t_critical(0.95, 98)) < 1e-12
