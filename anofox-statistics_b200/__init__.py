@@ -21,7 +21,7 @@ HEADER_SYMBOLS = [
     "anofox_free_result_inference", "anofox_t_critical", "anofox_predict_with_interval", "anofox_compute_aic",
     "anofox_compute_bic", "anofox_b200_workspace_bytes", "anofox_b200_fit_batch_device",
     "anofox_b200_fit_batch_host", "anofox_b200_fit_predict_batch_device", "anofox_b200_fit_predict_batch_host",
-    "anofox_b200_moment_block_len", "anofox_b200_moments_device", "anofox_b200_solve_moments_device",
+    "anofox_b200_moment_block_len", "anofox_b200_first_valid_row_device", "anofox_b200_moments_device", "anofox_b200_solve_moments_device",
     "anofox_b200_device_check", "anofox_b200_launch_count", "anofox_b200_version",
 ]
 
@@ -70,6 +70,9 @@ def load_library():
                                                                 C.POINTER(abi.B200FitOutputs), E]
     lib.anofox_b200_moment_block_len.restype = C.c_size_t
     lib.anofox_b200_moment_block_len.argtypes = [C.c_int32]
+    lib.anofox_b200_first_valid_row_device.restype = C.c_int32
+    lib.anofox_b200_first_valid_row_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
+                                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, E]
     lib.anofox_b200_moments_device.restype = C.c_int32
     lib.anofox_b200_moments_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, E]
@@ -88,6 +91,10 @@ def load_library():
     lib.anofox_b200_stage_timing_enable.argtypes = [C.c_int32]
     lib.anofox_b200_stage_timing_read.restype = C.c_int64
     lib.anofox_b200_stage_timing_read.argtypes = [abi.c_double_p, abi.c_double_p]
+    lib.anofox_b200_force_path.restype = None
+    lib.anofox_b200_force_path.argtypes = [C.c_int32]
+    lib.anofox_b200_plan.restype = C.c_int32
+    lib.anofox_b200_plan.argtypes = [C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, abi.c_int32_p]
     _LIB = lib
     return lib
 
@@ -277,6 +284,18 @@ def fit_batch_host_into(offsets, y, x, w, out_struct, G, N, p, **opt):
                                         cast(x, abi.c_double_p), cast(w, abi.c_double_p), N, p, C.byref(o),
                                         C.byref(out_struct), C.byref(err))
     _check(rc, err)
+
+
+def force_path(path):
+    """Test / A-B hook: "auto" or "record" (always the DMMA accumulation kernel + solve kernel)."""
+    load_library().anofox_b200_force_path({"auto": 0, "record": 1}[path])
+
+
+def plan(G, N, p, has_w=False, has_train=False):
+    """("fused", lanes_per_group) or ("record", 0): the kernel path a batch of this shape takes."""
+    t = C.c_int32(0)
+    r = load_library().anofox_b200_plan(G, N, p, int(has_w), int(has_train), C.byref(t))
+    return ("fused" if r == 1 else "record"), int(t.value)
 
 
 def moment_block_len(p):

@@ -48,12 +48,14 @@ struct AccArgs {
 	int n_stages;
 };
 
-struct StageHeader {
+template <int MAXG> struct StageHeaderT {
 	int64_t g_first;
 	int count; // groups in the stage; -1 = producer finished
+	int next;  // fused kernel: next unclaimed round of the stage (reset by the producer)
 	int lead_x, lead_y, lead_w, lead_t; // byte offset of element 0 inside each region
-	uint32_t rowstart[kMaxStageGroups + 1];
+	uint32_t rowstart[MAXG + 1];
 };
+using StageHeader = StageHeaderT<kMaxStageGroups>;
 
 // Copy `bytes` bytes from global `src` into the shared region `dst` (16-byte aligned) so that
 // byte e lands at dst + lead + e, lead = src & 15. The 16-byte aligned interior goes through one
@@ -518,6 +520,90 @@ __device__ __forceinline__ void accumulate_group(const SmemGroup &sg, const doub
 }
 
 // ---------------------------------------------------------------------------------------------
+// Producer warp (shared by the resident DMMA kernel and the fused small-group kernel): walks this
+// CTA's row windows, packs consecutive whole groups into a stage (at most max_groups of them, at most
+// cap_rows rows) and fetches their rows with one bulk copy per array. Groups larger than a stage go
+// to big_list. Ends with a stage whose count is -1.
+// ---------------------------------------------------------------------------------------------
+template <bool HASW, bool HAST, class Hdr>
+__device__ __forceinline__ void producer_loop(const AccArgs &a, unsigned char *smem, uint64_t *full_bar,
+                                              uint64_t *empty_bar, Hdr *hdr, int NS, int lane, int max_groups) {
+	const int p = a.p;
+	int it = 0;
+	for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+		int64_t g = a.tile_g0[t];
+		const int64_t gend = a.tile_g0[t + 1];
+		while (g < gend) {
+			const int s = it % NS;
+			const uint32_t ph = (uint32_t)((it / NS) & 1);
+			mbar_wait(&empty_bar[s], ph ^ 1u);
+			const int64_t row0 = a.offsets[g];
+			int cnt = 0;
+			int64_t row_end = row0;
+			bool closed = false;
+			while (!closed && g + cnt < gend && cnt < max_groups) {
+				const int64_t gi = g + cnt + lane;
+				const bool in = gi < gend && (cnt + lane) < max_groups;
+				const int64_t oe = in ? a.offsets[gi + 1] : row0;
+				const bool fits = in && (oe - row0) <= (int64_t)a.cap_rows;
+				const unsigned m = __ballot_sync(0xffffffffu, fits);
+				const int nfit = (m == 0xffffffffu) ? 32 : (__ffs(~m) - 1);
+				if (lane < nfit) hdr[s].rowstart[cnt + lane + 1] = (uint32_t)(oe - row0);
+				if (nfit > 0) row_end = __shfl_sync(0xffffffffu, oe, nfit - 1);
+				cnt += nfit;
+				if (nfit < 32) closed = true;
+			}
+			if (cnt == 0) {
+				// group g alone exceeds a stage: hand it to the streaming kernel
+				if (lane == 0) {
+					const int slot = atomicAdd(a.big_count, 1);
+					a.big_list[slot] = g;
+				}
+				g += 1;
+				continue;
+			}
+			const int64_t rows = row_end - row0;
+			unsigned char *base = smem + (size_t)s * a.stage_bytes;
+			int lx = 0, ly = 0, lw = 0, lt = 0;
+			uint32_t tx = 0;
+			tx += stage_fetch<8>(base, (const unsigned char *)(a.x + row0 * p), rows * p * 8, lane, &full_bar[s], &lx);
+			tx += stage_fetch<8>(base + a.xcap, (const unsigned char *)(a.y + row0), rows * 8, lane, &full_bar[s], &ly);
+			if (HASW)
+				tx += stage_fetch<8>(base + a.xcap + a.ycap, (const unsigned char *)(a.w + row0), rows * 8, lane,
+				                     &full_bar[s], &lw);
+			if (HAST)
+				tx += stage_fetch<1>(base + a.xcap + a.ycap + a.wcap, a.train + row0, rows, lane, &full_bar[s], &lt);
+			if (lane == 0) {
+				hdr[s].rowstart[0] = 0;
+				hdr[s].g_first = g;
+				hdr[s].count = cnt;
+				hdr[s].next = 0;
+				hdr[s].lead_x = lx;
+				hdr[s].lead_y = ly;
+				hdr[s].lead_w = lw;
+				hdr[s].lead_t = lt;
+			}
+			__syncwarp();
+			if (lane == 0) {
+				if (tx)
+					mbar_arrive_expect_tx(&full_bar[s], tx);
+				else
+					mbar_arrive(&full_bar[s]);
+			}
+			g += cnt;
+			++it;
+		}
+	}
+	// end marker
+	const int s = it % NS;
+	mbar_wait(&empty_bar[s], (uint32_t)(((it / NS) & 1) ^ 1));
+	if (lane == 0) {
+		hdr[s].count = -1;
+		mbar_arrive(&full_bar[s]);
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
 // Resident kernel: groups that fit a stage.
 // ---------------------------------------------------------------------------------------------
 template <int NT, bool SIDE, int NCW, bool HASW, bool HAST>
@@ -541,78 +627,7 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) acc_resident_kernel(const A
 	const int p = a.p;
 	const int L = rec_len(p);
 	if (warp == 0) {
-		// ------------------------------ producer ------------------------------
-		int it = 0;
-		for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
-			int64_t g = a.tile_g0[t];
-			const int64_t gend = a.tile_g0[t + 1];
-			while (g < gend) {
-				const int s = it % NS;
-				const uint32_t ph = (uint32_t)((it / NS) & 1);
-				mbar_wait(&empty_bar[s], ph ^ 1u);
-				const int64_t row0 = a.offsets[g];
-				int cnt = 0;
-				int64_t row_end = row0;
-				bool closed = false;
-				while (!closed && g + cnt < gend && cnt < kMaxStageGroups) {
-					const int64_t gi = g + cnt + lane;
-					const bool in = gi < gend && (cnt + lane) < kMaxStageGroups;
-					const int64_t oe = in ? a.offsets[gi + 1] : row0;
-					const bool fits = in && (oe - row0) <= (int64_t)a.cap_rows;
-					const unsigned m = __ballot_sync(0xffffffffu, fits);
-					const int nfit = (m == 0xffffffffu) ? 32 : (__ffs(~m) - 1);
-					if (lane < nfit) hdr[s].rowstart[cnt + lane + 1] = (uint32_t)(oe - row0);
-					if (nfit > 0) row_end = __shfl_sync(0xffffffffu, oe, nfit - 1);
-					cnt += nfit;
-					if (nfit < 32) closed = true;
-				}
-				if (cnt == 0) {
-					// group g alone exceeds a stage: hand it to the streaming kernel
-					if (lane == 0) {
-						const int slot = atomicAdd(a.big_count, 1);
-						a.big_list[slot] = g;
-					}
-					g += 1;
-					continue;
-				}
-				const int64_t rows = row_end - row0;
-				unsigned char *base = smem + (size_t)s * a.stage_bytes;
-				int lx = 0, ly = 0, lw = 0, lt = 0;
-				uint32_t tx = 0;
-				tx += stage_fetch<8>(base, (const unsigned char *)(a.x + row0 * p), rows * p * 8, lane, &full_bar[s], &lx);
-				tx += stage_fetch<8>(base + a.xcap, (const unsigned char *)(a.y + row0), rows * 8, lane, &full_bar[s], &ly);
-				if (HASW)
-					tx += stage_fetch<8>(base + a.xcap + a.ycap, (const unsigned char *)(a.w + row0), rows * 8, lane,
-					                     &full_bar[s], &lw);
-				if (HAST)
-					tx += stage_fetch<1>(base + a.xcap + a.ycap + a.wcap, a.train + row0, rows, lane, &full_bar[s], &lt);
-				if (lane == 0) {
-					hdr[s].rowstart[0] = 0;
-					hdr[s].g_first = g;
-					hdr[s].count = cnt;
-					hdr[s].lead_x = lx;
-					hdr[s].lead_y = ly;
-					hdr[s].lead_w = lw;
-					hdr[s].lead_t = lt;
-				}
-				__syncwarp();
-				if (lane == 0) {
-					if (tx)
-						mbar_arrive_expect_tx(&full_bar[s], tx);
-					else
-						mbar_arrive(&full_bar[s]);
-				}
-				g += cnt;
-				++it;
-			}
-		}
-		// end marker
-		const int s = it % NS;
-		mbar_wait(&empty_bar[s], (uint32_t)(((it / NS) & 1) ^ 1));
-		if (lane == 0) {
-			hdr[s].count = -1;
-			mbar_arrive(&full_bar[s]);
-		}
+		producer_loop<HASW, HAST>(a, smem, full_bar, empty_bar, hdr, NS, lane, kMaxStageGroups);
 	} else {
 		// ------------------------------ consumers -----------------------------
 		const int cw = warp - 1;

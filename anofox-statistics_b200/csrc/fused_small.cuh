@@ -1,0 +1,611 @@
+// fused_small.cuh -- ONE kernel for many small groups with few features (p <= 8): rows -> results.
+//
+// Covers, for the groups that fit a shared-memory stage, the whole reference path
+//   *AggUpdate / *AggCombine / *AggFinalize   src/aggregate_functions/ols_aggregate.cpp:120-338
+//   anofox_{ols,ridge,wls}_fit                crates/anofox-stats-ffi/src/lib.rs:98-265, :984, :1384
+//   fit_ols / fit_ridge / fit_wls             crates/anofox-stats-core/src/models/{ols,ridge,wls}.rs
+//   (+ the external regressor's statistics and compute_aic / compute_bic)
+// without ever writing a per-group record to HBM: each input row is read from HBM once (TMA bulk
+// copy into a shared-memory stage, producer_loop in accumulate.cuh) and only the result struct is
+// written back.
+//
+// Work mapping. A group is owned by T consecutive lanes of a warp (T = 4, 8, 16 or 32, chosen by the
+// host from the mean group size so that enough groups are resident per SM). Lane q of the T takes
+// rows q, q+T, ... and keeps the full upper triangle of sum w d d^T (d = row - first valid row) in
+// registers -- plain DFMA, every lane busy, no per-group prologue at warp granularity -- then a
+// log2(T)-step butterfly leaves the sums in all T lanes. The T lanes run the tiny Cholesky solve
+// redundantly (it is the same instruction stream) and split the per-coefficient distribution
+// functions (the expensive part: t p-values) between them. Rows are still in shared memory at that
+// point, so the exact residual pass that the moment form needs for (nearly) exact fits happens in
+// place instead of through a refinement queue.
+//
+// Rounds of 32/T groups are claimed dynamically from the stage by the consumer warps.
+#pragma once
+#include "accumulate.cuh"
+#include "solve.cuh"
+
+namespace b200 {
+
+template <int P> struct SmallMoments {
+	static constexpr int K = P + 1;
+	static constexpr int NS2 = K * (K + 1) / 2;
+	double s2[NS2]; // sum w d d^T, upper triangle row-major (i <= j), index K-1 = y
+	double s1[K];   // sum w d
+	double sw;      // sum w over valid rows (weighted fits only; otherwise nv)
+	double q2[P];   // unweighted sum d^2 per feature (weighted fits only; otherwise the diagonal of s2)
+	int nv;         // valid rows
+	int ns;         // rows that entered the aggregate state (training flag set)
+	__device__ __forceinline__ void clear() {
+#pragma unroll
+		for (int i = 0; i < NS2; ++i) s2[i] = 0.0;
+#pragma unroll
+		for (int i = 0; i < K; ++i) s1[i] = 0.0;
+#pragma unroll
+		for (int i = 0; i < P; ++i) q2[i] = 0.0;
+		sw = 0.0;
+		nv = ns = 0;
+	}
+};
+
+__host__ __device__ constexpr int utri(int i, int j, int k) { return i * k - (i * (i - 1)) / 2 + (j - i); } // i <= j
+__host__ __device__ constexpr int ltri(int i, int j) { return (i * (i + 1)) / 2 + j; }                       // j <= i
+
+__device__ __forceinline__ double shfl_xor_f64(unsigned mask, double v, int off) {
+	return __shfl_xor_sync(mask, v, off);
+}
+
+// Rows q, q+T, ... of one group (shared-memory addresses in sg) folded into M.
+//   CHECK = false: fast path. Rows are masked only by w > 0 / the training flag; non-finite values
+//                  poison the sums and the caller re-runs with CHECK = true.
+//   CHECK = true : the full row filter of ols.rs:59-66 / wls.rs:76-86.
+template <int P, bool HASW, bool HAST, bool CHECK>
+__device__ __forceinline__ void small_accumulate(SmallMoments<P> &M, const SmemGroup &sg, int n, int q, int T,
+                                                 const double (&sh)[P + 1]) {
+	constexpr int K = P + 1;
+	uint32_t px = sg.x + (uint32_t)(q * P) * 8u, py = sg.y + (uint32_t)q * 8u;
+	uint32_t pw = sg.w + (uint32_t)q * 8u, pt = sg.t + (uint32_t)q;
+	const uint32_t stepx = (uint32_t)(T * P) * 8u, stepy = (uint32_t)T * 8u;
+	constexpr bool MASK = HASW || HAST || CHECK;
+#pragma unroll 2
+	for (int i = q; i < n; i += T) {
+		double d[K];
+#pragma unroll
+		for (int c = 0; c < P; ++c) d[c] = lds_f64(px + (uint32_t)c * 8u);
+		d[P] = lds_f64(py);
+		px += stepx;
+		py += stepy;
+		bool ok = true;
+		double wv = 1.0;
+		if (HASW) {
+			wv = lds_f64(pw);
+			pw += stepy;
+			ok = wv > 0.0;
+			if (CHECK) ok = ok && finite_f64(wv);
+		}
+		if (HAST) {
+			const uint32_t tr = lds_u8(pt);
+			pt += (uint32_t)T;
+			ok = ok && tr != 0u;
+			M.ns += tr != 0u ? 1 : 0;
+		}
+		if (CHECK) {
+#pragma unroll
+			for (int c = 0; c < K; ++c) ok = ok && finite_f64(d[c]);
+		}
+#pragma unroll
+		for (int c = 0; c < K; ++c) d[c] -= sh[c];
+		if (!MASK || ok) {
+			if (MASK) M.nv += 1;
+			double a[K];
+#pragma unroll
+			for (int c = 0; c < K; ++c) a[c] = HASW ? wv * d[c] : d[c];
+#pragma unroll
+			for (int i2 = 0; i2 < K; ++i2)
+#pragma unroll
+				for (int j2 = i2; j2 < K; ++j2) M.s2[utri(i2, j2, K)] = fma(a[i2], d[j2], M.s2[utri(i2, j2, K)]);
+#pragma unroll
+			for (int c = 0; c < K; ++c) M.s1[c] += a[c];
+			if (HASW) {
+				M.sw += wv;
+#pragma unroll
+				for (int c = 0; c < P; ++c) M.q2[c] = fma(d[c], d[c], M.q2[c]);
+			}
+		}
+	}
+}
+
+// Butterfly over the T lanes of a group: afterwards every lane holds the group's sums.
+template <int P, bool HASW, bool HAST> __device__ __forceinline__ void small_reduce(SmallMoments<P> &M, int T, unsigned mask) {
+	constexpr int K = P + 1;
+	for (int off = 1; off < T; off <<= 1) {
+#pragma unroll
+		for (int i = 0; i < SmallMoments<P>::NS2; ++i) M.s2[i] += shfl_xor_f64(mask, M.s2[i], off);
+#pragma unroll
+		for (int i = 0; i < K; ++i) M.s1[i] += shfl_xor_f64(mask, M.s1[i], off);
+		if (HASW) {
+			M.sw += shfl_xor_f64(mask, M.sw, off);
+#pragma unroll
+			for (int i = 0; i < P; ++i) M.q2[i] += shfl_xor_f64(mask, M.q2[i], off);
+		}
+		M.nv += __shfl_xor_sync(mask, M.nv, off);
+		if (HAST) M.ns += __shfl_xor_sync(mask, M.ns, off);
+	}
+}
+
+// Shared-memory view of one round's group for this lane.
+struct SmallGroupView {
+	SmemGroup sg;
+	int n;     // rows of the group
+	int q, T;  // lane within the group, lanes per group
+	unsigned mask; // the T lanes of the group
+};
+
+// First row (in state order) that passes `pred(row)`, searched by the T lanes together; -1 if none.
+template <class Pred> __device__ __forceinline__ int small_first_row(const SmallGroupView &v, Pred pred) {
+	int f = 0x7fffffff;
+	for (int i = v.q; i < v.n; i += v.T)
+		if (pred(i)) {
+			f = i;
+			break;
+		}
+	for (int off = 1; off < v.T; off <<= 1) f = min(f, __shfl_xor_sync(v.mask, f, off));
+	return f == 0x7fffffff ? -1 : f;
+}
+
+template <int P, bool HASW, bool HAST> __device__ __forceinline__ bool small_row_valid_full(const SmallGroupView &v, int i) {
+	bool ok = finite_f64(lds_f64(v.sg.y + (uint32_t)i * 8u));
+	if (HASW) {
+		const double wv = lds_f64(v.sg.w + (uint32_t)i * 8u);
+		ok = ok && wv > 0.0 && finite_f64(wv);
+	}
+	if (HAST) ok = ok && lds_u8(v.sg.t + (uint32_t)i) != 0u;
+#pragma unroll
+	for (int c = 0; c < P; ++c) ok = ok && finite_f64(lds_f64(v.sg.x + (uint32_t)(i * P + c) * 8u));
+	return ok;
+}
+
+// Exact constant-column statistic for one feature: max |x - shift| over the valid rows (ols.rs:76-87).
+template <int P, bool HASW, bool HAST>
+__device__ __forceinline__ double small_exact_cdev(const SmallGroupView &v, int c, double shc) {
+	double m = 0.0;
+	for (int i = v.q; i < v.n; i += v.T)
+		if (small_row_valid_full<P, HASW, HAST>(v, i))
+			m = fmax(m, fabs(lds_f64(v.sg.x + (uint32_t)(i * P + c) * 8u) - shc));
+	for (int off = 1; off < v.T; off <<= 1) m = fmax(m, shfl_xor_f64(v.mask, m, off));
+	return m;
+}
+
+// sum w (y - b0 - x'beta)^2 over the valid rows with the coefficients just computed (NaN = aliased:
+// contributes nothing, lib.rs:2296-2303).
+template <int P, bool HASW, bool HAST>
+__device__ __forceinline__ double small_exact_rss(const SmallGroupView &v, const double (&beta)[P], unsigned live,
+                                                  double b0) {
+	double rss = 0.0;
+	for (int i = v.q; i < v.n; i += v.T) {
+		if (!small_row_valid_full<P, HASW, HAST>(v, i)) continue;
+		double fit = b0;
+#pragma unroll
+		for (int c = 0; c < P; ++c)
+			if ((live >> c) & 1u) fit = fma(beta[c], lds_f64(v.sg.x + (uint32_t)(i * P + c) * 8u), fit);
+		const double e = lds_f64(v.sg.y + (uint32_t)i * 8u) - fit;
+		const double wv = HASW ? lds_f64(v.sg.w + (uint32_t)i * 8u) : 1.0;
+		rss = fma(wv * e, e, rss);
+	}
+	for (int off = 1; off < v.T; off <<= 1) rss += shfl_xor_f64(v.mask, rss, off);
+	return rss;
+}
+
+// Solve + statistics of one group from its sums, executed by the T lanes of the group together.
+// Mirrors solve_group (solve.cuh) formula for formula; differences are structural only: no column
+// compaction (constant columns are simply dead from the start), reciprocals of the Cholesky diagonal,
+// distribution functions split across the lanes.
+template <int P, bool HASW, bool HAST>
+__device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const double (&sh)[P + 1], unsigned nonconst,
+                                            int n_state, int64_t g, const FitParams &Pm, const AnofoxB200FitOutputs &o,
+                                            const SmallGroupView &v) {
+	constexpr int K = P + 1;
+	const double nanv = nan_f64();
+	const int ic = Pm.fit_intercept ? 1 : 0;
+	const bool wls = Pm.method == ANOFOX_B200_WLS;
+	const int q = v.q, T = v.T;
+	const double n_valid = (double)M.nv;
+	const double sw = HASW ? M.sw : n_valid;
+	int status = 0;
+	if (n_state < Pm.min_state_rows)
+		status = ANOFOX_B200_STATUS_TOO_FEW_ROWS; // ols_aggregate.cpp:263-267
+	else if (M.nv <= 0)
+		status = ANOFOX_ERROR_NO_VALID_DATA; // ols.rs:68-70
+	const int pe = __popc(nonconst);
+	if (status == 0) {
+		if (pe == 0 && !ic) status = ANOFOX_ERROR_INSUFFICIENT_DATA;                // ols.rs:102-107
+		else if (pe > 0 && M.nv < pe + ic) status = ANOFOX_ERROR_INSUFFICIENT_DATA; // ols.rs:134-139
+	}
+	if (status != 0) {
+		if (q == 0) write_null_group(o, Pm, g, status);
+		return;
+	}
+	const double inv_sw = 1.0 / sw;
+	const double s1y = M.s1[P];
+	const double ybar = sh[P] + s1y * inv_sw;
+	const double syy_c = M.s2[utri(P, P, K)] - s1y * s1y * inv_sw;
+	const double tss = ic ? syy_c : syy_c + sw * ybar * ybar;
+	const bool inf_arrays = Pm.compute_inference && o.std_errors;
+
+	if (pe == 0) {
+		// all columns constant: intercept-only shortcut (ols.rs:108-130, wls.rs:126-150)
+		if (q == 0) {
+			const double ss = fmax(syy_c, 0.0);
+			const double var = wls ? ss * inv_sw : ss / (n_valid - 1.0);
+			o.status[g] = 0;
+			o.n_observations[g] = (int64_t)M.nv;
+			for (int j = 0; j < P; ++j) o.coefficients[g * P + j] = nanv;
+			o.intercept[g] = ybar;
+			o.r_squared[g] = 0.0;
+			o.adj_r_squared[g] = 0.0;
+			o.residual_std_error[g] = sqrt(var);
+			if (inf_arrays) {
+				for (int j = 0; j < P; ++j) {
+					o.std_errors[g * P + j] = nanv;
+					o.t_values[g * P + j] = nanv;
+					o.p_values[g * P + j] = nanv;
+					o.ci_lower[g * P + j] = nanv;
+					o.ci_upper[g * P + j] = nanv;
+				}
+				o.f_statistic[g] = nanv;
+				o.f_pvalue[g] = nanv;
+				if (o.has_inference) o.has_inference[g] = 0; // lib.rs:251-253
+			}
+			double aic, bic;
+			info_criteria_dev(ss, n_valid, 1.0, aic, bic);
+			if (o.aic) o.aic[g] = aic;
+			if (o.bic) o.bic[g] = bic;
+			if (o.rss) o.rss[g] = ss;
+		}
+		return;
+	}
+
+	// ---- centred (or raw, without intercept) Gram of all P columns; constant ones start dead ----
+	double A[P * (P + 1) / 2], b[P], orig[P], xm[P];
+#pragma unroll
+	for (int a = 0; a < P; ++a) {
+		const double s1a = M.s1[a];
+		const double ma = sh[a] + s1a * inv_sw;
+		xm[a] = ma;
+#pragma unroll
+		for (int c = 0; c <= a; ++c) {
+			double val = M.s2[utri(c, a, K)] - s1a * M.s1[c] * inv_sw;
+			if (!ic) val += sw * ma * xm[c];
+			A[ltri(a, c)] = val;
+		}
+		double cxy = M.s2[utri(a, P, K)] - s1a * s1y * inv_sw;
+		if (!ic) cxy += sw * ma * ybar;
+		b[a] = cxy;
+		const double caa = M.s2[utri(a, a, K)] - s1a * s1a * inv_sw;
+		orig[a] = caa + sw * ma * ma;
+	}
+	double lambda = 0.0;
+	if (Pm.method == ANOFOX_B200_RIDGE) {
+		lambda = Pm.alpha;
+		if (Pm.lambda_scaling == ANOFOX_LAMBDA_SCALING_GLMNET) {
+			const double sdy = sqrt(fmax(tss, 0.0) / n_valid);
+			lambda = Pm.alpha * n_valid;
+			if (sdy > 0.0) lambda /= sdy;
+		}
+	}
+	const bool ridge = lambda > 0.0;
+	if (ridge) {
+#pragma unroll
+		for (int a = 0; a < P; ++a) A[ltri(a, a)] += lambda;
+	}
+
+	// ---- Cholesky, left to right, limited pivoting (solve.cuh) --------------------------------
+	unsigned live = 0u;  // columns with a coefficient
+	double rinv[P];      // 1 / L_ii
+	int rank = 0;
+#pragma unroll
+	for (int i = 0; i < P; ++i) {
+#pragma unroll
+		for (int j = 0; j < i; ++j) {
+			double s = A[ltri(i, j)];
+#pragma unroll
+			for (int c = 0; c < j; ++c) s -= A[ltri(i, c)] * A[ltri(j, c)];
+			A[ltri(i, j)] = ((live >> j) & 1u) ? s * rinv[j] : 0.0;
+		}
+		double d = A[ltri(i, i)];
+#pragma unroll
+		for (int c = 0; c < i; ++c) d -= A[ltri(i, c)] * A[ltri(i, c)];
+		bool alias = ridge ? !(d > 0.0) : (!(d >= 1e-14 * orig[i]) || !(d > 0.0));
+		alias = alias || !((nonconst >> i) & 1u);
+		if (alias) {
+#pragma unroll
+			for (int c = 0; c < i; ++c) A[ltri(i, c)] = 0.0;
+			A[ltri(i, i)] = 0.0;
+			rinv[i] = 0.0;
+		} else {
+			const double l = sqrt(d);
+			A[ltri(i, i)] = l;
+			rinv[i] = 1.0 / l;
+			live |= 1u << i;
+			++rank;
+		}
+	}
+	// forward solve L v = b, back solve L^T beta = v (dead columns have zero rows/columns and rinv = 0)
+	double ess = 0.0;
+#pragma unroll
+	for (int i = 0; i < P; ++i) {
+		double s = b[i];
+#pragma unroll
+		for (int c = 0; c < i; ++c) s -= A[ltri(i, c)] * b[c];
+		s *= rinv[i];
+		b[i] = s;
+		ess = fma(s, s, ess);
+	}
+#pragma unroll
+	for (int i = P - 1; i >= 0; --i) {
+		double s = b[i];
+#pragma unroll
+		for (int c = i + 1; c < P; ++c) s -= A[ltri(c, i)] * b[c];
+		b[i] = s * rinv[i];
+	}
+	double bnorm2 = 0.0, b0 = ybar;
+#pragma unroll
+	for (int i = 0; i < P; ++i) {
+		bnorm2 = fma(b[i], b[i], bnorm2);
+		b0 -= xm[i] * b[i];
+	}
+	double rss = tss - ess - (ridge ? lambda * bnorm2 : 0.0);
+	if (!(rss > 1e-5 * tss)) {
+		// tss - ess keeps ~16 - log10(tss/rss) digits: take the residuals from the rows themselves
+		rss = small_exact_rss<P, HASW, HAST>(v, b, live, ic ? b0 : 0.0);
+	}
+	if (!(rss > 0.0)) rss = 0.0;
+
+	const int rank_total = rank + ic;
+	const double dfr = n_valid - (double)rank_total;
+	const double dfm = (double)rank;
+	const double r2 = 1.0 - rss / tss;
+	const double sigma2 = dfr > 0.0 ? rss / dfr : nanv;
+	if (q == 0) {
+		o.status[g] = 0;
+		o.n_observations[g] = (int64_t)M.nv;
+		o.intercept[g] = ic ? b0 : nanv; // ols.rs:172-176
+		o.r_squared[g] = r2;
+		o.adj_r_squared[g] = dfr > 0.0 ? 1.0 - (1.0 - r2) * (n_valid - (double)ic) / dfr : nanv;
+		o.residual_std_error[g] = sqrt(sigma2);
+		if (o.rss) o.rss[g] = rss;
+	}
+	if (q == (1 % T) && (o.aic || o.bic)) {
+		double aic, bic;
+		info_criteria_dev(rss, n_valid, (double)rank_total, aic, bic);
+		if (o.aic) o.aic[g] = aic;
+		if (o.bic) o.bic[g] = bic;
+	}
+	if (!inf_arrays) {
+#pragma unroll
+		for (int j = 0; j < P; ++j)
+			if ((j & (T - 1)) == q) o.coefficients[g * P + j] = ((live >> j) & 1u) ? b[j] : nanv;
+		return;
+	}
+
+	// ---- inference ------------------------------------------------------------------------------
+	// diag((L L^T)^-1)_j = sum_i (L^-1)_ij^2, all columns in every lane (P^3/6 multiply-adds) ...
+	double vdiag[P];
+#pragma unroll
+	for (int j = 0; j < P; ++j) {
+		double x[P];
+		double acc = 0.0;
+#pragma unroll
+		for (int i = j; i < P; ++i) {
+			double s = (i == j) ? 1.0 : 0.0;
+#pragma unroll
+			for (int c = j; c < i; ++c) s -= A[ltri(i, c)] * x[c];
+			s *= rinv[i];
+			x[i] = s;
+			acc = fma(s, s, acc);
+		}
+		vdiag[j] = acc;
+	}
+	const DfTables Tb{Pm.tcrit, Pm.gratio, Pm.rcp};
+	double tcrit = nanv;
+	if (dfr > 0.0) {
+		const int idf = (int)dfr;
+		tcrit = (Pm.tcrit && idf <= kTcritTable) ? Pm.tcrit[idf] : t_critical_dev(Pm.level, dfr);
+	}
+	// ... then lane q takes coefficients q, q+T, ...: the same instruction stream on different data
+	for (int j0 = 0; j0 < P; j0 += T) {
+		const int j = j0 + q;
+		if (j < P) {
+			double bj = 0.0, vj = 0.0;
+#pragma unroll
+			for (int c = 0; c < P; ++c)
+				if (c == j) {
+					bj = b[c];
+					vj = vdiag[c];
+				}
+			const int64_t oj = g * P + j;
+			if ((live >> j) & 1u) {
+				const double se = sqrt(sigma2 * vj);
+				const double t = bj / se;
+				o.coefficients[oj] = bj;
+				o.std_errors[oj] = se;
+				o.t_values[oj] = t;
+				o.p_values[oj] = dfr > 0.0 ? t_two_sided_p_fast(t, dfr, Tb) : nanv;
+				o.ci_lower[oj] = bj - tcrit * se;
+				o.ci_upper[oj] = bj + tcrit * se;
+			} else {
+				o.coefficients[oj] = nanv;
+				o.std_errors[oj] = nanv;
+				o.t_values[oj] = nanv;
+				o.p_values[oj] = nanv;
+				o.ci_lower[oj] = nanv;
+				o.ci_upper[oj] = nanv;
+			}
+		}
+	}
+	if (q == (2 % T)) {
+		double fs = nanv, fp = nanv;
+		if (dfm > 0.0 && dfr > 0.0) {
+			fs = ((tss - rss) / dfm) / sigma2;
+			fp = f_upper_p_fast(fs, dfm, dfr, Tb);
+		}
+		o.f_statistic[g] = fs;
+		o.f_pvalue[g] = fp;
+		if (o.has_inference) o.has_inference[g] = 1;
+	}
+}
+
+// One round: lanes [sub*T, sub*T+T) own group `gi` of the stage (valid = false: idle lanes).
+template <int P, bool HASW, bool HAST>
+__device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, const FitParams &Pm,
+                                            const AnofoxB200FitOutputs &o) {
+	constexpr int K = P + 1;
+	SmallMoments<P> M;
+	double sh[K];
+#pragma unroll
+	for (int c = 0; c < K; ++c) sh[c] = 0.0;
+	const int n = v.n;
+	int n_state = n;
+	bool have = n > 0;
+	// fast path: the shift row is the first row that passes the cheap mask (row 0 without masks)
+	int f = 0;
+	if (have && (HASW || HAST)) {
+		f = small_first_row(v, [&](int i) {
+			bool ok = true;
+			if (HASW) ok = lds_f64(v.sg.w + (uint32_t)i * 8u) > 0.0;
+			if (HAST) ok = ok && lds_u8(v.sg.t + (uint32_t)i) != 0u;
+			return ok;
+		});
+	}
+	bool redo = false;
+	M.clear();
+	if (have && f >= 0) {
+#pragma unroll
+		for (int c = 0; c < P; ++c) sh[c] = lds_f64(v.sg.x + (uint32_t)(f * P + c) * 8u);
+		sh[P] = lds_f64(v.sg.y + (uint32_t)f * 8u);
+		small_accumulate<P, HASW, HAST, false>(M, v.sg, n, v.q, v.T, sh);
+		small_reduce<P, HASW, HAST>(M, v.T, v.mask);
+		if (!(HASW || HAST)) M.nv = n;
+		bool bad = false;
+#pragma unroll
+		for (int c = 0; c < K; ++c) bad = bad || !finite_f64(M.s2[utri(c, c, K)]);
+		if (HASW) bad = bad || !finite_f64(M.sw);
+		redo = bad;
+	} else if (have) {
+		redo = true; // no row passes the mask: the checked path settles n_state / NO_VALID_DATA
+	}
+	if (redo) {
+		// a non-finite value somewhere: the full row filter of ols.rs:59-66
+		f = small_first_row(v, [&](int i) { return small_row_valid_full<P, HASW, HAST>(v, i); });
+		M.clear();
+		if (f >= 0) {
+#pragma unroll
+			for (int c = 0; c < P; ++c) sh[c] = lds_f64(v.sg.x + (uint32_t)(f * P + c) * 8u);
+			sh[P] = lds_f64(v.sg.y + (uint32_t)f * 8u);
+			small_accumulate<P, HASW, HAST, true>(M, v.sg, n, v.q, v.T, sh);
+		} else if (HAST) {
+			for (int i = v.q; i < n; i += v.T) M.ns += lds_u8(v.sg.t + (uint32_t)i) != 0u ? 1 : 0;
+		}
+		small_reduce<P, HASW, HAST>(M, v.T, v.mask);
+		if (f < 0) {
+#pragma unroll
+			for (int c = 0; c < K; ++c) sh[c] = 0.0;
+		}
+	}
+	if (HAST) n_state = M.ns;
+	// constant columns: all |x - shift| < 1e-10  <=>  max |d| < 1e-10. sum d^2 brackets max d^2
+	// (max d^2 <= sum d^2 <= n max d^2); only the band in between needs the exact statistic.
+	unsigned nonconst = 0u;
+	if (M.nv > 0) {
+#pragma unroll
+		for (int c = 0; c < P; ++c) {
+			const double s = HASW ? M.q2[c] : M.s2[utri(c, c, K)];
+			bool nc;
+			if (s < 0.99e-20)
+				nc = false;
+			else if (s > 1.01e-20 * (double)M.nv)
+				nc = true;
+			else
+				nc = !(small_exact_cdev<P, HASW, HAST>(v, c, sh[c]) < 1e-10);
+			nonconst |= nc ? (1u << c) : 0u;
+		}
+	}
+	small_solve<P, HASW, HAST>(M, sh, nonconst, n_state, g, Pm, o, v);
+}
+
+constexpr int kSmallStageGroups = 64; // groups per stage of the fused kernel at most (two rounds of 32)
+constexpr int kSmallMaxStages = 8;
+using SmallStageHeader = StageHeaderT<kSmallStageGroups>;
+
+struct SmallArgs {
+	AccArgs acc;
+	FitParams params;
+	AnofoxB200FitOutputs out;
+	int lanes_per_group; // T: 4, 8, 16 or 32
+	int max_stage_groups;
+};
+
+template <int P, int NCW, bool HASW, bool HAST>
+__global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const SmallArgs args) {
+	extern __shared__ __align__(128) unsigned char smem[];
+	__shared__ uint64_t full_bar[kSmallMaxStages], empty_bar[kSmallMaxStages];
+	__shared__ SmallStageHeader hdr[kSmallMaxStages];
+	const AccArgs &a = args.acc;
+	const int NS = a.n_stages;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	if (threadIdx.x == 0) {
+		for (int s = 0; s < NS; ++s) {
+			mbar_init(&full_bar[s], 1);
+			mbar_init(&empty_bar[s], NCW);
+		}
+		mbar_fence_init();
+	}
+	__syncthreads();
+	if (warp == 0) {
+		producer_loop<HASW, HAST>(a, smem, full_bar, empty_bar, hdr, NS, lane, args.max_stage_groups);
+		return;
+	}
+	const int T = args.lanes_per_group;
+	const int gpw = 32 / T; // groups per warp round
+	const int sub = lane / T, q = lane - sub * T;
+	const unsigned gmask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << (sub * T);
+	for (int it = 0;; ++it) {
+		const int s = it % NS;
+		mbar_wait(&full_bar[s], (uint32_t)((it / NS) & 1));
+		const int cnt = hdr[s].count;
+		if (cnt < 0) break;
+		unsigned char *base = smem + (size_t)s * a.stage_bytes;
+		const uint32_t ax = smem_u32(base + hdr[s].lead_x);
+		const uint32_t ay = smem_u32(base + a.xcap + hdr[s].lead_y);
+		const uint32_t aw = HASW ? smem_u32(base + a.xcap + a.ycap + hdr[s].lead_w) : 0u;
+		const uint32_t at = HAST ? smem_u32(base + a.xcap + a.ycap + a.wcap + hdr[s].lead_t) : 0u;
+		const int64_t g0 = hdr[s].g_first;
+		const int nrounds = (cnt + gpw - 1) / gpw;
+		for (;;) {
+			if (*(volatile int *)&hdr[s].next >= nrounds) break; // nothing left to claim: skip the atomic
+			int r = 0;
+			if (lane == 0) r = atomicAdd(&hdr[s].next, 1);
+			r = __shfl_sync(0xffffffffu, r, 0);
+			if (r >= nrounds) break;
+			const int gi = r * gpw + sub;
+			if (gi < cnt) {
+				const int rb = (int)hdr[s].rowstart[gi];
+				SmallGroupView v;
+				v.n = (int)hdr[s].rowstart[gi + 1] - rb;
+				v.q = q;
+				v.T = T;
+				v.mask = gmask;
+				v.sg.x = ax + (uint32_t)rb * (uint32_t)(P * 8);
+				v.sg.y = ay + (uint32_t)rb * 8u;
+				v.sg.w = aw + (uint32_t)rb * 8u;
+				v.sg.t = at + (uint32_t)rb;
+				v.sg.kone = v.sg.kzero = 0u;
+				small_group<P, HASW, HAST>(v, g0 + gi, args.params, args.out);
+			}
+			__syncwarp();
+		}
+		__syncwarp();
+		if (lane == 0) mbar_arrive(&empty_bar[s]);
+	}
+}
+
+} // namespace b200

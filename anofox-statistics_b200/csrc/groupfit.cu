@@ -20,6 +20,7 @@
 #include "acc_launch.h"
 #include "accumulate.cuh"
 #include "common.cuh"
+#include "fused_launch.h"
 #include "solve.cuh"
 #include "specfun.cuh"
 
@@ -62,6 +63,18 @@ __global__ void __launch_bounds__(128) solve_kernel(const double *__restrict__ r
                                                     AnofoxB200FitOutputs o, int *refine_count, int64_t *refine_list) {
 	const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (g >= n_groups) return;
+	solve_group<PMAX>(records + g * rec_len(P.p), 1, g, P, o, -1.0, nullptr, refine_count, refine_list);
+}
+
+// Same, for the groups named in a list (the big groups of a batch whose other groups went through the
+// fused kernel).
+template <int PMAX>
+__global__ void __launch_bounds__(128) solve_list_kernel(const double *__restrict__ records, const int64_t *__restrict__ list,
+                                                         int n_list, FitParams P, AnofoxB200FitOutputs o,
+                                                         int *refine_count, int64_t *refine_list) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_list) return;
+	const int64_t g = list[i];
 	solve_group<PMAX>(records + g * rec_len(P.p), 1, g, P, o, -1.0, nullptr, refine_count, refine_list);
 }
 
@@ -220,6 +233,39 @@ __global__ void split_record_kernel(const double *__restrict__ rec, int p, doubl
 	}
 }
 
+
+// First valid row of one row shard (row-sharded single group, step 0): blocks scan disjoint chunks in
+// order and stop as soon as an earlier chunk has reported a hit; `best` ends as the smallest valid row.
+__global__ void shard_first_valid_kernel(const double *__restrict__ y, const double *__restrict__ x,
+                                         const double *__restrict__ w, int64_t n_rows, int p,
+                                         unsigned long long *best) {
+	const int64_t chunk = ((n_rows + gridDim.x - 1) / gridDim.x + blockDim.x - 1) / blockDim.x * blockDim.x;
+	const int64_t b0 = (int64_t)blockIdx.x * chunk;
+	int64_t b1 = b0 + chunk;
+	if (b1 > n_rows) b1 = n_rows;
+	for (int64_t base = b0; base < b1; base += blockDim.x) {
+		// decided by an earlier chunk? (one thread reads, the vote makes the exit uniform)
+		const bool stop = threadIdx.x == 0 && *(volatile unsigned long long *)best < (unsigned long long)base;
+		if (__syncthreads_or(stop ? 1 : 0)) return;
+		const int64_t r = base + threadIdx.x;
+		bool ok = false;
+		if (r < b1) {
+			ok = row_ok_yw(y[r], w ? w[r] : 1.0, 1, w != nullptr);
+			for (int c = 0; ok && c < p; ++c) ok = finite_f64(x[r * p + c]);
+		}
+		if (ok) atomicMin(best, (unsigned long long)r);
+		if (__syncthreads_or(ok ? 1 : 0)) return;
+	}
+}
+__global__ void shard_shift_kernel(const double *__restrict__ y, const double *__restrict__ x, int p,
+                                   const unsigned long long *best, int64_t n_rows, double *__restrict__ shift,
+                                   int32_t *__restrict__ found) {
+	const unsigned long long f = *best;
+	const bool ok = f < (unsigned long long)n_rows;
+	for (int c = threadIdx.x; c <= p; c += blockDim.x) shift[c] = ok ? (c < p ? x[(int64_t)f * p + c] : y[f]) : 0.0;
+	if (threadIdx.x == 0) *found = ok ? 1 : 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Dispatch on the feature count
 // ---------------------------------------------------------------------------------------------
@@ -287,6 +333,40 @@ static cudaError_t launch_solve(const double *records, int64_t G, const FitParam
 		solve_kernel<64><<<blocks, threads, 0, st>>>(records, G, P, o, refine_count, refine_list);
 	LAUNCHED();
 	return cudaGetLastError();
+}
+
+static cudaError_t launch_solve_list(const double *records, const int64_t *list, int n_list, const FitParams &P,
+                                     const AnofoxB200FitOutputs &o, int *refine_count, int64_t *refine_list,
+                                     cudaStream_t st) {
+	if (n_list <= 0) return cudaSuccess;
+	const int threads = 128;
+	const unsigned blocks = (unsigned)((n_list + threads - 1) / threads);
+	if (P.p <= 8)
+		solve_list_kernel<8><<<blocks, threads, 0, st>>>(records, list, n_list, P, o, refine_count, refine_list);
+	else if (P.p <= 16)
+		solve_list_kernel<16><<<blocks, threads, 0, st>>>(records, list, n_list, P, o, refine_count, refine_list);
+	else if (P.p <= 32)
+		solve_list_kernel<32><<<blocks, threads, 0, st>>>(records, list, n_list, P, o, refine_count, refine_list);
+	else
+		solve_list_kernel<64><<<blocks, threads, 0, st>>>(records, list, n_list, P, o, refine_count, refine_list);
+	LAUNCHED();
+	return cudaGetLastError();
+}
+
+static cudaError_t launch_small(const SmallArgs &a, bool has_w, bool has_t, int grid, cudaStream_t st) {
+	cudaError_t e = cudaErrorInvalidValue;
+	switch (a.acc.p) {
+	case 1: e = launch_small_p1(has_w, has_t, a, grid, st); break;
+	case 2: e = launch_small_p2(has_w, has_t, a, grid, st); break;
+	case 3: e = launch_small_p3(has_w, has_t, a, grid, st); break;
+	case 4: e = launch_small_p4(has_w, has_t, a, grid, st); break;
+	case 5: e = launch_small_p5(has_w, has_t, a, grid, st); break;
+	case 6: e = launch_small_p6(has_w, has_t, a, grid, st); break;
+	case 7: e = launch_small_p7(has_w, has_t, a, grid, st); break;
+	case 8: e = launch_small_p8(has_w, has_t, a, grid, st); break;
+	}
+	LAUNCHED();
+	return e;
 }
 
 static cudaError_t launch_refine(const RefineArgs &a, const FitParams &P, const AnofoxB200FitOutputs &o, int sms,
@@ -373,6 +453,44 @@ static StageGeom stage_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	while ((int64_t)g.n_stages * g.stage_bytes > budget + 8 * 1024 && g.n_stages > 2) --g.n_stages;
 	g.window_rows = (int64_t)g.cap_rows * 8;
 	return g;
+}
+
+// Fused small-group path (fused_small.cuh): used when p <= 8 and the mean group is small enough for
+// many groups to be resident per SM. T lanes per group keep >= ~8 warps' worth of groups on chip.
+static std::atomic<int> g_force_path{0}; // 0 = auto, 1 = always the record path (tests / A-B runs)
+struct SmallGeom {
+	bool use;
+	int T, max_groups;
+	StageGeom sg;
+};
+static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, int64_t n_groups) {
+	SmallGeom r;
+	memset(&r, 0, sizeof r);
+	const int64_t row_bytes = 8 * (int64_t)(p + 1) + (has_w ? 8 : 0) + (has_t ? 1 : 0);
+	const double mean_rows = n_groups > 0 ? (double)n_rows / (double)n_groups : 0.0;
+	const double mean_bytes = mean_rows * (double)row_bytes;
+	r.use = g_force_path.load() != 1 && p <= kSmallMaxFeatures && n_groups > 0 && mean_bytes <= 24.0 * 1024.0;
+	if (!r.use) return r;
+	int T = 4;
+	while (T < 32 && mean_bytes > 700.0 * T) T *= 2;
+	r.T = T;
+	const int gpw = 32 / T;
+	r.max_groups = std::min(kSmallStageGroups, 2 * gpw); // two rounds per stage
+	const int64_t budget = 196 * 1024;
+	int64_t cap = (int64_t)std::ceil(std::max((double)r.max_groups, 4.0) * std::max(mean_rows, 1.0)) + 8;
+	if (cap * row_bytes > 96 * 1024) cap = 96 * 1024 / row_bytes;
+	if (cap * row_bytes < 8 * 1024) cap = 8 * 1024 / row_bytes;
+	StageGeom &g = r.sg;
+	g.cap_rows = (int)cap;
+	g.xcap = align16((int64_t)g.cap_rows * p * 8 + 16);
+	g.ycap = align16((int64_t)g.cap_rows * 8 + 16);
+	g.wcap = has_w ? align16((int64_t)g.cap_rows * 8 + 16) : 0;
+	g.tcap = has_t ? align16((int64_t)g.cap_rows + 32) : 0;
+	g.stage_bytes = (g.xcap + g.ycap + g.wcap + g.tcap + 127) & ~127;
+	g.n_stages = (int)std::min<int64_t>(kSmallMaxStages, budget / g.stage_bytes);
+	if (g.n_stages < 2) g.n_stages = 2;
+	g.window_rows = (int64_t)g.cap_rows * 8;
+	return r;
 }
 
 static void set_error(AnofoxError *err, int code, const char *msg) {
@@ -486,11 +604,17 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 		return base ? base + o : (unsigned char *)nullptr;
 	};
 	const int L = rec_len(p);
-	const StageGeom sg = stage_geometry(p, true, true, N, G);
-	const int64_t n_tiles = (N + sg.window_rows - 1) / sg.window_rows + 1;
-	// big groups hold more than cap_rows rows each (cap_rows depends on w/train only mildly: use the
-	// smallest capacity for the bound)
-	w.nbig_max = std::min<int64_t>(G, N / std::max(1, sg.cap_rows) + 1);
+	// bounds that hold for whichever path / (w, train) combination the call ends up using: the smallest
+	// stage capacity gives the most row windows and the most groups that can exceed a stage
+	int min_cap = 1 << 30;
+	for (int c = 0; c < 4; ++c) {
+		min_cap = std::min(min_cap, stage_geometry(p, c & 1, c & 2, N, G).cap_rows);
+		const SmallGeom sm = small_geometry(p, c & 1, c & 2, N, G);
+		if (sm.use) min_cap = std::min(min_cap, sm.sg.cap_rows);
+	}
+	min_cap = std::max(min_cap, 1);
+	const int64_t n_tiles = (N + (int64_t)min_cap * 8 - 1) / ((int64_t)min_cap * 8) + 1;
+	w.nbig_max = std::min<int64_t>(G, N / min_cap + 1);
 	w.n_part = sms * 2 * kStreamWarps;
 	w.records = (double *)take((size_t)std::max<int64_t>(G, 1) * L * 8);
 	w.tile_g0 = (int64_t *)take((size_t)(n_tiles + 2) * 8);
@@ -608,9 +732,23 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		}
 	}
 
-	const StageGeom sg = stage_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
+	AnofoxB200FitOutputs fo = out;
+	if (!fo.coefficients) { // predict path without fit outputs: use workspace arrays
+		memset(&fo, 0, sizeof fo);
+		fo.coefficients = ws.f_coef;
+		fo.intercept = ws.f_icpt;
+		fo.r_squared = ws.f_r2;
+		fo.adj_r_squared = ws.f_adj;
+		fo.residual_std_error = ws.f_rse;
+		fo.n_observations = ws.f_nobs;
+		fo.status = ws.f_status;
+	}
+
+	const SmallGeom small = small_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
+	const StageGeom sg = small.use ? small.sg : stage_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
 	const int64_t n_tiles = (N + sg.window_rows - 1) / sg.window_rows + 1; // +1: groups that start at row N
 	CU(cudaMemsetAsync(ws.big_count, 0, 256, st), "memset");
+	CU(cudaMemsetAsync(ws.refine_count, 0, 256, st), "memset");
 	tile_bounds_kernel<<<(unsigned)((n_tiles + 1 + 255) / 256), 256, 0, st>>>(offsets, G, sg.window_rows, n_tiles, ws.tile_g0);
 	LAUNCHED();
 	CU(cudaGetLastError(), "tile_bounds_kernel");
@@ -636,12 +774,23 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	a.n_stages = sg.n_stages;
 	const int grid = (int)std::min<int64_t>(di.sms, n_tiles);
 	timer_mark(st);
-	CU(launch_resident(a, grid, st), "acc_resident_kernel");
+	if (small.use) {
+		// rows -> results in one kernel for every group that fits a stage
+		SmallArgs sa;
+		sa.acc = a;
+		sa.params = P;
+		sa.out = fo;
+		sa.lanes_per_group = small.T;
+		sa.max_stage_groups = small.max_groups;
+		CU(launch_small(sa, wuse != nullptr, train_use != nullptr, grid, st), "fit_small_kernel");
+	} else {
+		CU(launch_resident(a, grid, st), "acc_resident_kernel");
+	}
 	timer_mark(st);
 
 	// Big groups (rare): the count decides whether the streaming kernels run at all.
+	int nbig = 0;
 	if (N > sg.cap_rows) {
-		int nbig = 0;
 		CU(cudaMemcpyAsync(&nbig, ws.big_count, sizeof(int), cudaMemcpyDeviceToHost, st), "read big_count");
 		CU(cudaStreamSynchronize(st), "sync");
 		for (int b0 = 0; b0 < nbig; b0 += 64) {
@@ -675,20 +824,12 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		}
 	}
 
-	AnofoxB200FitOutputs fo = out;
-	if (!fo.coefficients) { // predict path without fit outputs: use workspace arrays
-		memset(&fo, 0, sizeof fo);
-		fo.coefficients = ws.f_coef;
-		fo.intercept = ws.f_icpt;
-		fo.r_squared = ws.f_r2;
-		fo.adj_r_squared = ws.f_adj;
-		fo.residual_std_error = ws.f_rse;
-		fo.n_observations = ws.f_nobs;
-		fo.status = ws.f_status;
+	if (small.use) {
+		if (nbig > 0) CU(launch_solve_list(ws.records, ws.big_list, nbig, P, fo, ws.refine_count, ws.refine_list, st), "solve_list_kernel");
+	} else {
+		CU(launch_solve(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_kernel");
 	}
-	CU(cudaMemsetAsync(ws.refine_count, 0, 256, st), "memset");
-	CU(launch_solve(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_kernel");
-	{
+	if (!small.use || nbig > 0) {
 		RefineArgs ra;
 		ra.offsets = offsets;
 		ra.y = y;
@@ -1225,6 +1366,41 @@ size_t anofox_b200_moment_block_len(int32_t n_features) {
 	return (size_t)(4 + k + k * (k + 1) / 2);
 }
 
+int32_t anofox_b200_first_valid_row_device(const double *y, const double *x, const double *w, int64_t n_rows,
+                                           int32_t n_features, double *shift_out, int32_t *found_out, void *workspace,
+                                           size_t workspace_bytes, void *stream, AnofoxError *err) {
+	clear_error(err);
+	DeviceInfo &di = device_info();
+	if (!di.ok) {
+		set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+		return ANOFOX_ERROR_INTERNAL;
+	}
+	const int p = n_features;
+	if (p <= 0 || p > kMaxFeatures || n_rows < 0 || !shift_out || !found_out || (n_rows > 0 && (!x || !y))) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "invalid argument");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	Workspace ws;
+	const size_t need = carve(ws, (unsigned char *)workspace, 1, n_rows, p, di.sms);
+	if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 255)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "workspace too small or misaligned");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	cudaStream_t st = (cudaStream_t)stream;
+	unsigned long long *best = (unsigned long long *)ws.big_list;
+	CU(cudaMemsetAsync(best, 0xff, sizeof(unsigned long long), st), "memset");
+	if (n_rows > 0) {
+		const int blocks = (int)std::min<int64_t>(di.sms * 4, (n_rows + 255) / 256);
+		shard_first_valid_kernel<<<blocks, 256, 0, st>>>(y, x, w, n_rows, p, best);
+		LAUNCHED();
+		CU(cudaGetLastError(), "shard_first_valid_kernel");
+	}
+	shard_shift_kernel<<<1, 128, 0, st>>>(y, x, p, best, n_rows, shift_out, found_out);
+	LAUNCHED();
+	CU(cudaGetLastError(), "shard_shift_kernel");
+	return 0;
+}
+
 int32_t anofox_b200_moments_device(const double *y, const double *x, const double *w, int64_t n_rows,
                                    int32_t n_features, const double *shift, double *moments, double *cdev,
                                    void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err) {
@@ -1261,7 +1437,9 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	s.partials = ws.partials;
 	s.n_part = ws.n_part;
 	s.records = ws.records;
+	timer_mark(st);
 	CU(launch_stream(s, ws.n_part / kStreamWarps, st), "acc_stream_kernel");
+	timer_mark(st);
 	dim3 rg((unsigned)((rec_len(p) + 127) / 128), 1);
 	reduce_partials_kernel<<<rg, 128, 0, st>>>(s);
 	LAUNCHED();
@@ -1269,6 +1447,7 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	split_record_kernel<<<1, 256, 0, st>>>(ws.records, p, moments, cdev);
 	LAUNCHED();
 	CU(cudaGetLastError(), "split_record_kernel");
+	timer_mark(st);
 	return 0;
 }
 
@@ -1352,6 +1531,17 @@ int64_t anofox_b200_stage_timing_read(double *accumulate_ms, double *solve_ms) {
 	if (solve_ms) *solve_ms = b;
 	t.clear();
 	return n;
+}
+
+// Test / A-B hook: 0 = choose the kernel path automatically, 1 = always the record path (DMMA accumulation
+// kernel + solve kernel), even where the fused small-group kernel would be chosen.
+void anofox_b200_force_path(int32_t path) { g_force_path.store(path); }
+// Which path a batch of this shape takes: 1 = fused small-group kernel (lanes_per_group set), 0 = record path.
+int32_t anofox_b200_plan(int64_t n_groups, int64_t n_rows, int32_t n_features, int32_t has_w, int32_t has_train,
+                         int32_t *lanes_per_group) {
+	const SmallGeom sm = small_geometry(n_features, has_w != 0, has_train != 0, n_rows, n_groups);
+	if (lanes_per_group) *lanes_per_group = sm.use ? sm.T : 0;
+	return sm.use ? 1 : 0;
 }
 
 // Test hook: evaluate the device special functions on arrays (host pointers).

@@ -6,7 +6,7 @@ full inference, synthetic. One "step" = one pass of the hot path (accumulate + s
 over the whole batch. `value` = fits/s with inputs resident in HBM; `e2e` = the same through the
 host-pointer C-ABI call (pinned host buffers, H2D + D2H inside the timed region).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C1|C2|C3r|C3w|C5]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C1|C2|C3r|C3w|C4|C5]
   torchrun --nproc-per-node N bench.py --gpus N ...      (weak scaling: every rank fits its own C2)
 """
 import argparse
@@ -28,6 +28,8 @@ WORKLOADS = {
     "C3r": (1_000_000, 200, 16, "ridge", False, {"alpha": 1.0, "rank_deficient": True}),
     "C3w": (1_000_000, 200, 16, "wls", False, {"weights": True, "rank_deficient": True}),
     "C5": (100_000, 1_000, 8, "ols", False, {"holdout": 0.2, "predict": True}),
+    # one group, rows sharded over the ranks (125 M rows x 64 features per GPU; 1 B rows on 8 GPUs)
+    "C4": (1, 125_000_000, 64, "ols", True, {"row_sharded": True}),
 }
 
 
@@ -126,6 +128,122 @@ def cpu_reference_run(wl, host, steps, warmup, threads, budget_s=12.0):
     return gs / dt, dt, gs, threads
 
 
+def make_c4_shard(rows, p, seed, device="cuda", chunk=2_000_000):
+    """x ~ N(0,1) with AR(1) correlation 0.3 across features, y linear + noise."""
+    import math
+    import torch
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    x = torch.empty((rows, p), dtype=torch.float64, device=device)
+    y = torch.empty(rows, dtype=torch.float64, device=device)
+    gb = torch.Generator(device=device)
+    gb.manual_seed(4)  # the coefficients are the same on every rank: it is ONE group
+    beta = torch.rand(p, generator=gb, dtype=torch.float64, device=device) * 2 - 1
+    c = math.sqrt(1 - 0.09)
+    for r0 in range(0, rows, chunk):
+        r1 = min(rows, r0 + chunk)
+        z = torch.randn((r1 - r0, p), generator=gen, dtype=torch.float64, device=device)
+        for j in range(1, p):
+            z[:, j].mul_(c).add_(z[:, j - 1], alpha=0.3)
+        x[r0:r1] = z
+        y[r0:r1] = 1.5 + z @ beta + torch.randn(r1 - r0, generator=gen, dtype=torch.float64, device=device) * 0.7
+        del z
+    return x, y
+
+
+def run_c4(args, rank, world, local):
+    """Row-sharded single group: moments per rank + NCCL all-reduce of the moment block + replicated solve."""
+    import torch
+    import torch.distributed as dist
+    from importlib import import_module
+    from __graft_entry__ import load_package
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = load_package()
+    pkg.device_check()
+    D = import_module("anofox_statistics_b200.distributed")
+    G, n, p, method, inference, extra = WORKLOADS["C4"]
+    rows = max(4096, int(n * args.scale))
+    x, y = make_c4_shard(rows, p, seed=40 + rank)
+    fit = D.ShardedSingleGroupFit(rows, p, inference=inference)
+
+    def step():
+        return fit.fit(y, x, None, method=method, compute_inference=inference)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    pkg.stage_timing(True)
+    l0 = pkg.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        out = step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = pkg.launch_count() - l0
+    calls, acc_ms, red_ms = pkg.stage_timing_read()
+    pkg.stage_timing(False)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t.item()) / args.steps
+    total_rows = world * rows
+    value = total_rows / (ms_per_step * 1e-3)
+    # every rank must hold the same result (replicated solve on identical reduced blocks)
+    coef = out["coefficients"].clone()
+    same = True
+    if world > 1:
+        ref = coef.clone()
+        dist.broadcast(ref, 0)
+        flag = torch.tensor([1.0 if torch.equal(ref, coef) else 0.0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        same = bool(flag.item() == 1.0)
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        k = p + 2
+        acc_launch_ms = acc_ms / max(calls, 1)
+        acc_bytes = rows * 8 * (p + 1)
+        achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
+        flops = rows * k * (k + 1)  # symmetric Gram with the y and 1 columns, 2 flop per MAC on the triangle
+        tf = flops / (acc_launch_ms * 1e-3) / 1e12 if acc_launch_ms > 0 else None
+        roofline = {"bound": "hbm", "kernel": "acc_stream_kernel<8,SIDE> (FP64 DMMA Gram of one row shard)",
+                    "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                    "frac": (achieved / peak) if achieved else None, "traffic": None,
+                    "algorithmic_bytes_per_launch": acc_bytes, "avg_launch_ms": acc_launch_ms,
+                    "fp64_algorithmic_tflops": tf, "fp64_nominal_peak_tflops": 40.0,
+                    "fp64_frac_of_nominal": (tf / 40.0) if tf else None,
+                    "note": "p = 64 is ~8.5 flop/B: the FP64 DMMA pipe co-bounds this kernel (SURVEY.md 8d)",
+                    "reduce_and_split_ms": red_ms / max(calls, 1)}
+        line = {"metric": "rows_per_sec", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "single-group OLS, %d rows x %d features per GPU, row-sharded, "
+                                       "NCCL all-reduce of the moment block" % (rows, p),
+                           "rows_per_gpu": rows, "features": p, "method": method, "inference": inference,
+                           "collectives_per_step": "all_gather(p+2) + all_reduce SUM(%d f64) + all_reduce MAX(%d f64)"
+                                                   % (pkg.moment_block_len(p), p),
+                           "l2_policy": "inputs (%.1f GB/step/GPU) exceed the 126 MB L2" % (acc_bytes / 1e9)},
+                "fits_per_sec": 1.0 / (ms_per_step * 1e-3), "identical_on_all_ranks": same,
+                "status": int(out["status"][0].item()), "n_observations": int(out["n_observations"][0].item()),
+                "clocks": clocks, "e2e": None, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": None}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -142,6 +260,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "C4" and args.impl == "ours":
+        return run_c4(args, rank, world, local)
     G, n, p, method, inference, extra = WORKLOADS[args.workload]
     G = max(64, int(G * args.scale))
     wl = (G, n, p, method, inference, extra)

@@ -292,14 +292,24 @@ int32_t anofox_b200_fit_predict_batch_host(const int64_t *offsets, int64_t n_gro
                                            AnofoxError *err);
 
 /* Row-sharded single group (config "1 B rows x 64 features over 8 GPUs").
+ * Step 0, per rank: anofox_b200_first_valid_row_device finds the first row of this rank's shard that
+ *   passes the reference's row filter (ols.rs:59-66, wls.rs:76-86) and writes it to shift_out[p+1]
+ *   (x_1..x_p, y; zeros when none) and *found_out (0/1), both device memory. The caller all-gathers
+ *   (found, shift) and uses the row of the LOWEST rank that found one: that is the first valid row of
+ *   the whole group, the row the reference's constant-column test compares against (ols.rs:76-87).
  * Step 1, per rank: accumulate the shifted moment block of this rank's rows.
  *   shift   [p+1] device f64: common origin (x_1..x_p, y) -- every rank must pass the
  *           same values (rank 0's first valid row, broadcast by the caller)
- *   moments device f64 [anofox_b200_moment_block_len(p)]: additive under SUM
+ *   moments device f64 [anofox_b200_moment_block_len(p)]: additive under SUM. Layout: [0] valid rows,
+ *           [1] sum of weights, [2] rows seen, [3] spare, then S1[p+1] = sum w d, then the packed upper
+ *           triangle (row-major, i <= j) of S2 = sum w d d^T, d = (x_1..x_p, y) - shift
  *   cdev    device f64 [p]: max |x_j - shift_j| over valid rows: additive under MAX
  * Step 2, caller: ncclAllReduce(moments, SUM), ncclAllReduce(cdev, MAX).
  * Step 3, every rank: solve from the reduced block (one group) into `out` (G = 1). */
 size_t anofox_b200_moment_block_len(int32_t n_features);
+int32_t anofox_b200_first_valid_row_device(const double *y, const double *x, const double *w, int64_t n_rows,
+                                           int32_t n_features, double *shift_out, int32_t *found_out, void *workspace,
+                                           size_t workspace_bytes, void *stream, AnofoxError *err);
 int32_t anofox_b200_moments_device(const double *y, const double *x, const double *w, int64_t n_rows,
                                    int32_t n_features, const double *shift, double *moments, double *cdev,
                                    void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err);
