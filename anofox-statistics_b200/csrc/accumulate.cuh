@@ -708,6 +708,7 @@ struct StreamArgs {
 	double *partials;       // [nbig][n_part][L]
 	int n_part;             // gridDim.x * warps per CTA of acc_stream_kernel
 	double *records;        // group mode: [G][L]; shard mode: [1][L]
+	int64_t rec_gs, rec_es; // record element (g, i) lives at records[g * rec_gs + i * rec_es]
 };
 
 __device__ __forceinline__ bool row_valid_full(const StreamArgs &a, int64_t r) {
@@ -804,7 +805,7 @@ static __global__ void reduce_partials_kernel(const StreamArgs a) {
 		v = 0.0;
 		for (int q = 0; q < a.n_part; ++q) v += part[(int64_t)q * L + i];
 	}
-	a.records[g * L + i] = v;
+	a.records[g * a.rec_gs + (int64_t)i * a.rec_es] = v;
 }
 
 } // namespace b200

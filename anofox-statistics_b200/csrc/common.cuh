@@ -41,6 +41,8 @@ struct FitParams {
 	const double *tcrit;  // [kTcritTable + 1] t_{(1+level)/2, df}, index = df   (may be null: evaluate directly)
 	const double *gratio; // [kTcritTable + 1] Gamma((df+1)/2) / Gamma(df/2)
 	const double *rcp;    // [kRcpTable + 1]  1 / m
+	const double *ce;     // [kSeriesTable] binomial-series coefficients for even df (specfun.cuh)
+	const double *co;     // [kSeriesTable] ... and for odd df
 	int predict_mode;    // 1: df for t-critical follows anofox_predict_with_interval
 	int min_state_rows;  // 2 = aggregate rule (ols_aggregate.cpp:263-267); 0 = direct anofox_*_fit call
 };

@@ -138,6 +138,11 @@ struct SmallGroupView {
 	int n;     // rows of the group
 	int q, T;  // lane within the group, lanes per group
 	unsigned mask; // the T lanes of the group
+	double *pv;    // this group's slot of the warp's p-value scratch: f[P+1], d1, d2 (see fit_small_kernel)
+	// thread-per-group mode (solve_small_kernel): no rows at hand -- groups that need the exact residual
+	// pass are queued for refine_kernel instead
+	int *refine_count;
+	int64_t *refine_list;
 };
 
 // First row (in state order) that passes `pred(row)`, searched by the T lanes together; -1 if none.
@@ -199,7 +204,7 @@ __device__ __forceinline__ double small_exact_rss(const SmallGroupView &v, const
 // Mirrors solve_group (solve.cuh) formula for formula; differences are structural only: no column
 // compaction (constant columns are simply dead from the start), reciprocals of the Cholesky diagonal,
 // distribution functions split across the lanes.
-template <int P, bool HASW, bool HAST>
+template <int P, bool HASW, bool HAST, bool ROWS>
 __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const double (&sh)[P + 1], unsigned nonconst,
                                             int n_state, int64_t g, const FitParams &Pm, const AnofoxB200FitOutputs &o,
                                             const SmallGroupView &v) {
@@ -209,7 +214,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 	const bool wls = Pm.method == ANOFOX_B200_WLS;
 	const int q = v.q, T = v.T;
 	const double n_valid = (double)M.nv;
-	const double sw = HASW ? M.sw : n_valid;
+	const double sw = (HASW || !ROWS) ? M.sw : n_valid;
 	int status = 0;
 	if (n_state < Pm.min_state_rows)
 		status = ANOFOX_B200_STATUS_TOO_FEW_ROWS; // ols_aggregate.cpp:263-267
@@ -356,7 +361,12 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 	double rss = tss - ess - (ridge ? lambda * bnorm2 : 0.0);
 	if (!(rss > 1e-5 * tss)) {
 		// tss - ess keeps ~16 - log10(tss/rss) digits: take the residuals from the rows themselves
-		rss = small_exact_rss<P, HASW, HAST>(v, b, live, ic ? b0 : 0.0);
+		if (ROWS) {
+			rss = small_exact_rss<P, HASW, HAST>(v, b, live, ic ? b0 : 0.0);
+		} else if (v.refine_count) {
+			const int slot = atomicAdd(v.refine_count, 1);
+			v.refine_list[slot] = g;
+		}
 	}
 	if (!(rss > 0.0)) rss = 0.0;
 
@@ -374,7 +384,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		o.residual_std_error[g] = sqrt(sigma2);
 		if (o.rss) o.rss[g] = rss;
 	}
-	if (q == (1 % T) && (o.aic || o.bic)) {
+	if (q == (1 & (T - 1)) && (o.aic || o.bic)) {
 		double aic, bic;
 		info_criteria_dev(rss, n_valid, (double)rank_total, aic, bic);
 		if (o.aic) o.aic[g] = aic;
@@ -405,13 +415,14 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		}
 		vdiag[j] = acc;
 	}
-	const DfTables Tb{Pm.tcrit, Pm.gratio, Pm.rcp};
 	double tcrit = nanv;
 	if (dfr > 0.0) {
 		const int idf = (int)dfr;
 		tcrit = (Pm.tcrit && idf <= kTcritTable) ? Pm.tcrit[idf] : t_critical_dev(Pm.level, dfr);
 	}
-	// ... then lane q takes coefficients q, q+T, ...: the same instruction stream on different data
+	// ... then lane q takes coefficients q, q+T, ...: the same instruction stream on different data.
+	// The p-values themselves (the expensive part) are evaluated after the round by all 32 lanes of the
+	// warp from the statistics deposited in v.pv: t^2 per coefficient and the F statistic.
 	for (int j0 = 0; j0 < P; j0 += T) {
 		const int j = j0 + q;
 		if (j < P) {
@@ -429,35 +440,72 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 				o.coefficients[oj] = bj;
 				o.std_errors[oj] = se;
 				o.t_values[oj] = t;
-				o.p_values[oj] = dfr > 0.0 ? t_two_sided_p_fast(t, dfr, Tb) : nanv;
 				o.ci_lower[oj] = bj - tcrit * se;
 				o.ci_upper[oj] = bj + tcrit * se;
+				if (ROWS)
+					v.pv[j] = t * t;
+				else
+					o.p_values[oj] = pvalue_f(t * t, 1.0, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
 			} else {
 				o.coefficients[oj] = nanv;
 				o.std_errors[oj] = nanv;
 				o.t_values[oj] = nanv;
-				o.p_values[oj] = nanv;
 				o.ci_lower[oj] = nanv;
 				o.ci_upper[oj] = nanv;
+				if (ROWS)
+					v.pv[j] = nanv;
+				else
+					o.p_values[oj] = nanv;
 			}
 		}
 	}
-	if (q == (2 % T)) {
-		double fs = nanv, fp = nanv;
-		if (dfm > 0.0 && dfr > 0.0) {
-			fs = ((tss - rss) / dfm) / sigma2;
-			fp = f_upper_p_fast(fs, dfm, dfr, Tb);
-		}
+	if (q == (2 & (T - 1))) {
+		double fs = nanv;
+		if (dfm > 0.0 && dfr > 0.0) fs = ((tss - rss) / dfm) / sigma2;
 		o.f_statistic[g] = fs;
-		o.f_pvalue[g] = fp;
 		if (o.has_inference) o.has_inference[g] = 1;
+		if (ROWS) {
+			v.pv[P] = fs;
+			v.pv[P + 1] = dfm; // > 0 marks "p-values wanted" for this slot
+			v.pv[P + 2] = dfr;
+		} else {
+			o.f_pvalue[g] = pvalue_f(fs, dfm, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
+		}
 	}
 }
 
 // One round: lanes [sub*T, sub*T+T) own group `gi` of the stage (valid = false: idle lanes).
-template <int P, bool HASW, bool HAST>
+// Transposed moment record (element stride rs): same field order as the record of common.cuh, so that the
+// generic solve_group / refine_kernel can read it too. The sums are replicated in the T lanes of the group:
+// lane q stores the fields f with f % T == q.
+template <int P>
+__device__ __forceinline__ void small_store_record(const SmallMoments<P> &M, double sw, const double (&sh)[P + 1],
+                                                   unsigned nonconst, int n_state, double *__restrict__ rec, int64_t rs,
+                                                   int q, int T) {
+	constexpr int K = P + 1;
+	const int m = T - 1;
+	int f = 0;
+	auto put = [&](double val) {
+		if ((f & m) == q) rec[(int64_t)f * rs] = val;
+		++f;
+	};
+	put((double)M.nv);
+	put(sw);
+	put((double)n_state);
+	put(0.0);
+#pragma unroll
+	for (int c = 0; c < K; ++c) put(sh[c]);
+#pragma unroll
+	for (int c = 0; c < P; ++c) put(((nonconst >> c) & 1u) ? 1.0 : 0.0); // cdev: only "< 1e-10" is ever asked
+#pragma unroll
+	for (int c = 0; c < K; ++c) put(M.s1[c]);
+#pragma unroll
+	for (int i = 0; i < SmallMoments<P>::NS2; ++i) put(M.s2[i]);
+}
+
+template <int P, bool HASW, bool HAST, bool FUSED>
 __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, const FitParams &Pm,
-                                            const AnofoxB200FitOutputs &o) {
+                                            const AnofoxB200FitOutputs &o, double *records, int64_t n_groups) {
 	constexpr int K = P + 1;
 	SmallMoments<P> M;
 	double sh[K];
@@ -529,7 +577,50 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 			nonconst |= nc ? (1u << c) : 0u;
 		}
 	}
-	small_solve<P, HASW, HAST>(M, sh, nonconst, n_state, g, Pm, o, v);
+	if (FUSED)
+		small_solve<P, HASW, HAST, true>(M, sh, nonconst, n_state, g, Pm, o, v);
+	else
+		small_store_record<P>(M, HASW ? M.sw : (double)M.nv, sh, nonconst, n_state, records + g, n_groups, v.q, v.T);
+}
+
+// One thread per group: moments from the transposed record (coalesced: consecutive lanes read consecutive
+// groups of the same field), then the same solve as the fused kernel with every array in registers.
+template <int P>
+__global__ void __launch_bounds__(128) solve_small_kernel(const double *__restrict__ records, int64_t n_groups, FitParams Pm,
+                                                          AnofoxB200FitOutputs o, int *refine_count,
+                                                          int64_t *refine_list) {
+	constexpr int K = P + 1;
+	const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= n_groups) return;
+	const double *rec = records + g;
+	const int64_t rs = n_groups;
+	SmallMoments<P> M;
+	double sh[K];
+	int f = 0;
+	auto get = [&]() { return __ldcs(rec + (int64_t)(f++) * rs); };
+	M.nv = (int)get();
+	M.sw = get();
+	const int n_state = (int)get();
+	get();
+#pragma unroll
+	for (int c = 0; c < K; ++c) sh[c] = get();
+	unsigned nonconst = 0u;
+#pragma unroll
+	for (int c = 0; c < P; ++c) nonconst |= !(get() < 1e-10) ? (1u << c) : 0u;
+#pragma unroll
+	for (int c = 0; c < K; ++c) M.s1[c] = get();
+#pragma unroll
+	for (int i = 0; i < SmallMoments<P>::NS2; ++i) M.s2[i] = get();
+	M.ns = n_state;
+	SmallGroupView v;
+	v.n = 0;
+	v.q = 0;
+	v.T = 1;
+	v.mask = 0u;
+	v.pv = nullptr;
+	v.refine_count = refine_count;
+	v.refine_list = refine_list;
+	small_solve<P, false, false, false>(M, sh, nonconst, n_state, g, Pm, o, v);
 }
 
 constexpr int kSmallStageGroups = 64; // groups per stage of the fused kernel at most (two rounds of 32)
@@ -544,11 +635,13 @@ struct SmallArgs {
 	int max_stage_groups;
 };
 
-template <int P, int NCW, bool HASW, bool HAST>
+template <int P, int NCW, bool HASW, bool HAST, bool FUSED>
 __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const SmallArgs args) {
 	extern __shared__ __align__(128) unsigned char smem[];
 	__shared__ uint64_t full_bar[kSmallMaxStages], empty_bar[kSmallMaxStages];
 	__shared__ SmallStageHeader hdr[kSmallMaxStages];
+	constexpr int PVW = P + 3;                   // per slot: f[P] (t^2), F, d1 (0 = nothing to do), d2
+	__shared__ double pv_scratch[NCW][8 * PVW];  // at most 8 groups per warp round (T >= 4)
 	const AccArgs &a = args.acc;
 	const int NS = a.n_stages;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -565,12 +658,17 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 		return;
 	}
 	const int T = args.lanes_per_group;
-	const int gpw = 32 / T; // groups per warp round
-	const int sub = lane / T, q = lane - sub * T;
+	const int lt = 31 - __clz(T);      // log2 T
+	const int gpw = 32 >> lt, lg = 5 - lt; // groups per warp round and its log2
+	const int sub = lane >> lt, q = lane & (T - 1);
 	const unsigned gmask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << (sub * T);
-	for (int it = 0;; ++it) {
-		const int s = it % NS;
-		mbar_wait(&full_bar[s], (uint32_t)((it / NS) & 1));
+	double *pvw = pv_scratch[warp - 1];
+	const bool want_p = FUSED && args.params.compute_inference && args.out.std_errors;
+	const DfTables Tb{args.params.tcrit, args.params.gratio, args.params.rcp, args.params.ce, args.params.co};
+	int s = 0;
+	uint32_t ph = 0;
+	for (;;) {
+		mbar_wait(&full_bar[s], ph);
 		const int cnt = hdr[s].count;
 		if (cnt < 0) break;
 		unsigned char *base = smem + (size_t)s * a.stage_bytes;
@@ -579,14 +677,16 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 		const uint32_t aw = HASW ? smem_u32(base + a.xcap + a.ycap + hdr[s].lead_w) : 0u;
 		const uint32_t at = HAST ? smem_u32(base + a.xcap + a.ycap + a.wcap + hdr[s].lead_t) : 0u;
 		const int64_t g0 = hdr[s].g_first;
-		const int nrounds = (cnt + gpw - 1) / gpw;
+		const int nrounds = (cnt + gpw - 1) >> lg;
 		for (;;) {
 			if (*(volatile int *)&hdr[s].next >= nrounds) break; // nothing left to claim: skip the atomic
 			int r = 0;
 			if (lane == 0) r = atomicAdd(&hdr[s].next, 1);
 			r = __shfl_sync(0xffffffffu, r, 0);
 			if (r >= nrounds) break;
-			const int gi = r * gpw + sub;
+			const int gi = (r << lg) + sub;
+			if (want_p && q == 0) pvw[sub * PVW + P + 1] = 0.0;
+			__syncwarp();
 			if (gi < cnt) {
 				const int rb = (int)hdr[s].rowstart[gi];
 				SmallGroupView v;
@@ -594,17 +694,43 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 				v.q = q;
 				v.T = T;
 				v.mask = gmask;
+				v.pv = pvw + sub * PVW;
+				v.refine_count = nullptr;
+				v.refine_list = nullptr;
 				v.sg.x = ax + (uint32_t)rb * (uint32_t)(P * 8);
 				v.sg.y = ay + (uint32_t)rb * 8u;
 				v.sg.w = aw + (uint32_t)rb * 8u;
 				v.sg.t = at + (uint32_t)rb;
 				v.sg.kone = v.sg.kzero = 0u;
-				small_group<P, HASW, HAST>(v, g0 + gi, args.params, args.out);
+				small_group<P, HASW, HAST, FUSED>(v, g0 + gi, args.params, args.out, a.records, a.n_groups);
 			}
 			__syncwarp();
+			if (want_p) {
+				// the round's p-values: (P + 1) per group, spread over all 32 lanes. The t tests are the F(1, df)
+				// upper tail of t^2, so every lane runs the same function.
+				const int total = gpw * (P + 1);
+				for (int e = lane; e < total; e += 32) {
+					const int slot = e / (P + 1), item = e - slot * (P + 1);
+					const double *pv = pvw + slot * PVW;
+					const double d1 = pv[P + 1];
+					if (d1 > 0.0) {
+						const double pval = pvalue_f(pv[item], item < P ? 1.0 : d1, pv[P + 2], Tb);
+						const int64_t g = g0 + (r << lg) + slot;
+						if (item < P)
+							args.out.p_values[g * P + item] = pval;
+						else
+							args.out.f_pvalue[g] = pval;
+					}
+				}
+				__syncwarp();
+			}
 		}
 		__syncwarp();
 		if (lane == 0) mbar_arrive(&empty_bar[s]);
+		if (++s == NS) {
+			s = 0;
+			ph ^= 1u;
+		}
 	}
 }
 

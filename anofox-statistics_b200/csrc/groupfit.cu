@@ -87,6 +87,7 @@ struct RefineArgs {
 	const double *y, *x, *w;
 	const uint8_t *train;
 	const double *records;
+	int64_t rec_gs, rec_es; // record element (g, i) at records[g * rec_gs + i * rec_es]
 	const int *refine_count;
 	const int64_t *refine_list;
 };
@@ -120,7 +121,7 @@ __global__ void __launch_bounds__(256) refine_kernel(RefineArgs a, FitParams P, 
 			}
 		}
 		for (int off = 16; off; off >>= 1) rss += __shfl_xor_sync(0xffffffffu, rss, off);
-		if (lane == 0) solve_group<PMAX>(a.records + g * rec_len(p), 1, g, P, o, rss, nullptr, nullptr, nullptr);
+		if (lane == 0) solve_group<PMAX>(a.records + g * a.rec_gs, a.rec_es, g, P, o, rss, nullptr, nullptr, nullptr);
 	}
 }
 
@@ -353,17 +354,34 @@ static cudaError_t launch_solve_list(const double *records, const int64_t *list,
 	return cudaGetLastError();
 }
 
-static cudaError_t launch_small(const SmallArgs &a, bool has_w, bool has_t, int grid, cudaStream_t st) {
+static cudaError_t launch_small(const SmallArgs &a, bool fused, bool has_w, bool has_t, int grid, cudaStream_t st) {
 	cudaError_t e = cudaErrorInvalidValue;
 	switch (a.acc.p) {
-	case 1: e = launch_small_p1(has_w, has_t, a, grid, st); break;
-	case 2: e = launch_small_p2(has_w, has_t, a, grid, st); break;
-	case 3: e = launch_small_p3(has_w, has_t, a, grid, st); break;
-	case 4: e = launch_small_p4(has_w, has_t, a, grid, st); break;
-	case 5: e = launch_small_p5(has_w, has_t, a, grid, st); break;
-	case 6: e = launch_small_p6(has_w, has_t, a, grid, st); break;
-	case 7: e = launch_small_p7(has_w, has_t, a, grid, st); break;
-	case 8: e = launch_small_p8(has_w, has_t, a, grid, st); break;
+	case 1: e = launch_small_p1(fused, has_w, has_t, a, grid, st); break;
+	case 2: e = launch_small_p2(fused, has_w, has_t, a, grid, st); break;
+	case 3: e = launch_small_p3(fused, has_w, has_t, a, grid, st); break;
+	case 4: e = launch_small_p4(fused, has_w, has_t, a, grid, st); break;
+	case 5: e = launch_small_p5(fused, has_w, has_t, a, grid, st); break;
+	case 6: e = launch_small_p6(fused, has_w, has_t, a, grid, st); break;
+	case 7: e = launch_small_p7(fused, has_w, has_t, a, grid, st); break;
+	case 8: e = launch_small_p8(fused, has_w, has_t, a, grid, st); break;
+	}
+	LAUNCHED();
+	return e;
+}
+static cudaError_t launch_solve_small(const double *records, int64_t G, const FitParams &P, const AnofoxB200FitOutputs &o,
+                                      int *refine_count, int64_t *refine_list, cudaStream_t st) {
+	if (G <= 0) return cudaSuccess;
+	cudaError_t e = cudaErrorInvalidValue;
+	switch (P.p) {
+	case 1: e = launch_solve_small_p1(records, G, P, o, refine_count, refine_list, st); break;
+	case 2: e = launch_solve_small_p2(records, G, P, o, refine_count, refine_list, st); break;
+	case 3: e = launch_solve_small_p3(records, G, P, o, refine_count, refine_list, st); break;
+	case 4: e = launch_solve_small_p4(records, G, P, o, refine_count, refine_list, st); break;
+	case 5: e = launch_solve_small_p5(records, G, P, o, refine_count, refine_list, st); break;
+	case 6: e = launch_solve_small_p6(records, G, P, o, refine_count, refine_list, st); break;
+	case 7: e = launch_solve_small_p7(records, G, P, o, refine_count, refine_list, st); break;
+	case 8: e = launch_solve_small_p8(records, G, P, o, refine_count, refine_list, st); break;
 	}
 	LAUNCHED();
 	return e;
@@ -457,7 +475,9 @@ static StageGeom stage_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 
 // Fused small-group path (fused_small.cuh): used when p <= 8 and the mean group is small enough for
 // many groups to be resident per SM. T lanes per group keep >= ~8 warps' worth of groups on chip.
-static std::atomic<int> g_force_path{0}; // 0 = auto, 1 = always the record path (tests / A-B runs)
+// 0 = auto (small groups: accumulate-to-record kernel + register solve kernel), 1 = always the DMMA record
+// path, 2 = small groups through the single fused kernel (tests / A-B runs)
+static std::atomic<int> g_force_path{0};
 struct SmallGeom {
 	bool use;
 	int T, max_groups;
@@ -539,13 +559,15 @@ static int get_tables(double level, cudaStream_t st, DfTables &T, AnofoxError *e
 	std::lock_guard<std::mutex> lock(c.mu);
 	int dev = 0;
 	cudaGetDevice(&dev);
-	const size_t n1 = kTcritTable + 1, n3 = kRcpTable + 1;
+	const size_t n1 = kTcritTable + 1, n3 = kRcpTable + 1, n4 = kSeriesTable;
 	for (auto &e : c.entries)
 		if (e.device == dev && (e.level == level || (std::isnan(e.level) && std::isnan(level)))) {
 			CU(cudaStreamWaitEvent(st, e.ready, 0), "cudaStreamWaitEvent");
 			T.tcrit = e.buf;
 			T.gratio = e.buf + n1;
 			T.rcp = e.buf + 2 * n1;
+			T.ce = e.buf + 2 * n1 + n3;
+			T.co = e.buf + 2 * n1 + n3 + n4;
 			return 0;
 		}
 	if (c.entries.size() >= 64) { // unbounded growth guard: drop everything (after the device drains)
@@ -560,9 +582,10 @@ static int get_tables(double level, cudaStream_t st, DfTables &T, AnofoxError *e
 	e.device = dev;
 	e.level = level;
 	e.buf = nullptr;
-	CU(cudaMalloc(&e.buf, (2 * n1 + n3) * sizeof(double)), "cudaMalloc tables");
+	CU(cudaMalloc(&e.buf, (2 * n1 + n3 + 2 * n4) * sizeof(double)), "cudaMalloc tables");
 	CU(cudaEventCreateWithFlags(&e.ready, cudaEventDisableTiming), "cudaEventCreate");
-	df_tables_kernel<<<(unsigned)((n3 + 127) / 128), 128, 0, st>>>(level, e.buf, e.buf + n1, e.buf + 2 * n1);
+	df_tables_kernel<<<(unsigned)((n3 + 127) / 128), 128, 0, st>>>(level, e.buf, e.buf + n1, e.buf + 2 * n1,
+	                                                                e.buf + 2 * n1 + n3, e.buf + 2 * n1 + n3 + n4);
 	LAUNCHED();
 	CU(cudaGetLastError(), "df_tables_kernel");
 	CU(cudaEventRecord(e.ready, st), "cudaEventRecord");
@@ -570,6 +593,8 @@ static int get_tables(double level, cudaStream_t st, DfTables &T, AnofoxError *e
 	T.tcrit = e.buf;
 	T.gratio = e.buf + n1;
 	T.rcp = e.buf + 2 * n1;
+	T.ce = e.buf + 2 * n1 + n3;
+	T.co = e.buf + 2 * n1 + n3 + n4;
 	return 0;
 }
 
@@ -703,7 +728,7 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	P.lambda_scaling = opt->lambda_scaling;
 	P.level = opt->confidence_level;
 	P.alpha = opt->alpha;
-	P.tcrit = P.gratio = P.rcp = nullptr;
+	P.tcrit = P.gratio = P.rcp = P.ce = P.co = nullptr;
 	P.predict_mode = pred ? 1 : 0;
 	P.min_state_rows = min_state_rows;
 
@@ -714,6 +739,8 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		P.tcrit = T.tcrit;
 		P.gratio = T.gratio;
 		P.rcp = T.rcp;
+		P.ce = T.ce;
+		P.co = T.co;
 	}
 
 	const uint8_t *train_use = nullptr;
@@ -774,15 +801,18 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	a.n_stages = sg.n_stages;
 	const int grid = (int)std::min<int64_t>(di.sms, n_tiles);
 	timer_mark(st);
+	const bool fused = small.use && g_force_path.load() == 2;
+	const bool transposed = small.use && !fused; // record element (g, i) at records[g + i * G]
+	const int64_t rec_gs = transposed ? 1 : rec_len(p), rec_es = transposed ? G : 1;
 	if (small.use) {
-		// rows -> results in one kernel for every group that fits a stage
+		// fused: rows -> results in one kernel; otherwise rows -> transposed moment records
 		SmallArgs sa;
 		sa.acc = a;
 		sa.params = P;
 		sa.out = fo;
 		sa.lanes_per_group = small.T;
 		sa.max_stage_groups = small.max_groups;
-		CU(launch_small(sa, wuse != nullptr, train_use != nullptr, grid, st), "fit_small_kernel");
+		CU(launch_small(sa, fused, wuse != nullptr, train_use != nullptr, grid, st), "fit_small_kernel");
 	} else {
 		CU(launch_resident(a, grid, st), "acc_resident_kernel");
 	}
@@ -812,6 +842,8 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 			s.partials = ws.partials;
 			s.n_part = ws.n_part;
 			s.records = ws.records;
+			s.rec_gs = rec_gs;
+			s.rec_es = rec_es;
 			first_valid_kernel<<<nb, 32, 0, st>>>(s);
 			LAUNCHED();
 			CU(cudaGetLastError(), "first_valid_kernel");
@@ -824,12 +856,14 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		}
 	}
 
-	if (small.use) {
+	if (fused) {
 		if (nbig > 0) CU(launch_solve_list(ws.records, ws.big_list, nbig, P, fo, ws.refine_count, ws.refine_list, st), "solve_list_kernel");
+	} else if (transposed) {
+		CU(launch_solve_small(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_small_kernel");
 	} else {
 		CU(launch_solve(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_kernel");
 	}
-	if (!small.use || nbig > 0) {
+	if (!fused || nbig > 0) {
 		RefineArgs ra;
 		ra.offsets = offsets;
 		ra.y = y;
@@ -837,6 +871,8 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		ra.w = wuse;
 		ra.train = train_use;
 		ra.records = ws.records;
+		ra.rec_gs = rec_gs;
+		ra.rec_es = rec_es;
 		ra.refine_count = ws.refine_count;
 		ra.refine_list = ws.refine_list;
 		CU(launch_refine(ra, P, fo, di.sms, st), "refine_kernel");
@@ -1167,7 +1203,7 @@ static int eval_specfun_host(int mode, int n, const double *a, const double *b, 
 	CU(cudaMemcpyAsync(da, a, bytes, cudaMemcpyHostToDevice, st), "H2D");
 	CU(cudaMemcpyAsync(db, b, bytes, cudaMemcpyHostToDevice, st), "H2D");
 	if (c) CU(cudaMemcpyAsync(dc, c, bytes, cudaMemcpyHostToDevice, st), "H2D");
-	DfTables T{nullptr, nullptr, nullptr};
+	DfTables T{nullptr, nullptr, nullptr, nullptr, nullptr};
 	if (mode >= 3) {
 		rc = get_tables(0.95, st, T, err);
 		if (rc) return rc;
@@ -1437,6 +1473,8 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	s.partials = ws.partials;
 	s.n_part = ws.n_part;
 	s.records = ws.records;
+	s.rec_gs = rec_len(p);
+	s.rec_es = 1;
 	timer_mark(st);
 	CU(launch_stream(s, ws.n_part / kStreamWarps, st), "acc_stream_kernel");
 	timer_mark(st);
@@ -1482,7 +1520,7 @@ int32_t anofox_b200_solve_moments_device(const double *moments, const double *cd
 	P.lambda_scaling = options->lambda_scaling;
 	P.level = options->confidence_level;
 	P.alpha = options->alpha;
-	P.tcrit = P.gratio = P.rcp = nullptr; // one group: evaluate the distribution functions directly
+	P.tcrit = P.gratio = P.rcp = P.ce = P.co = nullptr; // one group: evaluate the distribution functions directly
 	P.predict_mode = 0;
 	P.min_state_rows = 2;
 	CU(launch_solve(rec, 1, P, *out, nullptr, nullptr, st), "solve_kernel");

@@ -289,7 +289,7 @@ __device__ void solve_group(const double *__restrict__ rec, int64_t rs, int64_t 
 
 	if (inf_arrays) {
 		if (o.has_inference) o.has_inference[g] = 1;
-		const DfTables T{P.tcrit, P.gratio, P.rcp};
+		const DfTables T{P.tcrit, P.gratio, P.rcp, P.ce, P.co};
 		double tcrit = nanv;
 		if (dfr > 0.0) {
 			int idf = (int)dfr;

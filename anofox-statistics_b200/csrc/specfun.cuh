@@ -125,66 +125,77 @@ __device__ inline double t_critical_dev(double level, double df) {
 
 // ---------------------------------------------------------------------------------------------
 // Fast paths for INTEGER degrees of freedom (every p-value of a fit has df = n - rank).
-// Three per-df tables are built once per confidence level (df_tables_kernel, cached by the host):
+// Tables built once per confidence level (df_tables_kernel, cached by the host):
 //   tcrit[df]  = t_{(1+level)/2, df}
 //   gratio[df] = Gamma((df+1)/2) / Gamma(df/2)
 //   rcp[m]     = 1 / m
-// With them I_x(df/2, 1/2) is either the classical finite trigonometric sum for the t CDF
-// (Abramowitz & Stegun 26.7.3-4: df/2 terms, used for the body of the distribution) or the
-// hypergeometric tail series x^a (1-x)^b / (a B(a,b)) * sum_n (a+b)_n / (a+1)_n x^n (relative
-// accuracy in the far tail, geometric convergence with ratio x). Every term costs one table load
-// and three multiply-adds instead of the ~6 divisions of a continued-fraction step.
+//   ce[i] = prod_{k=1..i} (2k-1)/(2k),  co[i] = prod_{k=1..i} 2k/(2k+1)      (level-independent)
+// ce / co are the coefficients of the binomial series (1-x)^(-1/2) = sum ce[j] x^j and of its
+// odd-df counterpart. With y = 1 - x = t^2/(df + t^2):
+//   df = 2m   : P(|T| > t) = 1 - sqrt(y) sum_{j<m} ce[j] x^j      = sqrt(y) sum_{j>=m} ce[j] x^j
+//   df = 2m+1 : P(|T| > t) = (2/pi)(atan2(sqrt x, sqrt y) - sqrt(xy) sum_{j<m} co[j] x^j)
+//                          = (2/pi) sqrt(xy) sum_{j>=m} co[j] x^j
+// i.e. the classical finite sum (A&S 26.7.3-4, used in the body of the distribution, m terms) and its
+// own remainder (all terms positive: full relative accuracy in the far tail, geometric convergence
+// with ratio x). Both are evaluated by Horner's rule straight from the coefficient table: one load
+// and one multiply-add per term, no division, no loop-carried exit test.
 // ---------------------------------------------------------------------------------------------
 constexpr int kRcpTable = 2 * kTcritTable + 1024;
+constexpr int kSeriesTerms = 500;                             // tail terms at most (x <= 0.85 needs 242)
+constexpr int kSeriesTable = kTcritTable / 2 + kSeriesTerms + 16; // ce / co entries
 
 struct DfTables {
 	const double *tcrit;
 	const double *gratio;
 	const double *rcp;
+	const double *ce;
+	const double *co;
 };
 
-__device__ inline double betai_half_tail_series(int nu, double x, double y, const DfTables &T) {
-	const double a = 0.5 * (double)nu;
-	const double pref = exp(a * log(x)) * sqrt(y) * T.gratio[nu] * (0.56418958354775628695 / a); // 1/sqrt(pi)
-	double u = 1.0, sum = 1.0;
-	int idx = nu + 2;
-	for (int n = 0; n < 500; ++n) {
-		u *= x * (1.0 - T.rcp[idx]);
-		idx += 2;
-		sum += u;
-		if (u < 1e-17 * sum) break;
+// sum_{n=0}^{N-1} tab[m+n] x^n
+__device__ __forceinline__ double horner_from(const double *__restrict__ tab, int m, int N, double x) {
+	const double *t = tab + m;
+	double acc = 0.0;
+	int n = N - 1;
+	for (; n >= 3; n -= 4) {
+		const double c0 = __ldg(t + n), c1 = __ldg(t + n - 1), c2 = __ldg(t + n - 2), c3 = __ldg(t + n - 3);
+		acc = fma(acc, x, c0);
+		acc = fma(acc, x, c1);
+		acc = fma(acc, x, c2);
+		acc = fma(acc, x, c3);
 	}
-	return pref * sum;
+	for (; n >= 0; --n) acc = fma(acc, x, __ldg(t + n));
+	return acc;
+}
+
+// Remainder series: I_x(nu/2, 1/2) = x^(nu/2) sqrt(y) {1 | 2/pi sqrt(x)... } sum_{n>=0} tab[m+n] x^n, lx = log x.
+__device__ inline double betai_half_tail_series(int nu, double x, double y, double lx, const DfTables &T) {
+	const int m = nu >> 1;
+	int N = (int)(-39.2 / lx) + 2; // x^N < 1e-17
+	if (N > kSeriesTerms) N = kSeriesTerms;
+	const double a = 0.5 * (double)nu;
+	const double xa = exp(a * lx);
+	if (nu & 1) return 0.63661977236758134308 * xa * sqrt(y) * horner_from(T.co, m, N, x);
+	return xa * sqrt(y) * horner_from(T.ce, m, N, x);
 }
 
 // I_x(nu/2, 1/2) = P(|T_nu| > t) with x = nu / (nu + t^2), y = 1 - x, nu integer in [1, kTcritTable].
 __device__ inline double betai_half_fast(int nu, double x, double y, const DfTables &T) {
 	if (!(x > 0.0)) return 0.0;
 	if (!(y > 0.0)) return 1.0;
-	if (x <= 0.6) return betai_half_tail_series(nu, x, y, T);
+	const double lx = log(x);
+	if (x <= 0.6) return betai_half_tail_series(nu, x, y, lx, T);
 	if (nu <= 400) {
 		const double s = sqrt(y), c = sqrt(x);
+		const int m = nu >> 1;
 		double p;
-		if (nu & 1) {
-			double o = 1.0, sum = nu > 1 ? 1.0 : 0.0;
-			const int jmax = (nu - 3) / 2;
-			for (int j = 1; j <= jmax; ++j) {
-				o *= x * (1.0 - T.rcp[2 * j + 1]);
-				sum += o;
-			}
-			p = 0.63661977236758134308 * (atan2(c, s) - s * c * sum); // 2/pi
-		} else {
-			double e = 1.0, sum = 1.0;
-			const int jmax = nu / 2 - 1;
-			for (int j = 1; j <= jmax; ++j) {
-				e *= x * (1.0 - T.rcp[2 * j]);
-				sum += e;
-			}
-			p = 1.0 - s * sum;
-		}
+		if (nu & 1)
+			p = 0.63661977236758134308 * (atan2(c, s) - (m > 0 ? s * c * horner_from(T.co, 0, m, x) : 0.0)); // 2/pi
+		else
+			p = 1.0 - s * horner_from(T.ce, 0, m, x);
 		if (p > 1e-4) return p; // 1 - A (df/2 rounded terms) keeps >= 11 digits
 	}
-	if (x <= 0.85) return betai_half_tail_series(nu, x, y, T);
+	if (x <= 0.85) return betai_half_tail_series(nu, x, y, lx, T);
 	return beta_inc(0.5 * (double)nu, 0.5, x, y);
 }
 
@@ -192,7 +203,7 @@ __device__ inline double t_two_sided_p_fast(double t, double df, const DfTables 
 	if (isnan(t) || !(df > 0.0)) return nan_f64();
 	if (isinf(t)) return 0.0;
 	const double t2 = t * t, den = df + t2;
-	if (T.rcp == nullptr || df > (double)kTcritTable || df != floor(df)) return beta_inc(0.5 * df, 0.5, df / den, t2 / den);
+	if (T.ce == nullptr || df > (double)kTcritTable || df != floor(df)) return beta_inc(0.5 * df, 0.5, df / den, t2 / den);
 	return betai_half_fast((int)df, df / den, t2 / den, T);
 }
 
@@ -205,18 +216,18 @@ __device__ inline double f_upper_p_fast(double f, double d1, double d2, const Df
 	if (isinf(f)) return 0.0;
 	const double den = d2 + d1 * f;
 	const double x = d2 / den, y = d1 * f / den;
-	if (T.rcp == nullptr || d2 > (double)kTcritTable || d2 != floor(d2) || d1 != floor(d1) || d1 > 1024.0)
+	if (T.ce == nullptr || d2 > (double)kTcritTable || d2 != floor(d2) || d1 != floor(d1) || d1 > 1024.0)
 		return beta_inc(0.5 * d2, 0.5 * d1, x, y);
 	const int nu = (int)d2, m = (int)d1;
 	const double a = 0.5 * d2;
-	const double xa = exp(a * log(x));
-	double acc, term;
+	double acc, term = 0.0;
 	int twob; // 2b of the term about to be added
 	if (m & 1) {
-		acc = betai_half_fast(nu, x, y, T);
-		term = xa * sqrt(y) * T.gratio[nu] * 1.12837916709551257390; // 2/sqrt(pi): T_{1/2}
+		acc = betai_half_fast(nu, x, y, T); // m == 1: the two-sided t test, f = t^2
+		if (m > 1) term = exp(a * log(x)) * sqrt(y) * T.gratio[nu] * 1.12837916709551257390; // 2/sqrt(pi): T_{1/2}
 		twob = 1;
 	} else {
+		const double xa = exp(a * log(x));
 		acc = xa;
 		term = xa * y * a; // T_1
 		twob = 2;
@@ -230,15 +241,28 @@ __device__ inline double f_upper_p_fast(double f, double d1, double d2, const Df
 	return fmin(acc, 1.0);
 }
 
+// The unified p-value entry point of the fit kernels: upper tail of F(d1, d2); the two-sided t test with df
+// degrees of freedom is pvalue_f(t^2, 1, df). Kept out of line: one copy of the (large) distribution code
+// per kernel instead of one per call site.
+static __device__ __noinline__ double pvalue_f(double f, double d1, double d2, const DfTables T) {
+	return f_upper_p_fast(f, d1, d2, T);
+}
+
 // One thread per table entry.
 static __global__ void df_tables_kernel(double level, double *__restrict__ tcrit, double *__restrict__ gratio,
-                                 double *__restrict__ rcp) {
+                                 double *__restrict__ rcp, double *__restrict__ ce, double *__restrict__ co) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i <= kRcpTable) rcp[i] = i > 0 ? 1.0 / (double)i : 0.0;
 	if (i <= kTcritTable) {
 		tcrit[i] = i == 0 ? nan_f64() : t_critical_dev(level, (double)i);
 		// Gamma((df+1)/2) / Gamma(df/2) = sqrt(pi) / B(df/2, 1/2)
 		gratio[i] = i == 0 ? 0.0 : 1.7724538509055160273 * exp(-lbeta_dev(0.5 * (double)i, 0.5));
+	}
+	if (i < kSeriesTable) {
+		// ce[i] = Gamma(i+1/2) / (sqrt(pi) i!) = 1 / (i B(i, 1/2));  co[i] = pi / ((2i+1) B(i+1/2, 1/2))
+		const double di = (double)i;
+		ce[i] = i == 0 ? 1.0 : exp(-lbeta_dev(di, 0.5)) / di;
+		co[i] = 3.14159265358979323846 * exp(-lbeta_dev(di + 0.5, 0.5)) / (2.0 * di + 1.0);
 	}
 }
 

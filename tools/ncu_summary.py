@@ -1,0 +1,43 @@
+#!/usr/bin/env python3
+"""Summarise an .ncu-rep here (no GPU): key raw metrics + instruction / stall-sample shares per source line.
+usage: tools/ncu_summary.py report.ncu-rep [top_n]"""
+import csv
+import io
+import subprocess
+import sys
+
+rep = sys.argv[1]
+top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+hdr, units, vals = rows[0], rows[1], rows[2]
+want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tensor_subpipe_dmma.avg.pct_of_peak_sustained_active", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "sm__cycles_elapsed.max", "sass__inst_executed_local_loads", "sass__inst_executed_local_stores",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+        "smsp__thread_inst_executed_per_inst_executed.ratio", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"]
+for h, u, v in zip(hdr, units, vals):
+    if h in want or ("pcsamp_warps_issue_stalled" in h and "not_issued" not in h):
+        print(f"{h:90s} {u:12s} {v}")
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"], capture_output=True, text=True).stdout
+agg, fileinfo = {}, None
+for r in csv.reader(io.StringIO(src)):
+    if len(r) >= 2 and r[0] == "File Path":
+        fileinfo = r[1].split("/")[-1]
+        continue
+    if len(r) < 8 or not r[0] or r[0] == "Line No" or r[2] != "-":
+        continue
+    try:
+        key = (fileinfo, int(r[0]), r[1].strip()[:80])
+        a = agg.get(key, (0, 0))
+        agg[key] = (a[0] + int(r[7]), a[1] + int(r[4]))
+    except ValueError:
+        pass
+tot = sum(v[0] for v in agg.values()) or 1
+ts = sum(v[1] for v in agg.values()) or 1
+print(f"\nwarp instructions {tot}, stall samples {ts}; top {top} source lines by instructions:")
+for k, v in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+    print(f"{v[0] / 1e6:9.2f}M {100 * v[0] / tot:5.1f}%  samples {100 * v[1] / ts:5.1f}%  {k[0]}:{k[1]}  {k[2]}")
