@@ -57,34 +57,21 @@ template <int MAXG> struct StageHeaderT {
 };
 using StageHeader = StageHeaderT<kMaxStageGroups>;
 
-// Copy `bytes` bytes from global `src` into the shared region `dst` (16-byte aligned) so that
-// byte e lands at dst + lead + e, lead = src & 15. The 16-byte aligned interior goes through one
-// bulk copy; the unaligned head / tail are moved with ELEM-sized plain loads by the warp.
-// Returns the number of bytes the bulk copy will deliver (for the mbarrier transaction count).
+// Copy `bytes` bytes from global `src` into the shared region `dst` (16-byte aligned) so that byte e lands
+// at dst + lead + e, lead = src & 15. ONE bulk copy moves the enclosing 16-byte aligned range
+// [src - lead, ceil16(src + bytes)): up to 15 bytes of the neighbouring elements on either side come
+// along (never across an allocation granule: device allocations are >= 256-byte aligned and sized), which
+// keeps the producer free of dependent patch loads. Returns the bytes the copy will deliver (for the
+// mbarrier transaction count).
 template <int ELEM>
 __device__ __forceinline__ uint32_t stage_fetch(unsigned char *dst, const unsigned char *src, int64_t bytes, int lane,
                                                 uint64_t *bar, int *lead_out) {
 	const uint32_t lead = (uint32_t)((uintptr_t)src & 15);
 	*lead_out = (int)lead;
 	if (bytes <= 0) return 0;
-	int64_t head = lead ? (int64_t)(16 - lead) : 0;
-	if (head > bytes) head = bytes;
-	int64_t mid = (bytes - head) & ~(int64_t)15;
-	int64_t tail = bytes - head - mid;
-	for (int64_t e = (int64_t)lane * ELEM; e < head; e += 32 * ELEM) {
-		if (ELEM == 8)
-			*(double *)(dst + lead + e) = *(const double *)(src + e);
-		else
-			dst[lead + e] = src[e];
-	}
-	for (int64_t e = (int64_t)lane * ELEM; e < tail; e += 32 * ELEM) {
-		if (ELEM == 8)
-			*(double *)(dst + lead + head + mid + e) = *(const double *)(src + head + mid + e);
-		else
-			dst[lead + head + mid + e] = src[head + mid + e];
-	}
-	if (mid > 0 && lane == 0) bulk_g2s(dst + lead + head, src + head, (uint32_t)mid, bar);
-	return (uint32_t)mid;
+	const uint32_t total = (uint32_t)((lead + bytes + 15) & ~(int64_t)15);
+	if (lane == 0) bulk_g2s(dst, src - lead, total, bar);
+	return total;
 }
 
 __device__ __forceinline__ double xor_sum4(double v) { // sum over the 4 lanes that share lane/4
@@ -529,22 +516,28 @@ template <bool HASW, bool HAST, class Hdr>
 __device__ __forceinline__ void producer_loop(const AccArgs &a, unsigned char *smem, uint64_t *full_bar,
                                               uint64_t *empty_bar, Hdr *hdr, int NS, int lane, int max_groups) {
 	const int p = a.p;
-	int it = 0;
+	int s = 0;
+	uint32_t ph = 0;
 	for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
 		int64_t g = a.tile_g0[t];
 		const int64_t gend = a.tile_g0[t + 1];
+		if (g >= gend) continue;
+		// offsets of the next stage's candidate groups are fetched one stage ahead (pf_*), so that the
+		// global-load latency overlaps the copy issue and the wait for a free stage
+		int64_t pf_row0 = a.offsets[g];
+		int64_t pf_oe = (g + lane < gend) ? a.offsets[g + lane + 1] : 0;
 		while (g < gend) {
-			const int s = it % NS;
-			const uint32_t ph = (uint32_t)((it / NS) & 1);
 			mbar_wait(&empty_bar[s], ph ^ 1u);
-			const int64_t row0 = a.offsets[g];
+			const int64_t row0 = pf_row0;
 			int cnt = 0;
 			int64_t row_end = row0;
-			bool closed = false;
+			bool closed = false, first = true;
 			while (!closed && g + cnt < gend && cnt < max_groups) {
 				const int64_t gi = g + cnt + lane;
 				const bool in = gi < gend && (cnt + lane) < max_groups;
-				const int64_t oe = in ? a.offsets[gi + 1] : row0;
+				int64_t oe = row0;
+				if (in) oe = first ? pf_oe : a.offsets[gi + 1];
+				first = false;
 				const bool fits = in && (oe - row0) <= (int64_t)a.cap_rows;
 				const unsigned m = __ballot_sync(0xffffffffu, fits);
 				const int nfit = (m == 0xffffffffu) ? 32 : (__ffs(~m) - 1);
@@ -560,8 +553,15 @@ __device__ __forceinline__ void producer_loop(const AccArgs &a, unsigned char *s
 					a.big_list[slot] = g;
 				}
 				g += 1;
+				if (g < gend) {
+					pf_row0 = a.offsets[g];
+					pf_oe = (g + lane < gend) ? a.offsets[g + lane + 1] : 0;
+				}
 				continue;
 			}
+			const int64_t g_next = g + cnt;
+			pf_row0 = row_end; // == offsets[g_next]
+			pf_oe = (g_next + lane < gend) ? a.offsets[g_next + lane + 1] : 0;
 			const int64_t rows = row_end - row0;
 			unsigned char *base = smem + (size_t)s * a.stage_bytes;
 			int lx = 0, ly = 0, lw = 0, lt = 0;
@@ -590,13 +590,15 @@ __device__ __forceinline__ void producer_loop(const AccArgs &a, unsigned char *s
 				else
 					mbar_arrive(&full_bar[s]);
 			}
-			g += cnt;
-			++it;
+			g = g_next;
+			if (++s == NS) {
+				s = 0;
+				ph ^= 1u;
+			}
 		}
 	}
 	// end marker
-	const int s = it % NS;
-	mbar_wait(&empty_bar[s], (uint32_t)(((it / NS) & 1) ^ 1));
+	mbar_wait(&empty_bar[s], ph ^ 1u);
 	if (lane == 0) {
 		hdr[s].count = -1;
 		mbar_arrive(&full_bar[s]);
@@ -796,9 +798,11 @@ static __global__ void reduce_partials_kernel(const StreamArgs a) {
 	double v;
 	if (i >= rec_off_shift(p) && i < rec_off_cdev(p)) {
 		v = a.shift[(int64_t)b * (p + 1) + (i - rec_off_shift(p))];
-	} else if (i >= rec_off_cdev(p) && i < rec_off_s1(p)) {
+	} else if (i >= rec_off_cdev(p) && i < rec_off_cdev(p) + p) {
 		v = 0.0;
 		for (int q = 0; q < a.n_part; ++q) v = fmax(v, part[(int64_t)q * L + i]);
+	} else if (i >= rec_off_cdev(p) && i < rec_off_s1(p)) {
+		v = 0.0; // pad
 	} else if (i == 3) {
 		v = 0.0;
 	} else {

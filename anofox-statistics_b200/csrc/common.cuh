@@ -14,15 +14,16 @@ namespace b200 {
 // the row the reference's constant-column test compares against, ols.rs:76-87).
 //   [0] n_valid   [1] sum w   [2] n_state (rows that entered the aggregate state)   [3] spare
 //   shift[k]      k = p + 1
-//   cdev[p]       max |x_j - shift_j| over valid rows
+//   cdev[p]       max |x_j - shift_j| over valid rows (then 0..3 pad fields)
 //   S1[k]         sum w d
 //   S2[k(k+1)/2]  sum w d d^T, packed upper triangle, row-major: (i,j), i <= j
 // n, sw, S1, S2 add across row shards that share a shift; cdev combines with max.
 // -------------------------------------------------------------------------------------------
 __host__ __device__ inline int rec_off_shift(int) { return 4; }
 __host__ __device__ inline int rec_off_cdev(int p) { return 4 + (p + 1); }
-__host__ __device__ inline int rec_off_s1(int p) { return 4 + (p + 1) + p; }
-__host__ __device__ inline int rec_off_s2(int p) { return 4 + (p + 1) + p + (p + 1); }
+// the sums S1 | S2 start at a multiple of 4 fields (the small-group kernel leaves sum j in lane j % 4)
+__host__ __device__ inline int rec_off_s1(int p) { return (4 + (p + 1) + p + 3) & ~3; }
+__host__ __device__ inline int rec_off_s2(int p) { return rec_off_s1(p) + (p + 1); }
 __host__ __device__ inline int rec_len(int p) { return rec_off_s2(p) + (p + 1) * (p + 2) / 2; }
 __host__ __device__ inline int tri_idx(int i, int j, int k) { return i * k - (i * (i - 1)) / 2 + (j - i); } // i <= j
 

@@ -132,6 +132,52 @@ template <int P, bool HASW, bool HAST> __device__ __forceinline__ void small_red
 	}
 }
 
+// Split reduction for the accumulate-to-record path. The record's sums (S1 | S2, NSUM of them) are not
+// needed in every lane, only stored once: after the butterfly steps that cross the 4-lane quads
+// (offsets >= 4, T > 4 only), the last two steps exchange HALVES, so that lane q ends up with the
+// complete sums j = 4k + (q & 3) in keep[k] -- the same shuffle count as a full butterfly but a
+// quarter of the stores afterwards, each with a compile-time field index.
+template <int P> struct SmallSplit {
+	static constexpr int K = P + 1;
+	static constexpr int NSUM = K + K * (K + 1) / 2;
+	static constexpr int NQ = (NSUM + 3) / 4;
+};
+template <int P> __device__ __forceinline__ double small_sum_at(const SmallMoments<P> &M, int j) {
+	return j < P + 1 ? M.s1[j] : M.s2[j - (P + 1)];
+}
+template <int P, bool HASW, bool HAST>
+__device__ __forceinline__ void small_reduce_split(SmallMoments<P> &M, int T, int q, unsigned mask,
+                                                   double (&keep)[SmallSplit<P>::NQ]) {
+	constexpr int K = P + 1;
+	constexpr int NSUM = SmallSplit<P>::NSUM, NQ = SmallSplit<P>::NQ;
+	for (int off = T >> 1; off >= 4; off >>= 1) {
+#pragma unroll
+		for (int i = 0; i < SmallMoments<P>::NS2; ++i) M.s2[i] += shfl_xor_f64(mask, M.s2[i], off);
+#pragma unroll
+		for (int i = 0; i < K; ++i) M.s1[i] += shfl_xor_f64(mask, M.s1[i], off);
+	}
+	for (int off = 1; off < T; off <<= 1) {
+		if (HASW) {
+			M.sw += shfl_xor_f64(mask, M.sw, off);
+#pragma unroll
+			for (int i = 0; i < P; ++i) M.q2[i] += shfl_xor_f64(mask, M.q2[i], off);
+		}
+		M.nv += __shfl_xor_sync(mask, M.nv, off);
+		if (HAST) M.ns += __shfl_xor_sync(mask, M.ns, off);
+	}
+	const bool b1 = (q & 2) != 0, b0 = (q & 1) != 0;
+#pragma unroll
+	for (int k = 0; k < NQ; ++k) {
+		const double v0 = small_sum_at<P>(M, 4 * k);
+		const double v1 = 4 * k + 1 < NSUM ? small_sum_at<P>(M, 4 * k + 1) : 0.0;
+		const double v2 = 4 * k + 2 < NSUM ? small_sum_at<P>(M, 4 * k + 2) : 0.0;
+		const double v3 = 4 * k + 3 < NSUM ? small_sum_at<P>(M, 4 * k + 3) : 0.0;
+		const double u0 = (b1 ? v2 : v0) + shfl_xor_f64(mask, b1 ? v0 : v2, 2);
+		const double u1 = (b1 ? v3 : v1) + shfl_xor_f64(mask, b1 ? v1 : v3, 2);
+		keep[k] = (b0 ? u1 : u0) + shfl_xor_f64(mask, b0 ? u0 : u1, 1);
+	}
+}
+
 // Shared-memory view of one round's group for this lane.
 struct SmallGroupView {
 	SmemGroup sg;
@@ -327,9 +373,9 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 			A[ltri(i, i)] = 0.0;
 			rinv[i] = 0.0;
 		} else {
-			const double l = sqrt(d);
-			A[ltri(i, i)] = l;
-			rinv[i] = 1.0 / l;
+			const double r = rsqrt(d);
+			A[ltri(i, i)] = d * r;
+			rinv[i] = r;
 			live |= 1u << i;
 			++rank;
 		}
@@ -476,20 +522,21 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 
 // One round: lanes [sub*T, sub*T+T) own group `gi` of the stage (valid = false: idle lanes).
 // Transposed moment record (element stride rs): same field order as the record of common.cuh, so that the
-// generic solve_group / refine_kernel can read it too. The sums are replicated in the T lanes of the group:
-// lane q stores the fields f with f % T == q.
+// generic solve_group / refine_kernel can read it too. Header fields (replicated in the lanes of the group)
+// are stored by lane f % 4; the sums come from small_reduce_split: lane q holds sum 4k + q in keep[k].
 template <int P>
-__device__ __forceinline__ void small_store_record(const SmallMoments<P> &M, double sw, const double (&sh)[P + 1],
-                                                   unsigned nonconst, int n_state, double *__restrict__ rec, int64_t rs,
-                                                   int q, int T) {
+__device__ __forceinline__ void small_store_record(const double (&keep)[SmallSplit<P>::NQ], int nv, double sw,
+                                                   const double (&sh)[P + 1], unsigned nonconst, int n_state,
+                                                   double *__restrict__ rec, int64_t rs, int q) {
 	constexpr int K = P + 1;
-	const int m = T - 1;
+	constexpr int NSUM = SmallSplit<P>::NSUM, NQ = SmallSplit<P>::NQ;
+	if (q >= 4) return; // lanes 4.. of a wider group hold copies
 	int f = 0;
 	auto put = [&](double val) {
-		if ((f & m) == q) rec[(int64_t)f * rs] = val;
+		if ((f & 3) == q) rec[(int64_t)f * rs] = val;
 		++f;
 	};
-	put((double)M.nv);
+	put((double)nv);
 	put(sw);
 	put((double)n_state);
 	put(0.0);
@@ -497,23 +544,43 @@ __device__ __forceinline__ void small_store_record(const SmallMoments<P> &M, dou
 	for (int c = 0; c < K; ++c) put(sh[c]);
 #pragma unroll
 	for (int c = 0; c < P; ++c) put(((nonconst >> c) & 1u) ? 1.0 : 0.0); // cdev: only "< 1e-10" is ever asked
+	double *recq = rec + (int64_t)(((4 + K + P + 3) & ~3) + q) * rs; // rec_off_s1(P) + q
 #pragma unroll
-	for (int c = 0; c < K; ++c) put(M.s1[c]);
-#pragma unroll
-	for (int i = 0; i < SmallMoments<P>::NS2; ++i) put(M.s2[i]);
+	for (int k = 0; k < NQ; ++k)
+		if (4 * k + 3 < NSUM || 4 * k + q < NSUM) recq[(int64_t)(4 * k) * rs] = keep[k];
 }
 
 template <int P, bool HASW, bool HAST, bool FUSED>
 __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, const FitParams &Pm,
                                             const AnofoxB200FitOutputs &o, double *records, int64_t n_groups) {
 	constexpr int K = P + 1;
+	constexpr int NQ = SmallSplit<P>::NQ;
 	SmallMoments<P> M;
+	double keep[NQ];
 	double sh[K];
 #pragma unroll
 	for (int c = 0; c < K; ++c) sh[c] = 0.0;
+#pragma unroll
+	for (int k = 0; k < NQ; ++k) keep[k] = 0.0;
 	const int n = v.n;
 	int n_state = n;
 	bool have = n > 0;
+	// reduce over the lanes of the group; true when a non-finite value poisoned the sums
+	auto reduce = [&]() {
+		bool bad = false;
+		if (FUSED) {
+			small_reduce<P, HASW, HAST>(M, v.T, v.mask);
+#pragma unroll
+			for (int c = 0; c < K; ++c) bad = bad || !finite_f64(M.s2[utri(c, c, K)]);
+		} else {
+			small_reduce_split<P, HASW, HAST>(M, v.T, v.q, v.mask, keep);
+#pragma unroll
+			for (int k = 0; k < NQ; ++k) bad = bad || !finite_f64(keep[k]);
+			bad = __any_sync(v.mask, bad);
+		}
+		if (HASW) bad = bad || !finite_f64(M.sw);
+		return bad;
+	};
 	// fast path: the shift row is the first row that passes the cheap mask (row 0 without masks)
 	int f = 0;
 	if (have && (HASW || HAST)) {
@@ -531,13 +598,8 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 		for (int c = 0; c < P; ++c) sh[c] = lds_f64(v.sg.x + (uint32_t)(f * P + c) * 8u);
 		sh[P] = lds_f64(v.sg.y + (uint32_t)f * 8u);
 		small_accumulate<P, HASW, HAST, false>(M, v.sg, n, v.q, v.T, sh);
-		small_reduce<P, HASW, HAST>(M, v.T, v.mask);
+		redo = reduce();
 		if (!(HASW || HAST)) M.nv = n;
-		bool bad = false;
-#pragma unroll
-		for (int c = 0; c < K; ++c) bad = bad || !finite_f64(M.s2[utri(c, c, K)]);
-		if (HASW) bad = bad || !finite_f64(M.sw);
-		redo = bad;
 	} else if (have) {
 		redo = true; // no row passes the mask: the checked path settles n_state / NO_VALID_DATA
 	}
@@ -553,7 +615,7 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 		} else if (HAST) {
 			for (int i = v.q; i < n; i += v.T) M.ns += lds_u8(v.sg.t + (uint32_t)i) != 0u ? 1 : 0;
 		}
-		small_reduce<P, HASW, HAST>(M, v.T, v.mask);
+		reduce();
 		if (f < 0) {
 #pragma unroll
 			for (int c = 0; c < K; ++c) sh[c] = 0.0;
@@ -564,23 +626,45 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 	// (max d^2 <= sum d^2 <= n max d^2); only the band in between needs the exact statistic.
 	unsigned nonconst = 0u;
 	if (M.nv > 0) {
+		unsigned bits = 0u; // low half: surely not constant; high half: in the band
 #pragma unroll
 		for (int c = 0; c < P; ++c) {
-			const double s = HASW ? M.q2[c] : M.s2[utri(c, c, K)];
-			bool nc;
-			if (s < 0.99e-20)
-				nc = false;
-			else if (s > 1.01e-20 * (double)M.nv)
-				nc = true;
-			else
-				nc = !(small_exact_cdev<P, HASW, HAST>(v, c, sh[c]) < 1e-10);
-			nonconst |= nc ? (1u << c) : 0u;
+			constexpr int dummy = 0;
+			(void)dummy;
+			const int jd = K + utri(c, c, K); // position of the diagonal sum in S1 | S2
+			double s;
+			bool mine = true;
+			if (HASW)
+				s = M.q2[c];
+			else if (FUSED)
+				s = M.s2[utri(c, c, K)];
+			else {
+				s = keep[jd >> 2];
+				mine = (v.q & 3) == (jd & 3);
+			}
+			if (mine) {
+				if (s > 1.01e-20 * (double)M.nv)
+					bits |= 1u << c;
+				else if (!(s < 0.99e-20))
+					bits |= 0x10000u << c;
+			}
+		}
+		if (!FUSED && !HASW) {
+			bits |= __shfl_xor_sync(v.mask, bits, 1);
+			bits |= __shfl_xor_sync(v.mask, bits, 2);
+		}
+		nonconst = bits & 0xffffu;
+		if (bits >> 16) {
+#pragma unroll
+			for (int c = 0; c < P; ++c)
+				if ((bits >> (16 + c)) & 1u)
+					nonconst |= !(small_exact_cdev<P, HASW, HAST>(v, c, sh[c]) < 1e-10) ? (1u << c) : 0u;
 		}
 	}
 	if (FUSED)
 		small_solve<P, HASW, HAST, true>(M, sh, nonconst, n_state, g, Pm, o, v);
 	else
-		small_store_record<P>(M, HASW ? M.sw : (double)M.nv, sh, nonconst, n_state, records + g, n_groups, v.q, v.T);
+		small_store_record<P>(keep, M.nv, HASW ? M.sw : (double)M.nv, sh, nonconst, n_state, records + g, n_groups, v.q);
 }
 
 // One thread per group: moments from the transposed record (coalesced: consecutive lanes read consecutive
@@ -607,6 +691,7 @@ __global__ void __launch_bounds__(128) solve_small_kernel(const double *__restri
 	unsigned nonconst = 0u;
 #pragma unroll
 	for (int c = 0; c < P; ++c) nonconst |= !(get() < 1e-10) ? (1u << c) : 0u;
+	f = rec_off_s1(P); // skip the pad fields
 #pragma unroll
 	for (int c = 0; c < K; ++c) M.s1[c] = get();
 #pragma unroll

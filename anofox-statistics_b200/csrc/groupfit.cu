@@ -212,8 +212,10 @@ __global__ void assemble_record_kernel(const double *__restrict__ moments, const
 			v = moments[i];
 		else if (i < rec_off_cdev(p))
 			v = shift[i - rec_off_shift(p)];
-		else if (i < rec_off_s1(p))
+		else if (i < rec_off_cdev(p) + p)
 			v = cdev[i - rec_off_cdev(p)];
+		else if (i < rec_off_s1(p))
+			v = 0.0;
 		else
 			v = moments[4 + (i - rec_off_s1(p))];
 		rec[i] = v;
@@ -227,8 +229,10 @@ __global__ void split_record_kernel(const double *__restrict__ rec, int p, doubl
 		if (i < 4)
 			moments[i] = (i == 3) ? 0.0 : v;
 		else if (i < rec_off_cdev(p)) {
-		} else if (i < rec_off_s1(p))
+		} else if (i < rec_off_cdev(p) + p)
 			cdev[i - rec_off_cdev(p)] = v;
+		else if (i < rec_off_s1(p)) {
+		}
 		else
 			moments[4 + (i - rec_off_s1(p))] = v;
 	}
@@ -463,9 +467,9 @@ static StageGeom stage_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	const int64_t overhead = 4 * 32; // alignment slack of the regions
 	g.cap_rows = (int)((stage - overhead) / row_bytes);
 	if (g.cap_rows < 4) g.cap_rows = 4;
-	g.xcap = align16((int64_t)g.cap_rows * p * 8 + 16);
-	g.ycap = align16((int64_t)g.cap_rows * 8 + 16);
-	g.wcap = has_w ? align16((int64_t)g.cap_rows * 8 + 16) : 0;
+	g.xcap = align16((int64_t)g.cap_rows * p * 8 + 32);
+	g.ycap = align16((int64_t)g.cap_rows * 8 + 32);
+	g.wcap = has_w ? align16((int64_t)g.cap_rows * 8 + 32) : 0;
 	g.tcap = has_t ? align16((int64_t)g.cap_rows + 32) : 0;
 	g.stage_bytes = (g.xcap + g.ycap + g.wcap + g.tcap + 127) & ~127;
 	while ((int64_t)g.n_stages * g.stage_bytes > budget + 8 * 1024 && g.n_stages > 2) --g.n_stages;
@@ -502,9 +506,9 @@ static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	if (cap * row_bytes < 8 * 1024) cap = 8 * 1024 / row_bytes;
 	StageGeom &g = r.sg;
 	g.cap_rows = (int)cap;
-	g.xcap = align16((int64_t)g.cap_rows * p * 8 + 16);
-	g.ycap = align16((int64_t)g.cap_rows * 8 + 16);
-	g.wcap = has_w ? align16((int64_t)g.cap_rows * 8 + 16) : 0;
+	g.xcap = align16((int64_t)g.cap_rows * p * 8 + 32);
+	g.ycap = align16((int64_t)g.cap_rows * 8 + 32);
+	g.wcap = has_w ? align16((int64_t)g.cap_rows * 8 + 32) : 0;
 	g.tcap = has_t ? align16((int64_t)g.cap_rows + 32) : 0;
 	g.stage_bytes = (g.xcap + g.ycap + g.wcap + g.tcap + 127) & ~127;
 	g.n_stages = (int)std::min<int64_t>(kSmallMaxStages, budget / g.stage_bytes);

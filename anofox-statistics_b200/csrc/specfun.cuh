@@ -142,7 +142,7 @@ __device__ inline double t_critical_dev(double level, double df) {
 // ---------------------------------------------------------------------------------------------
 constexpr int kRcpTable = 2 * kTcritTable + 1024;
 constexpr int kSeriesTerms = 500;                             // tail terms at most (x <= 0.85 needs 242)
-constexpr int kSeriesTable = kTcritTable / 2 + kSeriesTerms + 16; // ce / co entries
+constexpr int kSeriesTable = kTcritTable / 2 + kSeriesTerms + 32; // ce / co entries (+ Horner round-up slack)
 
 struct DfTables {
 	const double *tcrit;
@@ -152,50 +152,92 @@ struct DfTables {
 	const double *co;
 };
 
-// sum_{n=0}^{N-1} tab[m+n] x^n
+// sum_{n=0}^{N8-1} tab[m+n] x^n with N8 = N rounded up to a multiple of 8 (the extra terms are genuine
+// terms of the series, so rounding up only adds accuracy; the tables carry the slack).
 __device__ __forceinline__ double horner_from(const double *__restrict__ tab, int m, int N, double x) {
-	const double *t = tab + m;
+	const int N8 = (N + 7) & ~7;
+	const double *t = tab + m + N8;
 	double acc = 0.0;
-	int n = N - 1;
-	for (; n >= 3; n -= 4) {
-		const double c0 = __ldg(t + n), c1 = __ldg(t + n - 1), c2 = __ldg(t + n - 2), c3 = __ldg(t + n - 3);
-		acc = fma(acc, x, c0);
-		acc = fma(acc, x, c1);
-		acc = fma(acc, x, c2);
+	for (int n = N8; n > 0; n -= 8) {
+		t -= 8;
+		const double c7 = __ldg(t + 7), c6 = __ldg(t + 6), c5 = __ldg(t + 5), c4 = __ldg(t + 4);
+		const double c3 = __ldg(t + 3), c2 = __ldg(t + 2), c1 = __ldg(t + 1), c0 = __ldg(t);
+		acc = fma(acc, x, c7);
+		acc = fma(acc, x, c6);
+		acc = fma(acc, x, c5);
+		acc = fma(acc, x, c4);
 		acc = fma(acc, x, c3);
+		acc = fma(acc, x, c2);
+		acc = fma(acc, x, c1);
+		acc = fma(acc, x, c0);
 	}
-	for (; n >= 0; --n) acc = fma(acc, x, __ldg(t + n));
 	return acc;
 }
 
-// Remainder series: I_x(nu/2, 1/2) = x^(nu/2) sqrt(y) {1 | 2/pi sqrt(x)... } sum_{n>=0} tab[m+n] x^n, lx = log x.
-__device__ inline double betai_half_tail_series(int nu, double x, double y, double lx, const DfTables &T) {
+// sum_{n=0}^{N-1} tab[n] x^n, exactly N terms (the finite sums of the body of the distribution).
+__device__ __forceinline__ double horner_exact(const double *__restrict__ tab, int N, double x) {
+	const double *t = tab + N;
+	double acc = 0.0;
+	const int r = N & 7;
+	for (int i = 0; i < r; ++i) {
+		--t;
+		acc = fma(acc, x, __ldg(t));
+	}
+	for (int n = N - r; n > 0; n -= 8) {
+		t -= 8;
+		const double c7 = __ldg(t + 7), c6 = __ldg(t + 6), c5 = __ldg(t + 5), c4 = __ldg(t + 4);
+		const double c3 = __ldg(t + 3), c2 = __ldg(t + 2), c1 = __ldg(t + 1), c0 = __ldg(t);
+		acc = fma(acc, x, c7);
+		acc = fma(acc, x, c6);
+		acc = fma(acc, x, c5);
+		acc = fma(acc, x, c4);
+		acc = fma(acc, x, c3);
+		acc = fma(acc, x, c2);
+		acc = fma(acc, x, c1);
+		acc = fma(acc, x, c0);
+	}
+	return acc;
+}
+
+// x^m, m >= 0, by repeated squaring: <= 2 log2(m) multiplications, relative error ~ m ulp (m <= 2048).
+__device__ __forceinline__ double pow_int(double x, int m) {
+	double r = 1.0;
+	while (m > 0) {
+		if (m & 1) r *= x;
+		x *= x;
+		m >>= 1;
+	}
+	return r;
+}
+
+// Remainder series: I_x(nu/2, 1/2) = x^(nu/2) sqrt(y) {1 | 2/pi} sum_{n>=0} tab[m+n] x^n. c = sqrt(x).
+__device__ inline double betai_half_tail_series(int nu, double x, double y, double c, const DfTables &T) {
 	const int m = nu >> 1;
-	int N = (int)(-39.2 / lx) + 2; // x^N < 1e-17
+	// terms until x^N < 1e-17: N = 39.2 / -ln x; single precision is plenty for a term count
+	int N = (int)(-39.2f / __logf(fmaxf((float)x, 1e-30f))) + 3;
 	if (N > kSeriesTerms) N = kSeriesTerms;
-	const double a = 0.5 * (double)nu;
-	const double xa = exp(a * lx);
-	if (nu & 1) return 0.63661977236758134308 * xa * sqrt(y) * horner_from(T.co, m, N, x);
-	return xa * sqrt(y) * horner_from(T.ce, m, N, x);
+	const double xm = pow_int(x, m);
+	if (nu & 1) return 0.63661977236758134308 * xm * c * sqrt(y) * horner_from(T.co, m, N, x);
+	return xm * sqrt(y) * horner_from(T.ce, m, N, x);
 }
 
 // I_x(nu/2, 1/2) = P(|T_nu| > t) with x = nu / (nu + t^2), y = 1 - x, nu integer in [1, kTcritTable].
 __device__ inline double betai_half_fast(int nu, double x, double y, const DfTables &T) {
 	if (!(x > 0.0)) return 0.0;
 	if (!(y > 0.0)) return 1.0;
-	const double lx = log(x);
-	if (x <= 0.6) return betai_half_tail_series(nu, x, y, lx, T);
+	const double c = sqrt(x);
+	if (x <= 0.6) return betai_half_tail_series(nu, x, y, c, T);
 	if (nu <= 400) {
-		const double s = sqrt(y), c = sqrt(x);
+		const double s = sqrt(y);
 		const int m = nu >> 1;
 		double p;
 		if (nu & 1)
-			p = 0.63661977236758134308 * (atan2(c, s) - (m > 0 ? s * c * horner_from(T.co, 0, m, x) : 0.0)); // 2/pi
+			p = 0.63661977236758134308 * (atan2(c, s) - (m > 0 ? s * c * horner_exact(T.co, m, x) : 0.0)); // 2/pi
 		else
-			p = 1.0 - s * horner_from(T.ce, 0, m, x);
+			p = 1.0 - s * horner_exact(T.ce, m, x);
 		if (p > 1e-4) return p; // 1 - A (df/2 rounded terms) keeps >= 11 digits
 	}
-	if (x <= 0.85) return betai_half_tail_series(nu, x, y, lx, T);
+	if (x <= 0.85) return betai_half_tail_series(nu, x, y, c, T);
 	return beta_inc(0.5 * (double)nu, 0.5, x, y);
 }
 
@@ -224,10 +266,13 @@ __device__ inline double f_upper_p_fast(double f, double d1, double d2, const Df
 	int twob; // 2b of the term about to be added
 	if (m & 1) {
 		acc = betai_half_fast(nu, x, y, T); // m == 1: the two-sided t test, f = t^2
-		if (m > 1) term = exp(a * log(x)) * sqrt(y) * T.gratio[nu] * 1.12837916709551257390; // 2/sqrt(pi): T_{1/2}
+		if (m > 1) { // x^a sqrt(y) Gamma(a + 1/2) / (Gamma(a) Gamma(3/2)): T_{1/2}
+			const double xa = (nu & 1) ? pow_int(x, nu >> 1) * sqrt(x) : pow_int(x, nu >> 1);
+			term = xa * sqrt(y) * T.gratio[nu] * 1.12837916709551257390; // 2/sqrt(pi)
+		}
 		twob = 1;
 	} else {
-		const double xa = exp(a * log(x));
+		const double xa = (nu & 1) ? pow_int(x, nu >> 1) * sqrt(x) : pow_int(x, nu >> 1);
 		acc = xa;
 		term = xa * y * a; // T_1
 		twob = 2;

@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Summarise an .ncu-rep here (no GPU): key raw metrics + instruction / stall-sample shares per source line.
-usage: tools/ncu_summary.py report.ncu-rep [top_n]"""
+usage: tools/ncu_summary.py report.ncu-rep [top_n] [kernel-name-regex]"""
 import csv
 import io
 import subprocess
@@ -8,9 +8,11 @@ import sys
 
 rep = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+ksel = ["--kernel-name", "regex:" + sys.argv[3]] if len(sys.argv) > 3 else []
+raw = subprocess.run(["ncu", "-i", rep] + ksel + ["--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, vals = rows[0], rows[1], rows[2]
+print("kernel:", vals[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "?")
 want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
         "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
@@ -22,7 +24,7 @@ want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
 for h, u, v in zip(hdr, units, vals):
     if h in want or ("pcsamp_warps_issue_stalled" in h and "not_issued" not in h):
         print(f"{h:90s} {u:12s} {v}")
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"], capture_output=True, text=True).stdout
+src = subprocess.run(["ncu", "-i", rep] + ksel + ["--page", "source", "--print-source", "cuda,sass", "--csv"], capture_output=True, text=True).stdout
 agg, fileinfo = {}, None
 for r in csv.reader(io.StringIO(src)):
     if len(r) >= 2 and r[0] == "File Path":
