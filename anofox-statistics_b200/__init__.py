@@ -289,7 +289,7 @@ def fit_batch_host_into(offsets, y, x, w, out_struct, G, N, p, **opt):
 def force_path(path):
     """Test / A-B hook: "auto", "record" (always the DMMA accumulation kernel + solve kernel) or "fused"
     (small groups through the single rows-to-results kernel instead of accumulate + register solve)."""
-    load_library().anofox_b200_force_path({"auto": 0, "record": 1, "fused": 2}[path])
+    load_library().anofox_b200_force_path({"auto": 0, "record": 1, "fused": 2, "stages": 3}[path])
 
 
 def plan(G, N, p, has_w=False, has_train=False):

@@ -2,6 +2,7 @@
 // (acc_nt*.cu) so that the template instantiations compile in parallel.
 #pragma once
 #include "accumulate.cuh"
+#include "ring.cuh"
 
 namespace b200 {
 
@@ -10,7 +11,10 @@ constexpr int kStreamWarps = 8;
 #define B200_DECLARE_NT(NT_)                                                                                         \
 	cudaError_t launch_resident_nt##NT_(bool side, bool has_w, bool has_t, const AccArgs &a, int grid,               \
 	                                    cudaStream_t st);                                                            \
-	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st);
+	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st);                    \
+	cudaError_t launch_ring_nt##NT_(bool side, bool has_w, bool has_t, const RingArgs &a, int grid, size_t dyn,      \
+	                                cudaStream_t st);                                                                \
+	cudaError_t launch_redo_nt##NT_(bool side, const RingArgs &a, int grid, cudaStream_t st);
 B200_DECLARE_NT(1)
 B200_DECLARE_NT(2)
 B200_DECLARE_NT(3)
@@ -35,6 +39,16 @@ cudaError_t launch_resident_t(const AccArgs &a, int grid, cudaStream_t st) {
 	return cudaGetLastError();
 }
 
+template <int NT, bool SIDE, bool HASW, bool HAST>
+cudaError_t launch_ring_t(const RingArgs &a, int grid, size_t dyn, cudaStream_t st) {
+	constexpr int NCW = ring_warps(NT);
+	auto kern = acc_ring_kernel<NT, SIDE, NCW, HASW, HAST, ring_sets(NT)>;
+	cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+	if (e != cudaSuccess) return e;
+	kern<<<grid, 32 * (NCW + 1), dyn, st>>>(a);
+	return cudaGetLastError();
+}
+
 #define B200_DEFINE_NT(NT_)                                                                                          \
 	cudaError_t launch_resident_nt##NT_(bool side, bool has_w, bool has_t, const AccArgs &a, int grid,               \
 	                                    cudaStream_t st) {                                                           \
@@ -50,6 +64,27 @@ cudaError_t launch_resident_t(const AccArgs &a, int grid, cudaStream_t st) {
 		case 6: return launch_resident_t<NT_, true, W, true, false>(a, grid, st);                                    \
 		default: return launch_resident_t<NT_, true, W, true, true>(a, grid, st);                                    \
 		}                                                                                                            \
+	}                                                                                                                \
+	cudaError_t launch_ring_nt##NT_(bool side, bool has_w, bool has_t, const RingArgs &a, int grid, size_t dyn,      \
+	                                cudaStream_t st) {                                                               \
+		const int sel = (side ? 4 : 0) | (has_w ? 2 : 0) | (has_t ? 1 : 0);                                          \
+		switch (sel) {                                                                                               \
+		case 0: return launch_ring_t<NT_, false, false, false>(a, grid, dyn, st);                                    \
+		case 1: return launch_ring_t<NT_, false, false, true>(a, grid, dyn, st);                                     \
+		case 2: return launch_ring_t<NT_, false, true, false>(a, grid, dyn, st);                                     \
+		case 3: return launch_ring_t<NT_, false, true, true>(a, grid, dyn, st);                                      \
+		case 4: return launch_ring_t<NT_, true, false, false>(a, grid, dyn, st);                                     \
+		case 5: return launch_ring_t<NT_, true, false, true>(a, grid, dyn, st);                                      \
+		case 6: return launch_ring_t<NT_, true, true, false>(a, grid, dyn, st);                                      \
+		default: return launch_ring_t<NT_, true, true, true>(a, grid, dyn, st);                                      \
+		}                                                                                                            \
+	}                                                                                                                \
+	cudaError_t launch_redo_nt##NT_(bool side, const RingArgs &a, int grid, cudaStream_t st) {                       \
+		if (side)                                                                                                    \
+			redo_kernel<NT_, true><<<grid, 256, 0, st>>>(a);                                                         \
+		else                                                                                                         \
+			redo_kernel<NT_, false><<<grid, 256, 0, st>>>(a);                                                        \
+		return cudaGetLastError();                                                                                   \
 	}                                                                                                                \
 	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st) {                   \
 		if (side)                                                                                                    \

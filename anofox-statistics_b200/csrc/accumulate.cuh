@@ -359,10 +359,14 @@ __device__ __forceinline__ void lane_pointers(const SmemGroup &g, int p, int lan
 	}
 }
 
-template <int NT, bool SIDE, bool HASW, bool HAST, bool TAIL>
-__device__ __forceinline__ void fast_step(WarpAcc<NT, SIDE> &A, uint32_t (&pa)[NT], const uint32_t (&st)[NT],
-                                          uint32_t &py, uint32_t &pw, uint32_t &pt, const double (&sh)[NT], double shy,
-                                          bool in_range) {
+// c0 / c1: the DMMA accumulator set this step adds into (A's own, or one of the extra sets the ring kernel
+// rotates through to break the DMMA -> DMMA dependency between consecutive steps).
+// TRACKNC: keep the exact per-element constant-column flag (one DSETP per tile and step).
+template <int NT, bool SIDE, bool HASW, bool HAST, bool TAIL, bool TRACKNC>
+__device__ __forceinline__ void mma_step(WarpAcc<NT, SIDE> &A, double (&c0)[NT * (NT + 1) / 2],
+                                         double (&c1)[NT * (NT + 1) / 2], uint32_t (&pa)[NT], const uint32_t (&st)[NT],
+                                         uint32_t &py, uint32_t &pw, uint32_t &pt, const double (&sh)[NT], double shy,
+                                         bool in_range) {
 	double v[NT];
 #pragma unroll
 	for (int t = 0; t < NT; ++t) {
@@ -396,7 +400,7 @@ __device__ __forceinline__ void fast_step(WarpAcc<NT, SIDE> &A, uint32_t (&pa)[N
 		double dv = v[t] - sh[t];
 		if (MASK) dv = ok ? dv : 0.0;
 		d[t] = dv;
-		A.nc[t] = A.nc[t] || (fabs(dv) >= 1e-10);
+		if (TRACKNC) A.nc[t] = A.nc[t] || (fabs(dv) >= 1e-10);
 		a[t] = HASW ? weff * dv : dv;
 	}
 	int pair = 0;
@@ -404,7 +408,7 @@ __device__ __forceinline__ void fast_step(WarpAcc<NT, SIDE> &A, uint32_t (&pa)[N
 	for (int ta = 0; ta < NT; ++ta)
 #pragma unroll
 		for (int tb = ta; tb < NT; ++tb) {
-			dmma_884(A.c0[pair], A.c1[pair], a[ta], d[tb]);
+			dmma_884(c0[pair], c1[pair], a[ta], d[tb]);
 			++pair;
 		}
 	if (SIDE) {
@@ -420,6 +424,13 @@ __device__ __forceinline__ void fast_step(WarpAcc<NT, SIDE> &A, uint32_t (&pa)[N
 		A.sy += wdy;
 		A.sw += weff;
 	}
+}
+
+template <int NT, bool SIDE, bool HASW, bool HAST, bool TAIL>
+__device__ __forceinline__ void fast_step(WarpAcc<NT, SIDE> &A, uint32_t (&pa)[NT], const uint32_t (&st)[NT],
+                                          uint32_t &py, uint32_t &pw, uint32_t &pt, const double (&sh)[NT], double shy,
+                                          bool in_range) {
+	mma_step<NT, SIDE, HASW, HAST, TAIL, true>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, in_range);
 }
 
 // Returns false when the result is poisoned (non-finite input somewhere) or no row passed the

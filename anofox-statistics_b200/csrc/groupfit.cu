@@ -323,6 +323,41 @@ static cudaError_t launch_stream(const StreamArgs &a, int grid, cudaStream_t st)
 	return e;
 }
 
+static cudaError_t launch_ring(const RingArgs &a, bool hw, bool ht, int grid, size_t dyn, cudaStream_t st) {
+	const Shape s = shape_of(a.p);
+	cudaError_t e = cudaErrorInvalidValue;
+	switch (s.nt) {
+	case 1: e = launch_ring_nt1(s.side, hw, ht, a, grid, dyn, st); break;
+	case 2: e = launch_ring_nt2(s.side, hw, ht, a, grid, dyn, st); break;
+	case 3: e = launch_ring_nt3(s.side, hw, ht, a, grid, dyn, st); break;
+	case 4: e = launch_ring_nt4(s.side, hw, ht, a, grid, dyn, st); break;
+	case 5: e = launch_ring_nt5(s.side, hw, ht, a, grid, dyn, st); break;
+	case 6: e = launch_ring_nt6(s.side, hw, ht, a, grid, dyn, st); break;
+	case 7: e = launch_ring_nt7(s.side, hw, ht, a, grid, dyn, st); break;
+	case 8: e = launch_ring_nt8(s.side, hw, ht, a, grid, dyn, st); break;
+	case 9: e = launch_ring_nt9(s.side, hw, ht, a, grid, dyn, st); break;
+	}
+	LAUNCHED();
+	return e;
+}
+static cudaError_t launch_redo(const RingArgs &a, int grid, cudaStream_t st) {
+	const Shape s = shape_of(a.p);
+	cudaError_t e = cudaErrorInvalidValue;
+	switch (s.nt) {
+	case 1: e = launch_redo_nt1(s.side, a, grid, st); break;
+	case 2: e = launch_redo_nt2(s.side, a, grid, st); break;
+	case 3: e = launch_redo_nt3(s.side, a, grid, st); break;
+	case 4: e = launch_redo_nt4(s.side, a, grid, st); break;
+	case 5: e = launch_redo_nt5(s.side, a, grid, st); break;
+	case 6: e = launch_redo_nt6(s.side, a, grid, st); break;
+	case 7: e = launch_redo_nt7(s.side, a, grid, st); break;
+	case 8: e = launch_redo_nt8(s.side, a, grid, st); break;
+	case 9: e = launch_redo_nt9(s.side, a, grid, st); break;
+	}
+	LAUNCHED();
+	return e;
+}
+
 static cudaError_t launch_solve(const double *records, int64_t G, const FitParams &P, const AnofoxB200FitOutputs &o,
                                 int *refine_count, int64_t *refine_list, cudaStream_t st) {
 	if (G <= 0) return cudaSuccess;
@@ -477,6 +512,73 @@ static StageGeom stage_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	return g;
 }
 
+// Ring path (ring.cuh): window size, ring depth, team size and the shared-memory map.
+struct RingGeom {
+	int win_rows, n_win, team, ncw;
+	uint32_t x_off, y_off, w_off, t_off, slot_off;
+	size_t dyn_bytes;
+	int64_t big_rows;
+};
+static RingGeom ring_geometry(int p, bool has_w, bool has_t, int64_t n_rows, int64_t n_groups, int grid, int team_override) {
+	const Shape sh = shape_of(p);
+	RingGeom g;
+	g.ncw = ring_warps(sh.nt);
+	const int qr = 4 * ring_sets(sh.nt);
+	const int nv = sh.nt * (sh.nt + 1) + (sh.side ? 2 * sh.nt + 3 : 0) + 3;
+	const int64_t row_bytes = 8 * (int64_t)(p + 1) + (has_w ? 8 : 0) + (has_t ? 1 : 0);
+	const int64_t budget = 200 * 1024;
+	int sr = (int)((16 * 1024 / row_bytes + 15) / 16 * 16);
+	if (sr < 32) sr = 32;
+	const double mean_rows = n_groups > 0 ? (double)n_rows / (double)n_groups : 1.0;
+	int tw = 1;
+	if (team_override > 0) {
+		tw = team_override;
+	} else {
+		while (g.ncw % (tw * 2) == 0 && mean_rows >= 64.0 * (tw * 2)) tw *= 2;
+	}
+	for (;;) {
+		const int64_t slot_bytes = (int64_t)(g.ncw / tw) * (tw - 1) * nv * 256;
+		const int64_t apron = (int64_t)kRingApron * row_bytes + 4 * 16 + 4 * 128;
+		int64_t ns = (budget - (team_override > 0 ? 0 : slot_bytes) - apron) / ((int64_t)sr * row_bytes);
+		if (ns > kRingMaxWin) ns = kRingMaxWin;
+		const bool ok = ns >= 4 && (int64_t)ns * sr >= 2 * (int64_t)tw * qr + 2 * sr && (team_override > 0 || slot_bytes <= 64 * 1024);
+		if (ok || (tw == 1 && team_override <= 0)) {
+			if (ns < 4) { // very wide rows cannot happen for p <= 64, but never hand the kernel fewer than 4 windows
+				sr = 32;
+				ns = 4;
+			}
+			g.n_win = (int)ns;
+			g.team = tw;
+			break;
+		}
+		if (team_override > 0) { // slice mode: shrink the windows instead of the team
+			sr = std::max(16, sr / 2 / 16 * 16);
+			continue;
+		}
+		tw /= 2;
+	}
+	g.win_rows = sr;
+	const int64_t ring_rows = (int64_t)g.win_rows * g.n_win;
+	auto a128 = [](int64_t v) { return (uint32_t)((v + 127) & ~(int64_t)127); };
+	uint32_t off = 0;
+	g.x_off = off;
+	off += a128((ring_rows + kRingApron) * p * 8 + 16);
+	g.y_off = off;
+	off += a128((ring_rows + kRingApron) * 8 + 16);
+	g.w_off = off;
+	if (has_w) off += a128((ring_rows + kRingApron) * 8 + 16);
+	g.t_off = off;
+	if (has_t) off += a128(ring_rows + kRingApron + 16);
+	g.slot_off = off;
+	if (team_override <= 0) off += a128((int64_t)(g.ncw / g.team) * (g.team - 1) * nv * 256);
+	g.dyn_bytes = off;
+	int64_t big = n_rows / (2 * (int64_t)std::max(grid, 1));
+	if (big < 8 * ring_rows) big = 8 * ring_rows;
+	if (big > (int64_t)1 << 30) big = (int64_t)1 << 30;
+	g.big_rows = big;
+	return g;
+}
+
 // Fused small-group path (fused_small.cuh): used when p <= 8 and the mean group is small enough for
 // many groups to be resident per SM. T lanes per group keep >= ~8 warps' worth of groups on chip.
 // 0 = auto (small groups: accumulate-to-record kernel + register solve kernel), 1 = always the DMMA record
@@ -493,7 +595,7 @@ static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	const int64_t row_bytes = 8 * (int64_t)(p + 1) + (has_w ? 8 : 0) + (has_t ? 1 : 0);
 	const double mean_rows = n_groups > 0 ? (double)n_rows / (double)n_groups : 0.0;
 	const double mean_bytes = mean_rows * (double)row_bytes;
-	r.use = g_force_path.load() != 1 && p <= kSmallMaxFeatures && n_groups > 0 && mean_bytes <= 24.0 * 1024.0;
+	r.use = g_force_path.load() != 1 && g_force_path.load() != 3 && p <= kSmallMaxFeatures && n_groups > 0 && mean_bytes <= 24.0 * 1024.0;
 	if (!r.use) return r;
 	int T = 4;
 	while (T < 32 && mean_bytes > 700.0 * T) T *= 2;
@@ -615,6 +717,8 @@ struct Workspace {
 	double *partials;
 	int64_t *refine_list;
 	int *refine_count;
+	int64_t *redo_list;
+	int *redo_count;
 	uint8_t *train_tmp;
 	// fit outputs used internally by the predict path when the caller passes none
 	double *f_coef, *f_icpt, *f_r2, *f_adj, *f_rse;
@@ -646,7 +750,7 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 	w.nbig_max = std::min<int64_t>(G, N / min_cap + 1);
 	w.n_part = sms * 2 * kStreamWarps;
 	w.records = (double *)take((size_t)std::max<int64_t>(G, 1) * L * 8);
-	w.tile_g0 = (int64_t *)take((size_t)(n_tiles + 2) * 8);
+	w.tile_g0 = (int64_t *)take((size_t)(std::max<int64_t>(n_tiles, sms) + 2) * 8);
 	w.big_list = (int64_t *)take((size_t)(w.nbig_max + 1) * 8);
 	w.big_count = (int *)take(256);
 	w.shift = (double *)take((size_t)(w.nbig_max + 1) * (p + 1) * 8);
@@ -657,6 +761,8 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 	w.partials = (double *)take((size_t)part_groups * w.n_part * L * 8);
 	w.refine_list = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
 	w.refine_count = (int *)take(256);
+	w.redo_list = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
+	w.redo_count = (int *)take(256);
 	w.train_tmp = (uint8_t *)take((size_t)std::max<int64_t>(N, 1));
 	w.f_coef = (double *)take((size_t)std::max<int64_t>(G, 1) * p * 8);
 	w.f_icpt = (double *)take((size_t)std::max<int64_t>(G, 1) * 8);
@@ -776,55 +882,98 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	}
 
 	const SmallGeom small = small_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
+	// 0 = auto, 1 = never the small-group kernels, 2 = fused small kernel, 3 = whole-group stages (the
+	// pre-ring DMMA kernel, kept for A/B runs)
+	const bool use_ring = !small.use && g_force_path.load() != 3;
 	const StageGeom sg = small.use ? small.sg : stage_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
-	const int64_t n_tiles = (N + sg.window_rows - 1) / sg.window_rows + 1; // +1: groups that start at row N
 	CU(cudaMemsetAsync(ws.big_count, 0, 256, st), "memset");
 	CU(cudaMemsetAsync(ws.refine_count, 0, 256, st), "memset");
-	tile_bounds_kernel<<<(unsigned)((n_tiles + 1 + 255) / 256), 256, 0, st>>>(offsets, G, sg.window_rows, n_tiles, ws.tile_g0);
-	LAUNCHED();
-	CU(cudaGetLastError(), "tile_bounds_kernel");
-
-	AccArgs a;
-	a.offsets = offsets;
-	a.y = y;
-	a.x = x;
-	a.w = wuse;
-	a.train = train_use;
-	a.n_groups = G;
-	a.p = p;
-	a.tile_g0 = ws.tile_g0;
-	a.n_tiles = n_tiles;
-	a.records = ws.records;
-	a.big_list = ws.big_list;
-	a.big_count = ws.big_count;
-	a.cap_rows = sg.cap_rows;
-	a.stage_bytes = sg.stage_bytes;
-	a.xcap = sg.xcap;
-	a.ycap = sg.ycap;
-	a.wcap = sg.wcap;
-	a.n_stages = sg.n_stages;
-	const int grid = (int)std::min<int64_t>(di.sms, n_tiles);
-	timer_mark(st);
+	CU(cudaMemsetAsync(ws.redo_count, 0, 256, st), "memset");
 	const bool fused = small.use && g_force_path.load() == 2;
 	const bool transposed = small.use && !fused; // record element (g, i) at records[g + i * G]
 	const int64_t rec_gs = transposed ? 1 : rec_len(p), rec_es = transposed ? G : 1;
-	if (small.use) {
-		// fused: rows -> results in one kernel; otherwise rows -> transposed moment records
-		SmallArgs sa;
-		sa.acc = a;
-		sa.params = P;
-		sa.out = fo;
-		sa.lanes_per_group = small.T;
-		sa.max_stage_groups = small.max_groups;
-		CU(launch_small(sa, fused, wuse != nullptr, train_use != nullptr, grid, st), "fit_small_kernel");
+	int64_t big_threshold = sg.cap_rows;
+	if (use_ring) {
+		// one contiguous range of groups per CTA, balanced by rows
+		const int grid = (int)std::min<int64_t>(di.sms, std::max<int64_t>(1, (N + 4095) / 4096));
+		const int64_t window_rows = std::max<int64_t>(1, (N + grid - 1) / grid);
+		tile_bounds_kernel<<<1, 256, 0, st>>>(offsets, G, window_rows, grid, ws.tile_g0);
+		LAUNCHED();
+		CU(cudaGetLastError(), "tile_bounds_kernel");
+		const RingGeom rg = ring_geometry(p, wuse != nullptr, train_use != nullptr, N, G, grid, 0);
+		RingArgs r;
+		r.offsets = offsets;
+		r.y = y;
+		r.x = x;
+		r.w = wuse;
+		r.train = train_use;
+		r.p = p;
+		r.tile_g0 = ws.tile_g0;
+		r.records = ws.records;
+		r.shift_common = nullptr;
+		r.big_list = ws.big_list;
+		r.big_count = ws.big_count;
+		r.big_rows = rg.big_rows;
+		r.redo_list = ws.redo_list;
+		r.redo_count = ws.redo_count;
+		r.win_rows = rg.win_rows;
+		r.n_win = rg.n_win;
+		r.team = rg.team;
+		r.x_off = rg.x_off;
+		r.y_off = rg.y_off;
+		r.w_off = rg.w_off;
+		r.t_off = rg.t_off;
+		r.slot_off = rg.slot_off;
+		big_threshold = rg.big_rows;
+		timer_mark(st);
+		CU(launch_ring(r, wuse != nullptr, train_use != nullptr, grid, rg.dyn_bytes, st), "acc_ring_kernel");
+		CU(launch_redo(r, di.sms * 2, st), "redo_kernel");
+		timer_mark(st);
 	} else {
-		CU(launch_resident(a, grid, st), "acc_resident_kernel");
+		const int64_t n_tiles = (N + sg.window_rows - 1) / sg.window_rows + 1; // +1: groups that start at row N
+		tile_bounds_kernel<<<(unsigned)((n_tiles + 1 + 255) / 256), 256, 0, st>>>(offsets, G, sg.window_rows, n_tiles, ws.tile_g0);
+		LAUNCHED();
+		CU(cudaGetLastError(), "tile_bounds_kernel");
+
+		AccArgs a;
+		a.offsets = offsets;
+		a.y = y;
+		a.x = x;
+		a.w = wuse;
+		a.train = train_use;
+		a.n_groups = G;
+		a.p = p;
+		a.tile_g0 = ws.tile_g0;
+		a.n_tiles = n_tiles;
+		a.records = ws.records;
+		a.big_list = ws.big_list;
+		a.big_count = ws.big_count;
+		a.cap_rows = sg.cap_rows;
+		a.stage_bytes = sg.stage_bytes;
+		a.xcap = sg.xcap;
+		a.ycap = sg.ycap;
+		a.wcap = sg.wcap;
+		a.n_stages = sg.n_stages;
+		const int grid = (int)std::min<int64_t>(di.sms, n_tiles);
+		timer_mark(st);
+		if (small.use) {
+			// fused: rows -> results in one kernel; otherwise rows -> transposed moment records
+			SmallArgs sa;
+			sa.acc = a;
+			sa.params = P;
+			sa.out = fo;
+			sa.lanes_per_group = small.T;
+			sa.max_stage_groups = small.max_groups;
+			CU(launch_small(sa, fused, wuse != nullptr, train_use != nullptr, grid, st), "fit_small_kernel");
+		} else {
+			CU(launch_resident(a, grid, st), "acc_resident_kernel");
+		}
+		timer_mark(st);
 	}
-	timer_mark(st);
 
 	// Big groups (rare): the count decides whether the streaming kernels run at all.
 	int nbig = 0;
-	if (N > sg.cap_rows) {
+	if (N > big_threshold) {
 		CU(cudaMemcpyAsync(&nbig, ws.big_count, sizeof(int), cudaMemcpyDeviceToHost, st), "read big_count");
 		CU(cudaStreamSynchronize(st), "sync");
 		for (int b0 = 0; b0 < nbig; b0 += 64) {

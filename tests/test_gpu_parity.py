@@ -23,7 +23,7 @@ def lib(b200):
     return b200
 
 
-@pytest.fixture(params=["auto", "record", "fused"])
+@pytest.fixture(params=["auto", "record", "fused", "stages"])
 def path(request, lib):
     """Both kernel paths: "auto" takes the fused small-group kernel where it applies (p <= 8, small groups),
     "record" forces the DMMA accumulation kernel + solve kernel everywhere."""
@@ -326,6 +326,74 @@ def test_batch_large_groups_take_the_streaming_path(lib, oracle, path):
     dev = lib.fit_batch_host(off, y, x, None, compute_inference=True)
     ora = oracle.fit_batch(off, y, x, None, compute_inference=True)
     assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label="p64")
+
+
+RING_CASES = [
+    # p, (n_lo, n_hi), G, method   -- group sizes chosen to exercise team sizes 1 .. 16 of the ring kernel
+    (3, (3000, 5000), 12, "ols"),
+    (8, (900, 1100), 40, "ols"),
+    (8, (100, 140), 200, "wls"),
+    (12, (500, 700), 40, "ols"),
+    (16, (180, 420), 120, "wls"),
+    (16, (150, 260), 150, "ridge"),
+    (23, (260, 300), 60, "ols"),
+    (33, (300, 500), 30, "ols"),
+    (64, (300, 600), 10, "ols"),
+]
+
+
+@pytest.mark.parametrize("p,nr,G,method", RING_CASES, ids=[f"{c[3]}-p{c[0]}-n{c[1][0]}" for c in RING_CASES])
+def test_ring_kernel_teams(lib, oracle, p, nr, G, method):
+    """The streaming ring kernel (ring.cuh): clean batches (no redo), masked rows (w <= 0, training flags),
+    a few non-finite values (redo list), empty groups between large ones."""
+    lib.force_path("record")
+    try:
+        rng = np.random.default_rng(4000 + p)
+        c = make_case(rng, G, nr[0], nr[1], p, dirty=False, weights=(method == "wls"))
+        opt = dict(method=method, compute_inference=True, alpha=1.0 if method == "ridge" else 0.0)
+        dev = lib.fit_batch_host(c["offsets"], c["y"], c["x"], c["w"], **opt)
+        ora = oracle.fit_batch(c["offsets"], c["y"], c["x"], c["w"], **opt)
+        assert (ora["status"] == 0).all()
+        assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label=f"ring clean p={p}")
+        # the same result wherever the batch starts (odd row offset -> misaligned bulk copies)
+        sub = slice(int(c["offsets"][1]), None)
+        off2 = c["offsets"][1:] - c["offsets"][1]
+        dev2 = lib.fit_batch_host(off2, c["y"][sub].copy(), c["x"][sub].copy(), None if c["w"] is None else c["w"][sub].copy(), **opt)
+        assert np.array_equal(dev2["coefficients"], dev["coefficients"][1:])
+        assert np.array_equal(dev2["p_values"], dev["p_values"][1:], equal_nan=True)
+        # masks, non-finite values, degenerate columns, empty groups
+        N = len(c["y"])
+        y, x = c["y"].copy(), c["x"].copy()
+        w = c["w"].copy() if c["w"] is not None else None
+        offs = c["offsets"].copy()
+        offs = np.concatenate([offs[:3], [offs[2]], offs[3:]])  # an empty group in the middle
+        g0, g1, g2 = int(offs[0]), int(offs[1]), int(offs[2])
+        x[g0, 0] = np.nan                     # first row of group 0 invalid
+        y[g1:g1 + 40] = np.nan                # the first 40 rows of group 1 are held out
+        x[g2:int(offs[4]), p - 1] = 2.5       # constant column
+        x[int(offs[5]):int(offs[6]), 0] = x[int(offs[5]), 0] + 1e-10 * np.sign(rng.normal(size=int(offs[6] - offs[5])))  # the 1e-10 band
+        if p >= 2:
+            x[int(offs[6]):int(offs[7]), 1] = 3.0 * x[int(offs[6]):int(offs[7]), 0] - 1.0
+        y[rng.integers(0, N, size=5)] = np.inf
+        if w is not None:
+            w[rng.integers(0, N, size=N // 20)] = 0.0
+            w[g2:g2 + 50] = -1.0
+        dev = lib.fit_batch_host(offs, y, x, w, **opt)
+        ora = oracle.fit_batch(offs, y, x, w, **opt)
+        assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label=f"ring dirty p={p}")
+        # fit-predict engine: training flags (HAST) with whole blocks of held-out rows
+        train = (rng.uniform(size=N) < 0.8).astype(np.uint8)
+        train[g0:g0 + 70] = 0
+        train[~np.isfinite(y)] = 0
+        popt = dict(method=method, confidence_level=0.95, alpha=1.0 if method == "ridge" else 0.0)
+        pd, fd = lib.fit_predict_batch_host(offs, y, x, w, train, **popt)
+        po, fo = oracle.fit_predict_batch(offs, y, x, w, train, **popt)
+        assert_fit_parity(fd, fo, rtol=1e-9, label=f"ring predict p={p}")
+        m = np.isfinite(po["yhat_upper"])
+        assert np.array_equal(np.isnan(pd["yhat_upper"]), np.isnan(po["yhat_upper"]))
+        assert (np.abs(pd["yhat_upper"][m] - po["yhat_upper"][m]) / np.maximum(np.abs(po["yhat"][m]), 1)).max() < 1e-9
+    finally:
+        lib.force_path("auto")
 
 
 def test_exact_fit_groups_use_the_residual_pass(lib, oracle, path):
