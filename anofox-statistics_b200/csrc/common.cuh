@@ -80,6 +80,36 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 	    "r"(parity), "r"(20000u) // suspend-time hint (ns): sleep in hardware instead of spinning
 	    : "memory");
 }
+__device__ __forceinline__ void mbar_wait_addr(uint32_t bar_addr, uint32_t parity) {
+	asm volatile(
+	    "{\n"
+	    " .reg .pred p;\n"
+	    "WAIT_%=:\n"
+	    " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+	    " @p bra DONE_%=;\n"
+	    " bra WAIT_%=;\n"
+	    "DONE_%=:\n"
+	    "}\n" ::"r"(bar_addr),
+	    "r"(parity), "r"(20000u)
+	    : "memory");
+}
+__device__ __forceinline__ void st_release_s64(long long *p, long long v) {
+	asm volatile("st.release.cta.shared.s64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_s32(int *p, int v) {
+	asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_volatile_s32(const int *p) {
+	int v;
+	asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+	return v;
+}
+__device__ __forceinline__ longlong2 ld_volatile_s64x2(const long long *p) {
+	longlong2 v;
+	asm volatile("ld.volatile.shared.v2.s64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(smem_u32(p)));
+	return v;
+}
+__device__ __forceinline__ void fence_acq_rel_cta() { asm volatile("fence.acq_rel.cta;" ::: "memory"); }
 // One contiguous global -> shared bulk copy (SASS: UBLKCP). dst/src 16-byte aligned, bytes % 16 == 0.
 __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
 	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(

@@ -93,8 +93,10 @@ __device__ __forceinline__ uint32_t ring_fetch(unsigned char *dst, const unsigne
 template <int NT, bool SIDE, int NCW, bool HASW, bool HAST, int NSET>
 __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) {
 	extern __shared__ __align__(128) unsigned char smem[];
-	__shared__ uint64_t full_bar[kRingMaxWin], empty_bar[kRingMaxWin];
+	__shared__ uint64_t full_bar[kRingMaxWin];
 	__shared__ uint64_t dep_bar[NCW], rel_bar[NCW];
+	__shared__ int issued_s; // windows the producer has issued so far
+	__shared__ __align__(16) long long pos_s[NCW + (NCW & 1)]; // per consumer warp: it will not read rows below this again
 	__shared__ double kconst[2];
 	constexpr int NTP = NT * (NT + 1) / 2;
 	constexpr int QR = 4 * NSET; // rows of a quad
@@ -106,8 +108,8 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 	if (threadIdx.x == 0) {
 		for (int s = 0; s < NS; ++s) {
 			mbar_init(&full_bar[s], 1);
-			mbar_init(&empty_bar[s], NCW);
 		}
+		for (int t = 0; t < NCW + (NCW & 1); ++t) pos_s[t] = t < NCW ? 0 : ((long long)1 << 62);
 		for (int t = 0; t < NCW; ++t) {
 			mbar_init(&dep_bar[t], TW > 1 ? TW - 1 : 1);
 			mbar_init(&rel_bar[t], 1);
@@ -115,6 +117,7 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 		mbar_fence_init();
 		kconst[0] = 1.0;
 		kconst[1] = 0.0;
+		issued_s = 0;
 	}
 	__syncthreads();
 	const int64_t ga = a.tile_g0[blockIdx.x], gb = a.tile_g0[blockIdx.x + 1];
@@ -140,9 +143,27 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 		const int64_t WBx = (int64_t)SR * esx, WBy = (int64_t)SR * 8, WBt = SR;
 		const int64_t ABx = kRingApron * esx + 16, ABy = kRingApron * 8 + 16, ABt = kRingApron + 16;
 		auto lo = [](int64_t v, int64_t cap) { return v < cap ? v : cap; };
+		int64_t minpos = 0;
 		for (int k = 0; k < nwin; ++k) {
 			const int s = k % NS;
-			if (k >= NS) mbar_wait(&empty_bar[s], (uint32_t)(((k / NS) - 1) & 1));
+			if (k >= NS) {
+				// the slot's previous copy has landed (also when nobody waited for it: skipped big groups) ...
+				mbar_wait(&full_bar[s], (uint32_t)(((k / NS) - 1) & 1));
+				// ... and every consumer warp has moved past the window it held
+				const int64_t need = (int64_t)(k - NS + 1) * SR;
+				while (minpos < need) {
+					long long m = (long long)1 << 62;
+#pragma unroll
+					for (int t = 0; t < NCW + (NCW & 1); t += 2) {
+						const longlong2 v = ld_volatile_s64x2(&pos_s[t]);
+						m = v.x < m ? v.x : m;
+						m = v.y < m ? v.y : m;
+					}
+					minpos = m;
+					if (minpos < need) __nanosleep(32);
+				}
+				fence_acq_rel_cta();
+			}
 			uint64_t *bar = &full_bar[s];
 			uint32_t tx = 0;
 			const int64_t kb = k;
@@ -160,7 +181,10 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 				mbar_arrive_expect_tx(bar, tx);
 			else
 				mbar_arrive(bar);
+			st_release_s32(&issued_s, k + 1);
 		}
+		// no copy may be in flight when the CTA retires
+		for (int k = nwin > NS ? nwin - NS : 0; k < nwin; ++k) mbar_wait(&full_bar[k % NS], (uint32_t)((k / NS) & 1));
 		return;
 	}
 
@@ -175,35 +199,42 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 	const uint32_t ws = HASW ? smem_u32(smem + a.w_off) + lw : 0u, ts = HAST ? smem_u32(smem + a.t_off) + lt : 0u;
 	const uint32_t kone = smem_u32(&kconst[0]), kzero = smem_u32(&kconst[1]);
 	const int L = rec_len(p);
-	// Window cursors, kept without divisions: kw = last window waited for (slot kw_s, parity kw_ph), rows
-	// [0, ready) have landed; kr = next window to hand back (slot kr_s), it lies entirely below row rel_edge.
-	int kw = -1, kw_s = -1, kr = 0, kr_s = 0;
-	uint32_t kw_ph = 0;
-	int64_t ready = 0, rel_edge = SR;
-	auto wait_next = [&]() {
-		++kw;
-		if (++kw_s == NS) {
-			kw_s = 0;
-			kw_ph ^= 1u;
+	// Window cursor, kept without divisions: kn = next window to wait for (slot kn_s, parity kn_ph), `edge` =
+	// its nominal end row (kn + 1) SR; rows [0, ready) have landed as far as this warp reads them. A warp waits
+	// only for the windows it reads; the windows of other teams' groups are stepped over without waiting.
+	int kn = 0, kn_s = 0, issued = 0;
+	uint32_t kn_ph = 0;
+	int64_t edge = SR, ready = -15;
+	const uint32_t full0 = smem_u32(&full_bar[0]);
+	auto advance = [&]() {
+		++kn;
+		if (++kn_s == NS) {
+			kn_s = 0;
+			kn_ph ^= 1u;
 		}
-		mbar_wait(&full_bar[kw_s], kw_ph);
+		edge += SR;
 		// a row's last byte may sit up to 15 bytes (<= 15 rows of the flag array) into the next window
-		ready = (kw == nwin - 1) ? ((int64_t)1 << 62) : (int64_t)(kw + 1) * SR - 15;
+		ready = (kn == nwin) ? ((int64_t)1 << 62) : edge - SR - 15;
 	};
 	// rows [0, need) of the CTA's range have landed
 	auto ensure = [&](int64_t need) {
-		while (need > ready) wait_next();
-	};
-	// this warp will not read rows < pos again: hand back the windows that lie entirely below
-	auto release = [&](int64_t pos) {
-		while (pos >= rel_edge && kr < nwin) {
-			if (kr > kw) wait_next();
-			__syncwarp();
-			if (lane == 0) mbar_arrive(&empty_bar[kr_s]);
-			++kr;
-			if (++kr_s == NS) kr_s = 0;
-			rel_edge += SR;
+		while (need > ready) {
+			// a warp that stepped over other teams' windows may be more than a lap ahead of the producer: the
+			// parity wait is only meaningful once window kn itself has been issued
+			while (issued <= kn) {
+				issued = ld_volatile_s32(&issued_s);
+				if (issued <= kn) __nanosleep(64);
+			}
+			mbar_wait_addr(full0 + 8u * (uint32_t)kn_s, kn_ph);
+			advance();
 		}
+	};
+	// this warp will not read rows < pos again: step over the windows that lie entirely below and publish the
+	// position (the producer refills a slot once every warp's position has passed the window it held)
+	auto release = [&](int64_t pos) {
+		while (edge <= pos && kn < nwin) advance();
+		__syncwarp();
+		if (lane == 0) st_release_s64(&pos_s[cw], pos);
 	};
 	// per-lane address pattern of the tile columns: base + ring_row * rmul, step stride 4 * rmul
 	uint32_t base[NT], st[NT];
@@ -224,6 +255,8 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			st[t] = 0u;
 		}
 	}
+#pragma unroll
+	for (int t = 0; t < NT; ++t) asm volatile("" : "+r"(base[t]), "+r"(st[t])); // computed once, kept in registers
 	uint32_t n_comb = 0; // team combines so far (parity of dep_bar / rel_bar)
 	int64_t g = ga + team;
 	int64_t nr0 = 0, nr1 = 0;
@@ -294,7 +327,8 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 				}
 			}
 			ensure(r0 + f + 1);
-			const uint32_t rf = (uint32_t)((rp0 + f) % ring_rows);
+			uint32_t rf = (uint32_t)(rp0 + f);
+			if (rf >= (uint32_t)ring_rows) rf %= (uint32_t)ring_rows;
 #pragma unroll
 			for (int t = 0; t < NT; ++t) {
 				const int c = 8 * t + cl;
@@ -314,16 +348,25 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			for (int i = 0; i < NTP; ++i) e0[s][i] = e1[s][i] = 0.0;
 		if (ti == 0 && lane == 0) A.ns = ns_pre;
 
-		int rp = (rp0 + start + ti * QR) % ring_rows;
+		// This warp's quads are start + (ti + j TW) QR, j = 0, 1, ...: full quads run in batches (as many as the
+		// landed windows and the ring end allow) with nothing but pointer increments between them.
+		int rp = rp0 + start + ti * QR;
+		if (rp >= ring_rows) rp %= ring_rows;
 		const int rstep = TW * QR;
-		for (int row = start + ti * QR; row < n; row += rstep) {
-			const int cnt = n - row < QR ? n - row : QR;
-			ensure(r0 + row + cnt);
+		int row = start + ti * QR;
+		const uint32_t skip_rows = (uint32_t)(rstep - QR);
+		while (row + QR <= n) {
+			ensure(r0 + row + QR);
+			const int64_t av64 = ready - r0;
+			const int avail = av64 > (int64_t)n ? n : (int)av64;
+			const int span = avail - row - QR; // >= 0
+			const int nq = (slice ? span / rstep : span >> (ltw + (NSET == 4 ? 4 : (NSET == 2 ? 3 : 2)))) + 1;
 			uint32_t pa[NT];
 #pragma unroll
 			for (int t = 0; t < NT; ++t) pa[t] = base[t] + (uint32_t)rp * (st[t] >> 2);
 			uint32_t py = ys + (uint32_t)(rp + rl) * 8u, pw = ws + (uint32_t)(rp + rl) * 8u, pt = ts + (uint32_t)(rp + rl);
-			if (cnt == QR) {
+			int q = 0;
+			do {
 #pragma unroll
 				for (int s = 0; s < NSET; ++s) {
 					if (s == 0)
@@ -331,42 +374,57 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 					else
 						mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
 				}
-				if (!MASK) A.nv += NSET;
-			} else {
-				const int nfs = cnt >> 2;
 #pragma unroll
-				for (int s = 0; s < NSET - 1; ++s) {
-					if (s < nfs) {
-						if (s == 0)
-							mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
-						else
-							mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
-					}
+				for (int t = 0; t < NT; ++t) pa[t] += skip_rows * (st[t] >> 2);
+				py += skip_rows * 8u;
+				pw += skip_rows * 8u;
+				pt += skip_rows;
+				rp += rstep;
+				++q;
+			} while (q < nq && rp < ring_rows);
+			if (!MASK) A.nv += NSET * q;
+			row += q * rstep;
+			if (rp >= ring_rows) rp -= ring_rows;
+			release(r0 + (row < n ? row : n));
+		}
+		if (row < n) { // the group's last, partial quad
+			const int cnt = n - row;
+			ensure(r0 + n);
+			uint32_t pa[NT];
+#pragma unroll
+			for (int t = 0; t < NT; ++t) pa[t] = base[t] + (uint32_t)rp * (st[t] >> 2);
+			uint32_t py = ys + (uint32_t)(rp + rl) * 8u, pw = ws + (uint32_t)(rp + rl) * 8u, pt = ts + (uint32_t)(rp + rl);
+			const int nfs = cnt >> 2;
+#pragma unroll
+			for (int s = 0; s < NSET - 1; ++s) {
+				if (s < nfs) {
+					if (s == 0)
+						mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
+					else
+						mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
 				}
-				if (!MASK) A.nv += nfs;
-				if (cnt & 3) {
-					const bool in_range = rl < (cnt & 3);
-					if (!in_range) { // keep the loads inside the group's rows
+			}
+			if (!MASK) A.nv += nfs;
+			if (cnt & 3) {
+				const bool in_range = rl < (cnt & 3);
+				if (!in_range) { // keep the loads inside the group's rows
 #pragma unroll
-						for (int t = 0; t < NT; ++t) pa[t] -= (uint32_t)rl * (st[t] >> 2);
-						py -= (uint32_t)rl * 8u;
-						pw -= (uint32_t)rl * 8u;
-						pt -= (uint32_t)rl;
-					}
+					for (int t = 0; t < NT; ++t) pa[t] -= (uint32_t)rl * (st[t] >> 2);
+					py -= (uint32_t)rl * 8u;
+					pw -= (uint32_t)rl * 8u;
+					pt -= (uint32_t)rl;
+				}
 #pragma unroll
-					for (int s = 0; s < NSET; ++s) {
-						if (s == nfs) {
-							if (s == 0)
-								mma_step<NT, SIDE, HASW, HAST, true, HASW>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, in_range);
-							else
-								mma_step<NT, SIDE, HASW, HAST, true, HASW>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, in_range);
-						}
+				for (int s = 0; s < NSET; ++s) {
+					if (s == nfs) {
+						if (s == 0)
+							mma_step<NT, SIDE, HASW, HAST, true, HASW>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, in_range);
+						else
+							mma_step<NT, SIDE, HASW, HAST, true, HASW>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, in_range);
 					}
 				}
 			}
-			rp += rstep;
-			if (rp >= ring_rows) rp -= ring_rows;
-			release(r0 + (row + rstep < n ? row + rstep : n));
+			release(r0 + n);
 		}
 		// fold the accumulator sets in a fixed order
 #pragma unroll
