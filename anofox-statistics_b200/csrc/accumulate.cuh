@@ -362,7 +362,7 @@ __device__ __forceinline__ void lane_pointers(const SmemGroup &g, int p, int lan
 // c0 / c1: the DMMA accumulator set this step adds into (A's own, or one of the extra sets the ring kernel
 // rotates through to break the DMMA -> DMMA dependency between consecutive steps).
 // TRACKNC: keep the exact per-element constant-column flag (one DSETP per tile and step).
-template <int NT, bool SIDE, bool HASW, bool HAST, bool TAIL, bool TRACKNC>
+template <int NT, bool SIDE, bool HASW, bool HAST, bool TAIL, bool TRACKNC, bool COUNTS = true>
 __device__ __forceinline__ void mma_step(WarpAcc<NT, SIDE> &A, double (&c0)[NT * (NT + 1) / 2],
                                          double (&c1)[NT * (NT + 1) / 2], uint32_t (&pa)[NT], const uint32_t (&st)[NT],
                                          uint32_t &py, uint32_t &pw, uint32_t &pt, const double (&sh)[NT], double shy,
@@ -392,7 +392,9 @@ __device__ __forceinline__ void mma_step(WarpAcc<NT, SIDE> &A, double (&c0)[NT *
 	}
 	if (TAIL) ok = ok && in_range;
 	constexpr bool MASK = HASW || HAST || TAIL;
-	if (MASK) A.nv += ok ? 1 : 0;
+	// COUNTS = false (ring kernel, unweighted): n_valid equals the training-row count and sum w equals n_valid;
+	// both are filled in at the end of the group instead of per step
+	if (MASK && (COUNTS || HASW || !HAST)) A.nv += ok ? 1 : 0;
 	const double weff = MASK ? (ok ? wv : 0.0) : wv;
 	double d[NT], a[NT];
 #pragma unroll
@@ -422,7 +424,7 @@ __device__ __forceinline__ void mma_step(WarpAcc<NT, SIDE> &A, double (&c0)[NT *
 		}
 		A.syy = fma(wdy, dy, A.syy);
 		A.sy += wdy;
-		A.sw += weff;
+		if (COUNTS || HASW) A.sw += weff;
 	}
 }
 

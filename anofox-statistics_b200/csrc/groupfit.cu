@@ -527,14 +527,22 @@ static RingGeom ring_geometry(int p, bool has_w, bool has_t, int64_t n_rows, int
 	const int nv = sh.nt * (sh.nt + 1) + (sh.side ? 2 * sh.nt + 3 : 0) + 3;
 	const int64_t row_bytes = 8 * (int64_t)(p + 1) + (has_w ? 8 : 0) + (has_t ? 1 : 0);
 	const int64_t budget = 200 * 1024;
-	int sr = (int)((16 * 1024 / row_bytes + 15) / 16 * 16);
+	// tuning hooks (benchmarks only): window size in KB, team size
+	static const int env_win_kb = getenv("ANOFOX_B200_RING_WIN_KB") ? atoi(getenv("ANOFOX_B200_RING_WIN_KB")) : 0;
+	static const int env_team = getenv("ANOFOX_B200_RING_TEAM") ? atoi(getenv("ANOFOX_B200_RING_TEAM")) : 0;
+	// measured (tools/sweep.sh): 8 KB windows lose a third of the bandwidth to per-copy overhead; one-tile shapes
+	// (small p: y and the flags are tiny copies) want 32 KB, wider rows are best at 16 KB
+	const int64_t win_bytes = (env_win_kb > 0 ? env_win_kb : (sh.nt == 1 ? 32 : 16)) * 1024;
+	int sr = (int)((win_bytes / row_bytes + 15) / 16 * 16);
 	if (sr < 32) sr = 32;
 	const double mean_rows = n_groups > 0 ? (double)n_rows / (double)n_groups : 1.0;
 	int tw = 1;
 	if (team_override > 0) {
 		tw = team_override;
 	} else {
-		while (g.ncw % (tw * 2) == 0 && mean_rows >= 64.0 * (tw * 2)) tw *= 2;
+		// measured: a warp wants >= ~100 rows of a group (C3: 200 rows -> 2 warps, C5: 1000 rows -> 4 warps)
+		while (g.ncw % (tw * 2) == 0 && mean_rows >= 50.0 * (tw * 2) * (tw * 2)) tw *= 2;
+		if (env_team > 0 && g.ncw % env_team == 0) tw = env_team;
 	}
 	for (;;) {
 		const int64_t slot_bytes = (int64_t)(g.ncw / tw) * (tw - 1) * nv * 256;

@@ -56,7 +56,7 @@ template <int NT, bool SIDE> __host__ __device__ constexpr int ring_deposit_valu
 	return NT * (NT + 1) + (SIDE ? 2 * NT + 3 : 0) + 3;
 }
 __host__ __device__ constexpr int ring_sets(int nt) { return nt == 1 ? 4 : (nt <= 4 ? 2 : 1); }
-__host__ __device__ constexpr int ring_warps(int nt) { return nt <= 2 ? 12 : (nt <= 4 ? 8 : 4); }
+__host__ __device__ constexpr int ring_warps(int nt) { return nt == 1 ? 16 : (nt == 2 ? 12 : (nt <= 4 ? 8 : 4)); }
 // registers per thread that still let one CTA of (ncw + 1) warps launch: the register file is split over the
 // four SM sub-partitions (16384 each), and the fullest one holds ceil((ncw + 1) / 4) warps
 __host__ __device__ constexpr int ring_maxreg(int ncw) {
@@ -346,7 +346,6 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 		for (int s = 0; s < (NSET > 1 ? NSET - 1 : 1); ++s)
 #pragma unroll
 			for (int i = 0; i < NTP; ++i) e0[s][i] = e1[s][i] = 0.0;
-		if (ti == 0 && lane == 0) A.ns = ns_pre;
 
 		// This warp's quads are start + (ti + j TW) QR, j = 0, 1, ...: full quads run in batches (as many as the
 		// landed windows and the ring end allow) with nothing but pointer increments between them.
@@ -370,9 +369,9 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 #pragma unroll
 				for (int s = 0; s < NSET; ++s) {
 					if (s == 0)
-						mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
+						mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
 					else
-						mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
+						mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
 				}
 #pragma unroll
 				for (int t = 0; t < NT; ++t) pa[t] += skip_rows * (st[t] >> 2);
@@ -399,9 +398,9 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			for (int s = 0; s < NSET - 1; ++s) {
 				if (s < nfs) {
 					if (s == 0)
-						mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
+						mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
 					else
-						mma_step<NT, SIDE, HASW, HAST, false, HASW>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
+						mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
 				}
 			}
 			if (!MASK) A.nv += nfs;
@@ -418,14 +417,18 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 				for (int s = 0; s < NSET; ++s) {
 					if (s == nfs) {
 						if (s == 0)
-							mma_step<NT, SIDE, HASW, HAST, true, HASW>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, in_range);
+							mma_step<NT, SIDE, HASW, HAST, true, HASW, false>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, in_range);
 						else
-							mma_step<NT, SIDE, HASW, HAST, true, HASW>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, in_range);
+							mma_step<NT, SIDE, HASW, HAST, true, HASW, false>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, in_range);
 					}
 				}
 			}
 			release(r0 + n);
 		}
+		// the per-step counts the unweighted steps left out: valid rows = training rows, sum w = valid rows
+		if (HAST && !HASW) A.nv = A.ns;
+		if (SIDE && !HASW) A.sw = (double)A.nv;
+		if (ti == 0 && lane == 0) A.ns += ns_pre;
 		// fold the accumulator sets in a fixed order
 #pragma unroll
 		for (int s = 0; s < NSET - 1; ++s)
