@@ -18,6 +18,7 @@
 #include <vector>
 
 #include "acc_launch.h"
+#include "solve_mid.cuh"
 #include "accumulate.cuh"
 #include "common.cuh"
 #include "fused_launch.h"
@@ -361,6 +362,26 @@ static cudaError_t launch_redo(const RingArgs &a, int grid, cudaStream_t st) {
 static cudaError_t launch_solve(const double *records, int64_t G, const FitParams &P, const AnofoxB200FitOutputs &o,
                                 int *refine_count, int64_t *refine_list, cudaStream_t st) {
 	if (G <= 0) return cudaSuccess;
+	if (P.p > 8 && P.p <= 16) {
+		// 9 <= p <= 16: fixed-layout, fully unrolled shared-memory solve (solve_mid.cuh)
+		const size_t dyn = (size_t)FixLayout<16>::LEN * kFixTS * 8;
+		cudaError_t e = cudaFuncSetAttribute(solve_fixed_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+		if (e != cudaSuccess) return e;
+		solve_fixed_kernel<16><<<(unsigned)((G + kFixT - 1) / kFixT), kFixT, dyn, st>>>(records, G, P, o, refine_count, refine_list);
+		LAUNCHED();
+		return cudaGetLastError();
+	}
+	const int mid_threads = P.p > 8 && P.p <= 32 ? solve_mid_threads(P.p) : 0;
+	if (mid_threads > 0) {
+		// 9 <= p <= 32: per-thread arrays in shared memory (solve_mid.cuh)
+		const size_t dyn = (size_t)rec_len(P.p) * (mid_threads + 1) * 8;
+		cudaError_t e = cudaFuncSetAttribute(solve_mid_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+		if (e != cudaSuccess) return e;
+		solve_mid_kernel<0><<<(unsigned)((G + mid_threads - 1) / mid_threads), mid_threads, dyn, st>>>(records, G, P, o, refine_count,
+		                                                                                              refine_list);
+		LAUNCHED();
+		return cudaGetLastError();
+	}
 	const int threads = 128;
 	const unsigned blocks = (unsigned)((G + threads - 1) / threads);
 	if (P.p <= 8)
