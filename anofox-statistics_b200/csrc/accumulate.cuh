@@ -428,6 +428,90 @@ __device__ __forceinline__ void mma_step(WarpAcc<NT, SIDE> &A, double (&c0)[NT *
 	}
 }
 
+// Software-pipelined form of mma_step for full (unmasked-tail) steps: the operands of a step are loaded a step
+// ahead. The raw values are dead once the differences d = v - shift exist, so the next step's loads reuse their
+// registers and sit between the subtractions and the DMMAs of the current step: the shared-memory latency hides
+// behind ~NT(NT+1)/2 tensor instructions instead of stalling the warp at the top of every step.
+template <int NT, bool SIDE, bool HASW, bool HAST> struct StepIn {
+	double v[NT];
+	double yv, wv;
+	uint32_t tr;
+};
+template <int NT, bool SIDE, bool HASW, bool HAST>
+__device__ __forceinline__ void step_load(StepIn<NT, SIDE, HASW, HAST> &in, uint32_t (&pa)[NT], const uint32_t (&st)[NT],
+                                          uint32_t &py, uint32_t &pw, uint32_t &pt) {
+#pragma unroll
+	for (int t = 0; t < NT; ++t) {
+		in.v[t] = lds_f64(pa[t]);
+		pa[t] += st[t];
+	}
+	if (SIDE) {
+		in.yv = lds_f64(py);
+		py += 32u;
+	}
+	if (HASW) {
+		in.wv = lds_f64(pw);
+		pw += 32u;
+	}
+	if (HAST) {
+		in.tr = lds_u8(pt);
+		pt += 4u;
+	}
+}
+template <int NT, bool SIDE, bool HASW, bool HAST, bool TRACKNC, bool COUNTS>
+__device__ __forceinline__ void mma_step_pipe(WarpAcc<NT, SIDE> &A, double (&c0)[NT * (NT + 1) / 2],
+                                              double (&c1)[NT * (NT + 1) / 2], StepIn<NT, SIDE, HASW, HAST> &in,
+                                              uint32_t (&pa)[NT], const uint32_t (&st)[NT], uint32_t &py, uint32_t &pw,
+                                              uint32_t &pt, const double (&sh)[NT], double shy, bool more) {
+	bool ok = true;
+	double wv = 1.0;
+	if (HASW) {
+		wv = in.wv;
+		ok = wv > 0.0;
+	}
+	if (HAST) {
+		ok = ok && in.tr != 0u;
+		A.ns += in.tr != 0u ? 1 : 0;
+	}
+	constexpr bool MASK = HASW || HAST;
+	if (MASK && (COUNTS || HASW || !HAST)) A.nv += ok ? 1 : 0;
+	const double weff = MASK ? (ok ? wv : 0.0) : wv;
+	double d[NT], a[NT];
+#pragma unroll
+	for (int t = 0; t < NT; ++t) {
+		double dv = in.v[t] - sh[t];
+		if (MASK) dv = ok ? dv : 0.0;
+		d[t] = dv;
+		if (TRACKNC) A.nc[t] = A.nc[t] || (fabs(dv) >= 1e-10);
+		a[t] = HASW ? weff * dv : dv;
+	}
+	double dy = 0.0;
+	if (SIDE) {
+		dy = in.yv - shy;
+		if (MASK) dy = ok ? dy : 0.0;
+	}
+	if (more) step_load<NT, SIDE, HASW, HAST>(in, pa, st, py, pw, pt);
+	int pair = 0;
+#pragma unroll
+	for (int ta = 0; ta < NT; ++ta)
+#pragma unroll
+		for (int tb = ta; tb < NT; ++tb) {
+			dmma_884(c0[pair], c1[pair], a[ta], d[tb]);
+			++pair;
+		}
+	if (SIDE) {
+		const double wdy = HASW ? weff * dy : dy;
+#pragma unroll
+		for (int t = 0; t < NT; ++t) {
+			A.sxy[t] = fma(d[t], wdy, A.sxy[t]);
+			A.s1[t] += a[t];
+		}
+		A.syy = fma(wdy, dy, A.syy);
+		A.sy += wdy;
+		if (COUNTS || HASW) A.sw += weff;
+	}
+}
+
 template <int NT, bool SIDE, bool HASW, bool HAST, bool TAIL>
 __device__ __forceinline__ void fast_step(WarpAcc<NT, SIDE> &A, uint32_t (&pa)[NT], const uint32_t (&st)[NT],
                                           uint32_t &py, uint32_t &pw, uint32_t &pt, const double (&sh)[NT], double shy,
@@ -724,6 +808,12 @@ struct StreamArgs {
 	int n_part;             // gridDim.x * warps per CTA of acc_stream_kernel
 	double *records;        // group mode: [G][L]; shard mode: [1][L]
 	int64_t rec_gs, rec_es; // record element (g, i) lives at records[g * rec_gs + i * rec_es]
+	// Row-shard mode behind the ring kernel's slices: the checked streaming pass only runs when *run_if is
+	// non-zero (a slice met a non-finite value or an undecided constant column); the reduction then reads
+	// `partials` / `n_part`, otherwise the ring's partial records `ring_partials` / `ring_n_part`.
+	const int *run_if;
+	const double *ring_partials;
+	int ring_n_part;
 };
 
 __device__ __forceinline__ bool row_valid_full(const StreamArgs &a, int64_t r) {
@@ -757,6 +847,7 @@ template <int NT, bool SIDE, int NW> __global__ void __launch_bounds__(32 * NW) 
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cl = lane >> 2;
 	const int p = a.p, k = p + 1, L = rec_len(p);
 	const int nbig = a.offsets ? *a.big_count : 1;
+	if (a.run_if && *a.run_if == 0) return;
 	for (int b = 0; b < nbig; ++b) {
 		int64_t r0 = 0, r1 = a.fixed_rows;
 		if (a.offsets) {
@@ -807,20 +898,22 @@ static __global__ void reduce_partials_kernel(const StreamArgs a) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= L) return;
 	const int64_t g = a.offsets ? a.big_list[b] : 0;
-	const double *part = a.partials + (int64_t)b * a.n_part * L;
+	const bool ring = a.run_if && *a.run_if == 0;
+	const int n_part = ring ? a.ring_n_part : a.n_part;
+	const double *part = ring ? a.ring_partials : a.partials + (int64_t)b * a.n_part * L;
 	double v;
 	if (i >= rec_off_shift(p) && i < rec_off_cdev(p)) {
 		v = a.shift[(int64_t)b * (p + 1) + (i - rec_off_shift(p))];
 	} else if (i >= rec_off_cdev(p) && i < rec_off_cdev(p) + p) {
 		v = 0.0;
-		for (int q = 0; q < a.n_part; ++q) v = fmax(v, part[(int64_t)q * L + i]);
+		for (int q = 0; q < n_part; ++q) v = fmax(v, part[(int64_t)q * L + i]);
 	} else if (i >= rec_off_cdev(p) && i < rec_off_s1(p)) {
 		v = 0.0; // pad
 	} else if (i == 3) {
 		v = 0.0;
 	} else {
 		v = 0.0;
-		for (int q = 0; q < a.n_part; ++q) v += part[(int64_t)q * L + i];
+		for (int q = 0; q < n_part; ++q) v += part[(int64_t)q * L + i];
 	}
 	a.records[g * a.rec_gs + (int64_t)i * a.rec_es] = v;
 }

@@ -93,6 +93,20 @@ __device__ __forceinline__ void mbar_wait_addr(uint32_t bar_addr, uint32_t parit
 	    "r"(parity), "r"(20000u)
 	    : "memory");
 }
+// non-blocking: has the phase with this parity completed?
+__device__ __forceinline__ bool mbar_test_addr(uint32_t bar_addr, uint32_t parity) {
+	uint32_t ok;
+	asm volatile(
+	    "{\n"
+	    " .reg .pred p;\n"
+	    " mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+	    " selp.u32 %0, 1, 0, p;\n"
+	    "}\n"
+	    : "=r"(ok)
+	    : "r"(bar_addr), "r"(parity)
+	    : "memory");
+	return ok != 0u;
+}
 __device__ __forceinline__ void st_release_s64(long long *p, long long v) {
 	asm volatile("st.release.cta.shared.s64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory");
 }

@@ -19,6 +19,7 @@
 
 #include "acc_launch.h"
 #include "solve_mid.cuh"
+#include "solve_wide.cuh"
 #include "accumulate.cuh"
 #include "common.cuh"
 #include "fused_launch.h"
@@ -271,6 +272,17 @@ __global__ void shard_shift_kernel(const double *__restrict__ y, const double *_
 	for (int c = threadIdx.x; c <= p; c += blockDim.x) shift[c] = ok ? (c < p ? x[(int64_t)f * p + c] : y[f]) : 0.0;
 	if (threadIdx.x == 0) *found = ok ? 1 : 0;
 }
+// Row bounds of `units` equal slices of a shard (multiples of 16 rows) and the one-slice-per-CTA map the ring
+// kernel's slice mode reads.
+__global__ void slice_bounds_kernel(int64_t n_rows, int units, int64_t *__restrict__ bounds, int64_t *__restrict__ cta_map) {
+	int64_t per = (n_rows + units - 1) / units;
+	per = (per + 15) & ~(int64_t)15;
+	for (int i = threadIdx.x; i <= units; i += blockDim.x) {
+		const int64_t b = (int64_t)i * per;
+		bounds[i] = b < n_rows ? b : n_rows;
+		cta_map[i] = i;
+	}
+}
 
 // ---------------------------------------------------------------------------------------------
 // Dispatch on the feature count
@@ -379,6 +391,16 @@ static cudaError_t launch_solve(const double *records, int64_t G, const FitParam
 		if (e != cudaSuccess) return e;
 		solve_mid_kernel<0><<<(unsigned)((G + mid_threads - 1) / mid_threads), mid_threads, dyn, st>>>(records, G, P, o, refine_count,
 		                                                                                              refine_list);
+		LAUNCHED();
+		return cudaGetLastError();
+	}
+	if (P.p > 32) {
+		// 33 <= p <= 64: one thread block per group, factor in shared memory (solve_wide.cuh)
+		const size_t dyn = sizeof(WideSmem);
+		cudaError_t e = cudaFuncSetAttribute(solve_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+		if (e != cudaSuccess) return e;
+		solve_wide_kernel<<<(unsigned)std::min<int64_t>(G, 148 * 12), kWideThreads, dyn, st>>>(records, nullptr, G, P, o, refine_count,
+		                                                                                     refine_list);
 		LAUNCHED();
 		return cudaGetLastError();
 	}
@@ -744,6 +766,8 @@ struct Workspace {
 	double *shift;
 	int *first_ok;
 	double *partials;
+	double *ring_partials; // row-shard mode: partial records of the ring kernel's slices
+	int64_t *slice_off;    // row-shard mode: row bounds of the slices, then the CTA -> slice map
 	int64_t *refine_list;
 	int *refine_count;
 	int64_t *redo_list;
@@ -788,6 +812,8 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 	// big groups one call may hold (see fit_device); sized here for that cap.
 	const int64_t part_groups = std::min<int64_t>(w.nbig_max, 64);
 	w.partials = (double *)take((size_t)part_groups * w.n_part * L * 8);
+	w.ring_partials = (double *)take(G == 1 ? (size_t)sms * 16 * L * 8 : 0);
+	w.slice_off = (int64_t *)take((size_t)(2 * sms + 4) * 8);
 	w.refine_list = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
 	w.refine_count = (int *)take(256);
 	w.redo_list = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
@@ -1026,6 +1052,9 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 			s.records = ws.records;
 			s.rec_gs = rec_gs;
 			s.rec_es = rec_es;
+			s.run_if = nullptr;
+			s.ring_partials = nullptr;
+			s.ring_n_part = 0;
 			first_valid_kernel<<<nb, 32, 0, st>>>(s);
 			LAUNCHED();
 			CU(cudaGetLastError(), "first_valid_kernel");
@@ -1640,6 +1669,41 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 		return ANOFOX_ERROR_INVALID_INPUT;
 	}
 	cudaStream_t st = (cudaStream_t)stream;
+	// Fast pass: the ring kernel in slice mode (ring.cuh) -- one slice of the shard per CTA, the CTA's warps
+	// interleave its quads, rows flow through the shared-memory ring. It checks nothing per element; a
+	// non-finite value or an undecided constant column raises redo_count, and only then the checked
+	// streaming pass below runs (decided on the device: no host round trip).
+	const Shape shp = shape_of(p);
+	const int ncw = ring_warps(shp.nt);
+	const int units = (int)std::max<int64_t>(1, std::min<int64_t>(di.sms, (n_rows + 4095) / 4096));
+	const RingGeom rg_ = ring_geometry(p, w != nullptr, false, n_rows, units, units, ncw);
+	CU(cudaMemsetAsync(ws.redo_count, 0, 256, st), "memset");
+	slice_bounds_kernel<<<1, 256, 0, st>>>(n_rows, units, ws.slice_off, ws.slice_off + units + 1);
+	LAUNCHED();
+	CU(cudaGetLastError(), "slice_bounds_kernel");
+	RingArgs r;
+	r.offsets = ws.slice_off;
+	r.y = y;
+	r.x = x;
+	r.w = w;
+	r.train = nullptr;
+	r.p = p;
+	r.tile_g0 = ws.slice_off + units + 1;
+	r.records = ws.ring_partials;
+	r.shift_common = shift;
+	r.big_list = ws.big_list;
+	r.big_count = ws.big_count;
+	r.big_rows = (int64_t)1 << 40;
+	r.redo_list = ws.redo_list;
+	r.redo_count = ws.redo_count;
+	r.win_rows = rg_.win_rows;
+	r.n_win = rg_.n_win;
+	r.team = rg_.team;
+	r.x_off = rg_.x_off;
+	r.y_off = rg_.y_off;
+	r.w_off = rg_.w_off;
+	r.t_off = rg_.t_off;
+	r.slot_off = rg_.slot_off;
 	StreamArgs s;
 	s.offsets = nullptr;
 	s.big_list = nullptr;
@@ -1657,7 +1721,15 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	s.records = ws.records;
 	s.rec_gs = rec_len(p);
 	s.rec_es = 1;
+	s.run_if = ws.redo_count;
+	s.ring_partials = ws.ring_partials;
+	s.ring_n_part = units * ncw;
 	timer_mark(st);
+	if (n_rows > 0 && g_force_path.load() != 3) {
+		CU(launch_ring(r, w != nullptr, false, units, rg_.dyn_bytes, st), "acc_ring_kernel (slices)");
+	} else {
+		s.run_if = nullptr; // empty shard or A/B run: the checked streaming pass alone
+	}
 	CU(launch_stream(s, ws.n_part / kStreamWarps, st), "acc_stream_kernel");
 	timer_mark(st);
 	dim3 rg((unsigned)((rec_len(p) + 127) / 128), 1);

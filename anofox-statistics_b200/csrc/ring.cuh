@@ -228,6 +228,16 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			mbar_wait_addr(full0 + 8u * (uint32_t)kn_s, kn_ph);
 			advance();
 		}
+		// look ahead: take every further window that has already landed, so that the batch below runs over all
+		// rows on chip instead of the one window that was asked for
+		while (kn < nwin) {
+			if (issued <= kn) {
+				issued = ld_volatile_s32(&issued_s);
+				if (issued <= kn) break;
+			}
+			if (!mbar_test_addr(full0 + 8u * (uint32_t)kn_s, kn_ph)) break;
+			advance();
+		}
 	};
 	// this warp will not read rows < pos again: step over the windows that lie entirely below and publish the
 	// position (the producer refills a slot once every warp's position has passed the window it held)
@@ -364,23 +374,31 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 #pragma unroll
 			for (int t = 0; t < NT; ++t) pa[t] = base[t] + (uint32_t)rp * (st[t] >> 2);
 			uint32_t py = ys + (uint32_t)(rp + rl) * 8u, pw = ws + (uint32_t)(rp + rl) * 8u, pt = ts + (uint32_t)(rp + rl);
+			// quads of this batch: as many as have landed, up to the ring end
+			const int to_end = (ring_rows - rp + rstep - 1) / rstep;
+			const int nqe = nq < to_end ? nq : to_end;
+			StepIn<NT, SIDE, HASW, HAST> in;
+			step_load<NT, SIDE, HASW, HAST>(in, pa, st, py, pw, pt);
 			int q = 0;
 			do {
 #pragma unroll
 				for (int s = 0; s < NSET; ++s) {
-					if (s == 0)
-						mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
-					else
-						mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
-				}
+					if (s == NSET - 1) { // the next step is the first of the next quad
 #pragma unroll
-				for (int t = 0; t < NT; ++t) pa[t] += skip_rows * (st[t] >> 2);
-				py += skip_rows * 8u;
-				pw += skip_rows * 8u;
-				pt += skip_rows;
+						for (int t = 0; t < NT; ++t) pa[t] += skip_rows * (st[t] >> 2);
+						py += skip_rows * 8u;
+						pw += skip_rows * 8u;
+						pt += skip_rows;
+					}
+					const bool more = s + 1 < NSET || q + 1 < nqe;
+					if (s == 0)
+						mma_step_pipe<NT, SIDE, HASW, HAST, HASW, false>(A, A.c0, A.c1, in, pa, st, py, pw, pt, sh, shy, more);
+					else
+						mma_step_pipe<NT, SIDE, HASW, HAST, HASW, false>(A, e0[s - 1], e1[s - 1], in, pa, st, py, pw, pt, sh, shy, more);
+				}
 				rp += rstep;
 				++q;
-			} while (q < nq && rp < ring_rows);
+			} while (q < nqe);
 			if (!MASK) A.nv += NSET * q;
 			row += q * rstep;
 			if (rp >= ring_rows) rp -= ring_rows;

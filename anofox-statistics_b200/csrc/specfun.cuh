@@ -73,12 +73,54 @@ __device__ inline double beta_inc(double a, double b, double x, double xc) {
 	return 1.0 - exp(lnpre) * beta_cf(b, a, xc) / b;
 }
 
+// Large degrees of freedom: the continued fraction needs O(sqrt(df)) steps (a 10^8-row group: ~10^4 per
+// evaluation), so above kLargeDf the two-sided tail comes from Hill's normalising expansion (CACM Algorithm
+// 395, 1970): P(|T_df| > t) = erfc(z / sqrt 2) with z a series in 1 / (48 (df - 1/2)^2). Relative error
+// against a 60-digit reference <= 8e-11 for df >= 4097 down to tails of 1e-300 (tests/test_gpu_parity.py).
+constexpr double kLargeDf = 4096.0;
+__device__ inline double t_two_sided_p_large(double t2, double df) {
+	const double a = df - 0.5, b = 48.0 * a * a;
+	const double y = a * log1p(t2 / df);
+	const double z = (((((-0.4 * y - 3.3) * y - 24.0) * y - 85.5) / (0.8 * y * y + 100.0 + b) + y + 3.0) / b + 1.0) * sqrt(y);
+	return erfc(z * 0.70710678118654752440);
+}
+
 // 2 * (1 - T_df(|t|)) = I_{df/(df+t^2)}(df/2, 1/2)
 __device__ inline double t_two_sided_p(double t, double df) {
 	if (isnan(t) || !(df > 0.0)) return nan_f64();
 	if (isinf(t)) return 0.0;
 	double t2 = t * t;
+	if (df > kLargeDf) return t_two_sided_p_large(t2, df);
 	return beta_inc(0.5 * df, 0.5, df / (df + t2), t2 / (df + t2));
+}
+
+// Upper tail of F(d1, d2) for integer d1 and d2 > kLargeDf: I_x(a, b), a = d2/2, b = d1/2, built up from
+// b = 1 (x^a) or b = 1/2 (the t tail above) with I_x(a, b+1) = I_x(a, b) + x^a y^b / (b B(a, b)): at most
+// d1/2 positive terms, x^a = exp(-a log1p(d1 f / d2)) applied last (the sum can be 1e50 times x^a).
+__device__ inline double f_upper_p_large(double f, double d1, double d2) {
+	const double a = 0.5 * d2, b = 0.5 * d1;
+	const double y = d1 * f / (d2 + d1 * f);
+	const double lnxa = -a * log1p(d1 * f / d2);
+	// result = base + exp(lnbase) S, S = 1 + r_1 + r_2 + ... kept apart from the (possibly underflowing) x^a
+	double base = 0.0, lnbase = lnxa, bp = 1.0;
+	if (fmod(d1, 2.0) != 0.0) {
+		base = t_two_sided_p_large(d1 * f, d2); // I_x(a, 1/2)
+		if (b < 1.0) return base;
+		lnbase = 0.69314718055994530942 + lnxa + 0.5 * log(y) - lbeta_dev(a, 0.5); // T_{1/2}
+		bp = 1.5;
+	}
+	double S = 1.0, r = 1.0, lnscale = 0.0;
+	while (bp < b - 0.25) {
+		r *= y * (a + bp - 1.0) / bp;
+		S += r;
+		bp += 1.0;
+		if (S > 1e200) {
+			S *= 1e-200;
+			r *= 1e-200;
+			lnscale += 460.51701859880913680; // 200 ln 10
+		}
+	}
+	return fmin(base + exp(lnbase + lnscale + log(S)), 1.0);
 }
 
 // Upper tail of F(d1,d2)
@@ -86,6 +128,7 @@ __device__ inline double f_upper_p(double f, double d1, double d2) {
 	if (isnan(f) || !(d1 > 0.0) || !(d2 > 0.0)) return nan_f64();
 	if (f <= 0.0) return 1.0;
 	if (isinf(f)) return 0.0;
+	if (d2 > kLargeDf && d1 == floor(d1) && d1 <= 4096.0) return f_upper_p_large(f, d1, d2);
 	double den = d2 + d1 * f;
 	return beta_inc(0.5 * d2, 0.5 * d1, d2 / den, d1 * f / den);
 }
@@ -245,7 +288,8 @@ __device__ inline double t_two_sided_p_fast(double t, double df, const DfTables 
 	if (isnan(t) || !(df > 0.0)) return nan_f64();
 	if (isinf(t)) return 0.0;
 	const double t2 = t * t, den = df + t2;
-	if (T.ce == nullptr || df > (double)kTcritTable || df != floor(df)) return beta_inc(0.5 * df, 0.5, df / den, t2 / den);
+	if (df > kLargeDf) return t_two_sided_p_large(t2, df);
+	if (T.ce == nullptr || df != floor(df)) return beta_inc(0.5 * df, 0.5, df / den, t2 / den);
 	return betai_half_fast((int)df, df / den, t2 / den, T);
 }
 
@@ -258,6 +302,7 @@ __device__ inline double f_upper_p_fast(double f, double d1, double d2, const Df
 	if (isinf(f)) return 0.0;
 	const double den = d2 + d1 * f;
 	const double x = d2 / den, y = d1 * f / den;
+	if (d2 > kLargeDf && d1 == floor(d1) && d1 <= 4096.0) return f_upper_p_large(f, d1, d2);
 	if (T.ce == nullptr || d2 > (double)kTcritTable || d2 != floor(d2) || d1 != floor(d1) || d1 > 1024.0)
 		return beta_inc(0.5 * d2, 0.5 * d1, x, y);
 	const int nu = (int)d2, m = (int)d1;

@@ -176,6 +176,75 @@ def test_device_special_functions(lib, oracle):
     assert lib.predict_with_interval(coef, 0.0, [1.0], 1.0, 10, 0.9)[0] is False  # length mismatch
 
 
+def test_device_special_functions_large_df(lib):
+    """df above the table range (groups of more than 4096 rows, up to the 10^9-row single group of config 4):
+    Hill's normalising expansion for the t tail and the finite beta recurrence for the F tail, against
+    60-digit mpmath values."""
+    import mpmath as mp
+    mp.mp.dps = 60
+
+    def t_tail(t, n):
+        t, n = mp.mpf(t), mp.mpf(n)
+        if t * t > 3000 and n > 4000:
+            return mp.mpf(0)  # < 1e-600: below the double range (and mpmath's series gives up out there)
+        return mp.betainc(n / 2, mp.mpf(1) / 2, 0, n / (n + t * t), regularized=True)
+
+    def f_tail(f, d1, d2):
+        # I_x(a, b), a = d2/2, b = d1/2, from I_x(a, 1) = x^a or I_x(a, 1/2) (the t tail) by the exact recurrence
+        # I_x(a, b+1) = I_x(a, b) + x^a y^b / (b B(a, b)), in 60-digit arithmetic (mpmath's own betainc does not
+        # converge for a ~ 10^8); the identity itself is checked against betainc for d2 <= 10^5 below
+        f, a, b = mp.mpf(f), mp.mpf(d2) / 2, mp.mpf(d1) / 2
+        x, y = d2 / (d2 + d1 * f), d1 * f / (d2 + d1 * f)
+        if d1 % 2 == 0:
+            acc, bp = x ** a, mp.mpf(1)
+        else:
+            acc, bp = t_tail(mp.sqrt(d1 * f), d2), mp.mpf(1) / 2
+        while bp < b:
+            acc += mp.exp(a * mp.log(x) + bp * mp.log(y) - mp.log(bp) - mp.log(mp.beta(a, bp)))
+            bp += 1
+        return acc
+
+    for d1, d2, f in [(3, 4097, 2.0), (64, 10**5, 1.2), (63, 20001, 30.0), (2, 4097, 0.01)]:
+        direct = mp.betainc(mp.mpf(d2) / 2, mp.mpf(d1) / 2, 0, mp.mpf(d2) / (d2 + d1 * mp.mpf(f)), regularized=True)
+        assert abs(f_tail(f, d1, d2) / direct - 1) < 1e-30
+
+    dfl = [4097, 20001, 10**5, 999_999, 124_999_935, 10**9]
+    ts, dfs = [], []
+    for df in dfl:
+        for t in [1e-5, 0.02, 0.5, 1.0, 1.96, 3.0, 6.0, 10.0, 20.0, 37.0]:
+            ts.append(t)
+            dfs.append(df)
+    want = np.array([float(t_tail(t, d)) for t, d in zip(ts, dfs)])
+    for mode in (0, 3):
+        got = lib.eval_specfun(mode, ts, dfs)
+        rel = np.abs(got - want) / want
+        assert rel.max() < 1e-10, (mode, rel.max(), ts[int(rel.argmax())], dfs[int(rel.argmax())])
+    assert (lib.eval_specfun(3, [1e3, 1e6], [10**8, 5000]) == 0.0).all()
+    lv, dd = [], []
+    for df in dfl:
+        for level in [0.5, 0.9, 0.95, 0.99, 0.999999]:
+            lv.append(level)
+            dd.append(df)
+    got = lib.eval_specfun(1, lv, dd)
+    back = np.array([float(t_tail(t, d)) for t, d in zip(got, dd)])
+    alpha = 1.0 - np.array(lv)
+    assert (np.abs(back - alpha) / alpha).max() < 1e-10
+    fs, d1, d2 = [], [], []
+    for b in dfl:
+        for a in [1, 2, 3, 5, 16, 63, 64]:
+            for f in [0.001, 0.01, 0.3, 1.0, 1.5, 3.0, 10.0, 25.0, 40.0, 1e5]:
+                fs.append(f)
+                d1.append(a)
+                d2.append(b)
+    want = np.array([float(f_tail(f, a, b)) for f, a, b in zip(fs, d1, d2)])
+    for mode in (2, 4):
+        got = lib.eval_specfun(mode, fs, d1, d2)
+        ok = want > 1e-290
+        rel = np.abs(got[ok] - want[ok]) / want[ok]
+        i = int(rel.argmax())
+        assert rel.max() < 1e-10, (mode, rel.max(), np.array(fs)[ok][i], np.array(d1)[ok][i], np.array(d2)[ok][i])
+
+
 # ------------------------------------------------------------------ batch layer vs oracle
 def make_case(rng, G, n_lo, n_hi, p, dirty=True, weights=False, collinear=True):
     sizes = rng.integers(n_lo, n_hi + 1, size=G)
@@ -499,6 +568,81 @@ def test_row_sharded_single_group(lib, oracle):
         torch.cuda.synchronize()
         dev = {k: v.cpu().numpy() for k, v in fit.out.items()}
         assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label=f"sharded p={p}")
+
+
+def _fit_from_row_shards(lib, x, y, w, cuts, **opt):
+    """Row shards -> moment blocks (anofox_b200_moments_device) -> SUM / MAX -> anofox_b200_solve_moments_device."""
+    import ctypes as C
+    import torch
+    A = lib.abi
+    l = lib.load_library()
+    N, p = x.shape
+    xd, yd = torch.tensor(x, device="cuda"), torch.tensor(y, device="cuda")
+    wd = None if w is None else torch.tensor(w, device="cuda")
+    shift = torch.cat([xd[0], yd[:1]]).contiguous()
+    L = lib.moment_block_len(p)
+    wb = l.anofox_b200_workspace_bytes(1, N, p)
+    ws = torch.empty(wb + 256, dtype=torch.uint8, device="cuda")
+    wp = (ws.data_ptr() + 255) & ~255
+    err = A.AnofoxError()
+    msum = torch.zeros(L, dtype=torch.float64, device="cuda")
+    cmax = torch.zeros(p, dtype=torch.float64, device="cuda")
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        m = torch.zeros(L, dtype=torch.float64, device="cuda")
+        cd = torch.zeros(p, dtype=torch.float64, device="cuda")
+        # views into the big arrays: shard starts are not 16-byte aligned when `a` is odd
+        xs, ys = xd[a:b], yd[a:b]
+        wsd = None if wd is None else C.c_void_p(wd[a:b].data_ptr())
+        rc = l.anofox_b200_moments_device(C.c_void_p(ys.data_ptr()), C.c_void_p(xs.data_ptr()), wsd, b - a, p,
+                                          C.c_void_p(shift.data_ptr()), C.c_void_p(m.data_ptr()),
+                                          C.c_void_p(cd.data_ptr()), C.c_void_p(wp), wb, None, C.byref(err))
+        assert rc == 0, err.message
+        torch.cuda.synchronize()
+        msum += m
+        cmax = torch.maximum(cmax, cd)
+    fit = lib.DeviceFit(1, N, p, inference=True)
+    o = A.make_fit_options(compute_inference=True, **opt)
+    rc = l.anofox_b200_solve_moments_device(C.c_void_p(msum.data_ptr()), C.c_void_p(cmax.data_ptr()),
+                                            C.c_void_p(shift.data_ptr()), p, C.byref(o), C.byref(fit.out_struct),
+                                            None, C.byref(err))
+    assert rc == 0, err.message
+    torch.cuda.synchronize()
+    return {k: v.cpu().numpy() for k, v in fit.out.items()}
+
+
+SHARD_CASES = [
+    # p, N, method, constant column: clean shards stay on the ring kernel's slice mode (no checked pass)
+    (64, 300_000, "ols", False),
+    (5, 1_000_003, "ols", False),
+    (16, 250_001, "wls", False),
+    (33, 120_000, "ols", True),
+    (8, 77, "ols", False),
+    (48, 150_000, "ridge", False),
+]
+
+
+@pytest.mark.parametrize("p,N,method,const", SHARD_CASES, ids=[f"{c[2]}-p{c[0]}-n{c[1]}" for c in SHARD_CASES])
+def test_row_sharded_clean_shards(lib, oracle, p, N, method, const):
+    rng = np.random.default_rng(77 + p)
+    x = rng.normal(size=(N, p)) + 3.0
+    for j in range(1, p):
+        x[:, j] = 0.3 * x[:, j - 1] + math.sqrt(1 - 0.09) * x[:, j]
+    if const:
+        x[:, 2] = -4.25
+        x[:, p - 1] = x[:, 0]  # and an exactly duplicated one: the later column is aliased
+    y = 1.5 + x @ rng.uniform(-1, 1, size=p) + rng.normal(0, 0.7, size=N)
+    w = rng.uniform(0.5, 1.5, size=N) if method == "wls" else None
+    opt = dict(method=method, alpha=2.0 if method == "ridge" else 0.0)
+    cuts = [0, N // 3 + 1, N]
+    dev = _fit_from_row_shards(lib, x, y, w, cuts, **opt)
+    ora = oracle.fit_batch(np.array([0, N], dtype=np.int64), y, x, w, compute_inference=True, **opt)
+    assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label=f"clean shards p={p} {method}")
+    if const:
+        assert np.isnan(dev["coefficients"][0, 2]) and np.isnan(dev["coefficients"][0, p - 1])
+    # the same rows in different shard cuts: the sums differ in the last bits only
+    dev2 = _fit_from_row_shards(lib, x, y, w, [0, N // 2, N], **opt)
+    m = np.isfinite(dev["coefficients"])
+    assert np.allclose(dev["coefficients"][m], dev2["coefficients"][m], rtol=1e-10, atol=0)
 
 
 def test_sharded_single_group_fit_class(lib, oracle):

@@ -154,6 +154,11 @@ int main() {
 		cudaEventRecord(e0); dmma_kernel<1><<<sms * 4, 128>>>(out, iters); cudaEventRecord(e1); CK(cudaEventSynchronize(e1));
 		cudaEventElapsedTime(&ms, e0, e1);
 		printf("DMMA m8n8k4 dependent chain, 4 warps/SMSP-set: latency ~%.1f cycles @1.9GHz\n", ms * 1e-3 * 1.9e9 / iters);
+		for (int wps : {4, 8, 16}) { // warps per SM with 36 independent accumulator pairs each (the p = 64 Gram step)
+			cudaEventRecord(e0); dmma_kernel<36><<<sms, 32 * wps>>>(out, iters / 4); cudaEventRecord(e1); CK(cudaEventSynchronize(e1));
+			cudaEventElapsedTime(&ms, e0, e1);
+			printf("DMMA m8n8k4 x36 acc, %d warps/SM: %.2f TFLOP/s (%.3f ms)\n", wps, 2.0 * 256 * 36 * (iters / 4) * sms * wps / ms / 1e9, ms);
+		}
 		cudaEventRecord(e0); dmma16_kernel<<<blocks, thr>>>(out, iters / 4); cudaEventRecord(e1); CK(cudaEventSynchronize(e1));
 		cudaEventElapsedTime(&ms, e0, e1);
 		printf("DMMA m16n8k16 x4 acc: %.2f TFLOP/s (%.3f ms)\n", 2.0 * 2048 * 4 * (iters / 4) * blocks * (thr / 32) / ms / 1e9, ms);
