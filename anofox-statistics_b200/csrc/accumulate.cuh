@@ -437,13 +437,33 @@ template <int NT, bool SIDE, bool HASW, bool HAST> struct StepIn {
 	double yv, wv;
 	uint32_t tr;
 };
+// p0: the lane's pointer into tile 0 (tiles 1 .. NT-2 are +64 t bytes, same row stride st0); pl / stl: the
+// last tile, whose lanes may read y, the constant 1 or the zero padding instead.
+template <int OFF> __device__ __forceinline__ double lds_f64_off(uint32_t addr) {
+	double v;
+	asm volatile("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(addr), "n"(OFF));
+	return v;
+}
+template <int NT, int T> struct TileLoads {
+	static __device__ __forceinline__ void run(double (&v)[NT], uint32_t p0) {
+		v[T] = lds_f64_off<64 * T>(p0);
+		TileLoads<NT, T + 1>::run(v, p0);
+	}
+};
+template <int NT> struct TileLoads<NT, NT> {
+	static __device__ __forceinline__ void run(double (&)[NT], uint32_t) {}
+};
 template <int NT, bool SIDE, bool HASW, bool HAST>
-__device__ __forceinline__ void step_load(StepIn<NT, SIDE, HASW, HAST> &in, uint32_t (&pa)[NT], const uint32_t (&st)[NT],
-                                          uint32_t &py, uint32_t &pw, uint32_t &pt) {
+__device__ __forceinline__ void step_load(StepIn<NT, SIDE, HASW, HAST> &in, uint32_t &p0, uint32_t &pl, uint32_t st0,
+                                          uint32_t stl, uint32_t &py, uint32_t &pw, uint32_t &pt) {
+	{
+		double head[NT > 1 ? NT - 1 : 1];
+		TileLoads<(NT > 1 ? NT - 1 : 1), (NT > 1 ? 0 : 1)>::run(head, p0);
 #pragma unroll
-	for (int t = 0; t < NT; ++t) {
-		in.v[t] = lds_f64(pa[t]);
-		pa[t] += st[t];
+		for (int t = 0; t < NT - 1; ++t) in.v[t] = head[t];
+		in.v[NT - 1] = lds_f64(pl);
+		p0 += st0;
+		pl += stl;
 	}
 	if (SIDE) {
 		in.yv = lds_f64(py);
@@ -461,8 +481,8 @@ __device__ __forceinline__ void step_load(StepIn<NT, SIDE, HASW, HAST> &in, uint
 template <int NT, bool SIDE, bool HASW, bool HAST, bool TRACKNC, bool COUNTS>
 __device__ __forceinline__ void mma_step_pipe(WarpAcc<NT, SIDE> &A, double (&c0)[NT * (NT + 1) / 2],
                                               double (&c1)[NT * (NT + 1) / 2], StepIn<NT, SIDE, HASW, HAST> &in,
-                                              uint32_t (&pa)[NT], const uint32_t (&st)[NT], uint32_t &py, uint32_t &pw,
-                                              uint32_t &pt, const double (&sh)[NT], double shy, bool more) {
+                                              uint32_t &p0, uint32_t &pl, uint32_t st0, uint32_t stl, uint32_t &py,
+                                              uint32_t &pw, uint32_t &pt, const double (&sh)[NT], double shy, bool more) {
 	bool ok = true;
 	double wv = 1.0;
 	if (HASW) {
@@ -490,7 +510,7 @@ __device__ __forceinline__ void mma_step_pipe(WarpAcc<NT, SIDE> &A, double (&c0)
 		dy = in.yv - shy;
 		if (MASK) dy = ok ? dy : 0.0;
 	}
-	if (more) step_load<NT, SIDE, HASW, HAST>(in, pa, st, py, pw, pt);
+	if (more) step_load<NT, SIDE, HASW, HAST>(in, p0, pl, st0, stl, py, pw, pt);
 	int pair = 0;
 #pragma unroll
 	for (int ta = 0; ta < NT; ++ta)

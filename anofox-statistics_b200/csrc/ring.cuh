@@ -30,6 +30,8 @@
 
 namespace b200 {
 
+// tile counts whose CTAs hold only four consumer warps take the software-pipelined step (accumulate.cuh)
+template <int NT> constexpr bool kRingPipelined = NT >= 5;
 constexpr int kRingApron = 16;  // rows mirrored behind the ring end (>= rows of a quad - 1)
 constexpr int kRingMaxWin = 24; // windows in the ring at most
 
@@ -206,6 +208,7 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 	uint32_t kn_ph = 0;
 	int64_t edge = SR, ready = -15;
 	const uint32_t full0 = smem_u32(&full_bar[0]);
+	const int64_t la_rows = ring_rows / 4 > SR ? ring_rows / 4 : SR;
 	auto advance = [&]() {
 		++kn;
 		if (++kn_s == NS) {
@@ -228,9 +231,11 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			mbar_wait_addr(full0 + 8u * (uint32_t)kn_s, kn_ph);
 			advance();
 		}
-		// look ahead: take every further window that has already landed, so that the batch below runs over all
-		// rows on chip instead of the one window that was asked for
-		while (kn < nwin) {
+		// look ahead: take further windows that have already landed, so that the batch below runs over more than
+		// the one window that was asked for -- but not over the whole ring: rows are released at the end of a
+		// batch, and the producer needs released windows early enough to keep copies in flight
+		const int64_t la_end = need + la_rows;
+		while (kRingPipelined<NT> && kn < nwin && ready < la_end) {
 			if (issued <= kn) {
 				issued = ld_volatile_s32(&issued_s);
 				if (issued <= kn) break;
@@ -247,26 +252,34 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 		if (lane == 0) st_release_s64(&pos_s[cw], pos);
 	};
 	// per-lane address pattern of the tile columns: base + ring_row * rmul, step stride 4 * rmul
-	uint32_t base[NT], st[NT];
-#pragma unroll
-	for (int t = 0; t < NT; ++t) {
-		const int c = 8 * t + cl;
+	// Tiles 0 .. NT-2 hold feature columns only, so one pointer serves them all (tile t = +64 t bytes, row stride
+	// 8 p); only the last tile has lanes that read y, the constant 1 or the zero padding.
+	const uint32_t base0 = xs + (uint32_t)(rl * p + cl) * 8u, st0 = 32u * (uint32_t)p;
+	uint32_t baseL, stL;
+	{
+		const int c = 8 * (NT - 1) + cl;
 		if (c < p) {
-			base[t] = xs + (uint32_t)(rl * p + c) * 8u;
-			st[t] = 32u * (uint32_t)p;
+			baseL = xs + (uint32_t)(rl * p + c) * 8u;
+			stL = 32u * (uint32_t)p;
 		} else if (!SIDE && c == p) {
-			base[t] = ys + (uint32_t)rl * 8u;
-			st[t] = 32u;
+			baseL = ys + (uint32_t)rl * 8u;
+			stL = 32u;
 		} else if (!SIDE && c == p + 1) {
-			base[t] = kone;
-			st[t] = 0u;
+			baseL = kone;
+			stL = 0u;
 		} else {
-			base[t] = kzero;
-			st[t] = 0u;
+			baseL = kzero;
+			stL = 0u;
 		}
 	}
+	// the per-tile form the (rare) tail and shift code uses
+	auto tile_ptrs = [&](uint32_t (&b)[NT], uint32_t (&s)[NT]) {
 #pragma unroll
-	for (int t = 0; t < NT; ++t) asm volatile("" : "+r"(base[t]), "+r"(st[t])); // computed once, kept in registers
+		for (int t = 0; t < NT; ++t) {
+			b[t] = t < NT - 1 ? base0 + 64u * (uint32_t)t : baseL;
+			s[t] = t < NT - 1 ? st0 : stL;
+		}
+	};
 	uint32_t n_comb = 0; // team combines so far (parity of dep_bar / rel_bar)
 	int64_t g = ga + team;
 	int64_t nr0 = 0, nr1 = 0;
@@ -339,6 +352,8 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			ensure(r0 + f + 1);
 			uint32_t rf = (uint32_t)(rp0 + f);
 			if (rf >= (uint32_t)ring_rows) rf %= (uint32_t)ring_rows;
+			uint32_t base[NT], st[NT];
+			tile_ptrs(base, st);
 #pragma unroll
 			for (int t = 0; t < NT; ++t) {
 				const int c = 8 * t + cl;
@@ -370,35 +385,58 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			const int avail = av64 > (int64_t)n ? n : (int)av64;
 			const int span = avail - row - QR; // >= 0
 			const int nq = (slice ? span / rstep : span >> (ltw + (NSET == 4 ? 4 : (NSET == 2 ? 3 : 2)))) + 1;
-			uint32_t pa[NT];
-#pragma unroll
-			for (int t = 0; t < NT; ++t) pa[t] = base[t] + (uint32_t)rp * (st[t] >> 2);
 			uint32_t py = ys + (uint32_t)(rp + rl) * 8u, pw = ws + (uint32_t)(rp + rl) * 8u, pt = ts + (uint32_t)(rp + rl);
 			// quads of this batch: as many as have landed, up to the ring end
 			const int to_end = (ring_rows - rp + rstep - 1) / rstep;
 			const int nqe = nq < to_end ? nq : to_end;
-			StepIn<NT, SIDE, HASW, HAST> in;
-			step_load<NT, SIDE, HASW, HAST>(in, pa, st, py, pw, pt);
 			int q = 0;
-			do {
+			if constexpr (kRingPipelined<NT>) {
+				// few warps per SM (wide Gram): loads a step ahead, one pointer for all full tiles
+				uint32_t p0 = base0 + (uint32_t)rp * (st0 >> 2), pl = baseL + (uint32_t)rp * (stL >> 2);
+				StepIn<NT, SIDE, HASW, HAST> in;
+				step_load<NT, SIDE, HASW, HAST>(in, p0, pl, st0, stL, py, pw, pt);
+				do {
 #pragma unroll
-				for (int s = 0; s < NSET; ++s) {
-					if (s == NSET - 1) { // the next step is the first of the next quad
-#pragma unroll
-						for (int t = 0; t < NT; ++t) pa[t] += skip_rows * (st[t] >> 2);
-						py += skip_rows * 8u;
-						pw += skip_rows * 8u;
-						pt += skip_rows;
+					for (int s = 0; s < NSET; ++s) {
+						if (s == NSET - 1) { // the next step is the first of the next quad
+							p0 += skip_rows * (st0 >> 2);
+							pl += skip_rows * (stL >> 2);
+							py += skip_rows * 8u;
+							pw += skip_rows * 8u;
+							pt += skip_rows;
+						}
+						const bool more = s + 1 < NSET || q + 1 < nqe;
+						if (s == 0)
+							mma_step_pipe<NT, SIDE, HASW, HAST, HASW, false>(A, A.c0, A.c1, in, p0, pl, st0, stL, py, pw, pt, sh, shy, more);
+						else
+							mma_step_pipe<NT, SIDE, HASW, HAST, HASW, false>(A, e0[s - 1], e1[s - 1], in, p0, pl, st0, stL, py, pw, pt, sh, shy, more);
 					}
-					const bool more = s + 1 < NSET || q + 1 < nqe;
-					if (s == 0)
-						mma_step_pipe<NT, SIDE, HASW, HAST, HASW, false>(A, A.c0, A.c1, in, pa, st, py, pw, pt, sh, shy, more);
-					else
-						mma_step_pipe<NT, SIDE, HASW, HAST, HASW, false>(A, e0[s - 1], e1[s - 1], in, pa, st, py, pw, pt, sh, shy, more);
-				}
-				rp += rstep;
-				++q;
-			} while (q < nqe);
+					rp += rstep;
+					++q;
+				} while (q < nqe);
+			} else {
+				// many warps per SM hide the shared-memory latency by themselves: plain steps
+				uint32_t pa[NT], st[NT];
+				tile_ptrs(pa, st);
+#pragma unroll
+				for (int t = 0; t < NT; ++t) pa[t] += (uint32_t)rp * (st[t] >> 2);
+				do {
+#pragma unroll
+					for (int s = 0; s < NSET; ++s) {
+						if (s == 0)
+							mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
+						else
+							mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
+					}
+#pragma unroll
+					for (int t = 0; t < NT; ++t) pa[t] += skip_rows * (st[t] >> 2);
+					py += skip_rows * 8u;
+					pw += skip_rows * 8u;
+					pt += skip_rows;
+					rp += rstep;
+					++q;
+				} while (q < nqe);
+			}
 			if (!MASK) A.nv += NSET * q;
 			row += q * rstep;
 			if (rp >= ring_rows) rp -= ring_rows;
@@ -407,9 +445,10 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 		if (row < n) { // the group's last, partial quad
 			const int cnt = n - row;
 			ensure(r0 + n);
-			uint32_t pa[NT];
+			uint32_t pa[NT], st[NT];
+			tile_ptrs(pa, st);
 #pragma unroll
-			for (int t = 0; t < NT; ++t) pa[t] = base[t] + (uint32_t)rp * (st[t] >> 2);
+			for (int t = 0; t < NT; ++t) pa[t] += (uint32_t)rp * (st[t] >> 2);
 			uint32_t py = ys + (uint32_t)(rp + rl) * 8u, pw = ws + (uint32_t)(rp + rl) * 8u, pt = ts + (uint32_t)(rp + rl);
 			const int nfs = cnt >> 2;
 #pragma unroll
