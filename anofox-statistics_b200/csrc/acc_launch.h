@@ -3,6 +3,7 @@
 #pragma once
 #include "accumulate.cuh"
 #include "ring.cuh"
+#include "slice.cuh"
 
 namespace b200 {
 
@@ -14,7 +15,8 @@ constexpr int kStreamWarps = 8;
 	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st);                    \
 	cudaError_t launch_ring_nt##NT_(bool side, bool has_w, bool has_t, const RingArgs &a, int grid, size_t dyn,      \
 	                                cudaStream_t st);                                                                \
-	cudaError_t launch_redo_nt##NT_(bool side, const RingArgs &a, int grid, cudaStream_t st);
+	cudaError_t launch_redo_nt##NT_(bool side, const RingArgs &a, int grid, cudaStream_t st);                       \
+	cudaError_t launch_slice_nt##NT_(bool side, bool has_w, const SliceArgs &a, int grid, size_t dyn, cudaStream_t st);
 B200_DECLARE_NT(1)
 B200_DECLARE_NT(2)
 B200_DECLARE_NT(3)
@@ -47,6 +49,21 @@ cudaError_t launch_ring_t(const RingArgs &a, int grid, size_t dyn, cudaStream_t 
 	if (e != cudaSuccess) return e;
 	kern<<<grid, 32 * (NCW + 1), dyn, st>>>(a);
 	return cudaGetLastError();
+}
+
+// wide shapes only (five or more tiles): narrower shards stay on the ring kernel's slice mode
+constexpr int kSliceMinTiles = 5;
+template <int NT, bool SIDE, bool HASW>
+cudaError_t launch_slice_t(const SliceArgs &a, int grid, size_t dyn, cudaStream_t st) {
+	if constexpr (NT >= kSliceMinTiles) {
+		auto kern = acc_slice_kernel<NT, SIDE, HASW>;
+		cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+		if (e != cudaSuccess) return e;
+		kern<<<grid, 32 * (kSliceWarps + 1), dyn, st>>>(a);
+		return cudaGetLastError();
+	} else {
+		return cudaErrorInvalidValue;
+	}
 }
 
 #define B200_DEFINE_NT(NT_)                                                                                          \
@@ -85,6 +102,13 @@ cudaError_t launch_ring_t(const RingArgs &a, int grid, size_t dyn, cudaStream_t 
 		else                                                                                                         \
 			redo_kernel<NT_, false><<<grid, 256, 0, st>>>(a);                                                        \
 		return cudaGetLastError();                                                                                   \
+	}                                                                                                                \
+	cudaError_t launch_slice_nt##NT_(bool side, bool has_w, const SliceArgs &a, int grid, size_t dyn,                \
+	                                 cudaStream_t st) {                                                              \
+		if (side) return has_w ? launch_slice_t<NT_, true, true>(a, grid, dyn, st)                                   \
+		                       : launch_slice_t<NT_, true, false>(a, grid, dyn, st);                                 \
+		return has_w ? launch_slice_t<NT_, false, true>(a, grid, dyn, st)                                            \
+		             : launch_slice_t<NT_, false, false>(a, grid, dyn, st);                                          \
 	}                                                                                                                \
 	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st) {                   \
 		if (side)                                                                                                    \

@@ -353,6 +353,19 @@ static cudaError_t launch_ring(const RingArgs &a, bool hw, bool ht, int grid, si
 	LAUNCHED();
 	return e;
 }
+static cudaError_t launch_slice(const SliceArgs &a, bool hw, int grid, size_t dyn, cudaStream_t st) {
+	const Shape s = shape_of(a.p);
+	cudaError_t e = cudaErrorInvalidValue;
+	switch (s.nt) {
+	case 5: e = launch_slice_nt5(s.side, hw, a, grid, dyn, st); break;
+	case 6: e = launch_slice_nt6(s.side, hw, a, grid, dyn, st); break;
+	case 7: e = launch_slice_nt7(s.side, hw, a, grid, dyn, st); break;
+	case 8: e = launch_slice_nt8(s.side, hw, a, grid, dyn, st); break;
+	case 9: e = launch_slice_nt9(s.side, hw, a, grid, dyn, st); break;
+	}
+	LAUNCHED();
+	return e;
+}
 static cudaError_t launch_redo(const RingArgs &a, int grid, cudaStream_t st) {
 	const Shape s = shape_of(a.p);
 	cudaError_t e = cudaErrorInvalidValue;
@@ -1725,7 +1738,33 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	s.ring_partials = ws.ring_partials;
 	s.ring_n_part = units * ncw;
 	timer_mark(st);
-	if (n_rows > 0 && g_force_path.load() != 3) {
+	if (n_rows > 0 && g_force_path.load() != 3 && shp.nt >= kSliceMinTiles && g_force_path.load() != 4) {
+		// wide Gram: the split-role slice kernel (slice.cuh), 8 partial records per slice
+		SliceArgs sa;
+		sa.bounds = ws.slice_off;
+		sa.y = y;
+		sa.x = x;
+		sa.w = w;
+		sa.p = p;
+		sa.shift = shift;
+		sa.partials = ws.ring_partials;
+		sa.redo_count = ws.redo_count;
+		const int64_t row_bytes = 8 * (int64_t)(p + 1) + (w ? 8 : 0);
+		int sr = 64;
+		while (sr > 16 && (int64_t)sr * row_bytes * 4 > 216 * 1024) sr -= 16;
+		sa.win_rows = sr;
+		sa.x_slot = (uint32_t)(sr * p * 8 + 16);
+		sa.y_slot = (uint32_t)(sr * 8 + 16);
+		const int64_t slot_bytes = (int64_t)sa.x_slot + sa.y_slot * (w ? 2 : 1);
+		sa.n_win = (int)std::min<int64_t>(kSliceMaxWin, (216 * 1024) / slot_bytes);
+		auto a128 = [](int64_t v) { return (uint32_t)((v + 127) & ~(int64_t)127); };
+		sa.x_off = 0;
+		sa.y_off = a128((int64_t)sa.n_win * sa.x_slot);
+		sa.w_off = sa.y_off + a128((int64_t)sa.n_win * sa.y_slot);
+		const size_t dyn = sa.w_off + (w ? a128((int64_t)sa.n_win * sa.y_slot) : 0);
+		s.ring_n_part = units * kSliceWarps;
+		CU(launch_slice(sa, w != nullptr, units, dyn, st), "acc_slice_kernel");
+	} else if (n_rows > 0 && g_force_path.load() != 3) {
 		CU(launch_ring(r, w != nullptr, false, units, rg_.dyn_bytes, st), "acc_ring_kernel (slices)");
 	} else {
 		s.run_if = nullptr; // empty shard or A/B run: the checked streaming pass alone
