@@ -1750,8 +1750,7 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 		sa.partials = ws.ring_partials;
 		sa.redo_count = ws.redo_count;
 		const int64_t row_bytes = 8 * (int64_t)(p + 1) + (w ? 8 : 0);
-		int sr = 64;
-		while (sr > 16 && (int64_t)sr * row_bytes * 4 > 216 * 1024) sr -= 16;
+		const int sr = kSliceRows;
 		sa.win_rows = sr;
 		sa.x_slot = (uint32_t)(sr * p * 8 + 16);
 		sa.y_slot = (uint32_t)(sr * 8 + 16);

@@ -25,6 +25,7 @@ namespace b200 {
 constexpr int kSliceWarps = 8;   // consumer warps: 4 step lanes x 2 roles
 constexpr int kSliceMaxWin = 8;  // ring slots at most
 constexpr int kSliceRegs = 168;  // 9 warps: the fullest scheduler holds 3 -> 16384 / 96 = 170 registers
+constexpr int kSliceRows = 64;   // rows of a window (p <= 64: 4 windows of 64 rows are 135 KB at most)
 
 struct SliceArgs {
 	const int64_t *bounds; // [gridDim.x + 1] row bounds of the slices
@@ -165,12 +166,30 @@ __device__ __forceinline__ void slice_consume(const SliceArgs &a, unsigned char 
 		};
 		const int nfull = rows_in >> 2;
 		double v[NT], yv = 0.0, wv = 1.0;
-		int step = rq;
-		if (step < nfull) {
+		if (rows_in == kSliceRows) {
+			// full window: this warp's kSliceRows / 16 steps, straight-line. Per step: differences, then the next
+			// step's loads into the freed registers, then the DMMAs (which hide the load latency).
+			SliceLoads L = plan(rq);
+			slice_load<NT, SIDE, HASW>(v, yv, wv, L);
+#pragma unroll
+			for (int j = 0; j < kSliceRows / 16; ++j) {
+				SliceVals<NT> sv;
+				slice_prep<NT, SIDE, HASW, ROLE, false>(A, sv, v, yv, wv, sh, shy, true);
+				if (j + 1 < kSliceRows / 16) {
+					L.p0 += 4u * step_x;
+					if (kindL == 0) L.pl += 4u * step_x;
+					if (kindL == 1) L.pl += 128u;
+					L.py += 128u;
+					L.pw += 128u;
+					slice_load<NT, SIDE, HASW>(v, yv, wv, L);
+				}
+				slice_mma<NT, SIDE, HASW, ROLE>(A, sv);
+			}
+		} else if (rq < nfull) {
+			int step = rq;
 			slice_load<NT, SIDE, HASW>(v, yv, wv, plan(step));
 			for (;;) {
 				const int next = step + 4;
-				// differences first, then the next step's loads into the freed registers, then the DMMAs
 				SliceVals<NT> sv;
 				slice_prep<NT, SIDE, HASW, ROLE, false>(A, sv, v, yv, wv, sh, shy, true);
 				const bool more = next < nfull;

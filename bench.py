@@ -219,13 +219,21 @@ def run_c4(args, rank, world, local):
         achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
         flops = rows * k * (k + 1)  # symmetric Gram with the y and 1 columns, 2 flop per MAC on the triangle
         tf = flops / (acc_launch_ms * 1e-3) / 1e12 if acc_launch_ms > 0 else None
-        roofline = {"bound": "hbm", "kernel": "acc_stream_kernel<8,SIDE> (FP64 DMMA Gram of one row shard)",
-                    "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                    "frac": (achieved / peak) if achieved else None, "traffic": None,
-                    "algorithmic_bytes_per_launch": acc_bytes, "avg_launch_ms": acc_launch_ms,
-                    "fp64_algorithmic_tflops": tf, "fp64_nominal_peak_tflops": 40.0,
-                    "fp64_frac_of_nominal": (tf / 40.0) if tf else None,
-                    "note": "p = 64 is ~8.5 flop/B: the FP64 DMMA pipe co-bounds this kernel (SURVEY.md 8d)",
+        # p = 64 is ~8.5 flop/B: the FP64 tensor pipe bounds this kernel (floor 0.55 TFLOP / 37 TFLOP/s = 15 ms per
+        # GPU), HBM is the lower floor (65 GB / 6.5 TB/s = 9.9 ms). Peak = DMMA.8x8x4 issue rate measured on this
+        # pool by tools/microbench.cu (profiles/r01d_microbench.txt): 37.0 TFLOP/s at 1965 MHz.
+        dmma_peak = 37.0
+        roofline = {"bound": "tensor", "kernel": "acc_slice_kernel<8,SIDE> (FP64 DMMA Gram of one row shard, "
+                                                 "split-role warps, TMA-fed ring)",
+                    "achieved": tf, "peak": dmma_peak,
+                    "peak_source": "measured FP64 DMMA m8n8k4 rate, tools/microbench.cu (nominal 40)",
+                    "unit": "TFLOP/s", "frac": (tf / dmma_peak) if tf else None, "traffic": None,
+                    "algorithmic_flops_per_launch": flops, "algorithmic_bytes_per_launch": acc_bytes,
+                    "avg_launch_ms": acc_launch_ms,
+                    "hbm_achieved_gbs": achieved, "hbm_peak_gbs": peak, "hbm_peak_source": peak_src,
+                    "hbm_frac": (achieved / peak) if achieved else None,
+                    "note": "algorithmic flops = rows * k(k+1), k = p + 2 (symmetric Gram with the y and 1 columns); "
+                            "the kernel executes 36 8x8x4 tile products per 4 rows = 4608 flop/row (+4 %)",
                     "reduce_and_split_ms": red_ms / max(calls, 1)}
         line = {"metric": "rows_per_sec", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
