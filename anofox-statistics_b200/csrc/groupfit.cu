@@ -203,6 +203,73 @@ __global__ void predict_kernel(const int64_t *__restrict__ offsets, int64_t n_gr
 	}
 }
 
+// Same predictions for p = 2, 4, 8, 16 with fully coalesced reads: P/2 lanes share a row (one 16-byte load
+// each, a warp-wide load instruction covers 512 contiguous bytes), the row's dot product meets in a shuffle
+// tree and the row's first lane writes the three outputs. x must be 16-byte aligned.
+template <int P>
+__global__ void __launch_bounds__(256) predict_flat_kernel(const int64_t *__restrict__ offsets, int64_t n_groups,
+                                                           const double *__restrict__ x, FitParams Pm,
+                                                           AnofoxB200FitOutputs fit, AnofoxB200PredictOutputs out) {
+	constexpr int LPR = P / 2, RPW = 32 / LPR; // lanes per row, rows per warp-wide load
+	const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (g >= n_groups) return;
+	const int64_t r0 = offsets[g], r1 = offsets[g + 1];
+	const double nanv = nan_f64();
+	const bool ok = fit.status[g] == 0;
+	const int sub = lane % LPR, rw = lane / LPR;
+	double b0 = 0.0, margin = 0.0, c0 = 0.0, c1 = 0.0;
+	bool n0 = true, n1 = true;
+	if (ok) {
+		const double icpt = fit.intercept[g];
+		const bool has_i = !isnan(icpt);
+		b0 = has_i ? icpt : 0.0;
+		const double rse = fit.residual_std_error[g];
+		const int64_t n = fit.n_observations[g];
+		if (!(isnan(rse) || rse <= 0.0 || n <= (int64_t)P + 1)) {
+			const int64_t kk = (int64_t)P + (has_i ? 1 : 0);
+			const int64_t df = n > kk ? n - kk : 0;
+			if (df > 0) {
+				const double tc = (Pm.tcrit && df <= kTcritTable) ? Pm.tcrit[df] : t_critical_dev(Pm.level, (double)df);
+				if (!isnan(tc)) margin = tc * (rse * sqrt(1.0 + 1.0 / (double)n));
+			}
+		}
+		c0 = fit.coefficients[g * P + 2 * sub];
+		c1 = fit.coefficients[g * P + 2 * sub + 1];
+		n0 = isnan(c0); // aliased / constant columns contribute nothing (lib.rs:2292-2300)
+		n1 = isnan(c1);
+	}
+	const double2 *xv = reinterpret_cast<const double2 *>(x);
+	constexpr int U = 4; // independent loads in flight per lane
+	for (int64_t rb = r0; rb < r1; rb += (int64_t)RPW * U) {
+		double2 v[U];
+#pragma unroll
+		for (int u = 0; u < U; ++u) {
+			const int64_t r = rb + u * RPW + rw;
+			v[u] = r < r1 ? __ldg(xv + (r * P) / 2 + sub) : make_double2(0.0, 0.0);
+		}
+#pragma unroll
+		for (int u = 0; u < U; ++u) {
+			const int64_t r = rb + u * RPW + rw;
+			double s = (n0 ? 0.0 : c0 * v[u].x) + (n1 ? 0.0 : c1 * v[u].y);
+#pragma unroll
+			for (int m = 1; m < LPR; m <<= 1) s += __shfl_xor_sync(0xffffffffu, s, m);
+			if (sub == 0 && r < r1) {
+				double yh = nanv, lo = nanv, hi = nanv;
+				s += b0;
+				if (ok && finite_f64(s)) { // ols_predict_aggregate.cpp:409-417
+					yh = s;
+					lo = s - margin;
+					hi = s + margin;
+				}
+				out.yhat[r] = yh;
+				out.yhat_lower[r] = lo;
+				out.yhat_upper[r] = hi;
+			}
+		}
+	}
+}
+
 // Shifted moment block of the row-sharded path -> standard record. The block layout is the
 // record without header rewrite: we only need to splice shift and cdev in.
 __global__ void assemble_record_kernel(const double *__restrict__ moments, const double *__restrict__ cdev,
@@ -1106,7 +1173,17 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	if (pred && N > 0) {
 		const int threads = 256;
 		const unsigned blocks = (unsigned)((G * 32 + threads - 1) / threads);
-		predict_kernel<<<blocks, threads, 0, st>>>(offsets, G, x, p, P, fo, *pred);
+		const bool flat = (((uintptr_t)x) & 15) == 0;
+		if (flat && p == 2)
+			predict_flat_kernel<2><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred);
+		else if (flat && p == 4)
+			predict_flat_kernel<4><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred);
+		else if (flat && p == 8)
+			predict_flat_kernel<8><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred);
+		else if (flat && p == 16)
+			predict_flat_kernel<16><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred);
+		else
+			predict_kernel<<<blocks, threads, 0, st>>>(offsets, G, x, p, P, fo, *pred);
 		LAUNCHED();
 		CU(cudaGetLastError(), "predict_kernel");
 	}
