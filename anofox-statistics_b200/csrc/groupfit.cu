@@ -1195,11 +1195,25 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 // ---------------------------------------------------------------------------------------------
 struct HostContext {
 	std::mutex mu;
-	cudaStream_t stream = nullptr;
+	cudaStream_t stream = nullptr;           // compute
+	cudaStream_t in_stream = nullptr;        // host -> device copies of the chunks
+	cudaStream_t out_stream = nullptr;       // device -> host copies of finished chunks
+	static constexpr int kMaxChunks = 16;
+	cudaEvent_t in_ev[kMaxChunks], done_ev[kMaxChunks];
+	bool events = false;
 	unsigned char *dev = nullptr;
 	size_t dev_bytes = 0;
 	int ensure(size_t bytes, AnofoxError *err) {
 		if (!stream) CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "cudaStreamCreate");
+		if (!in_stream) CU(cudaStreamCreateWithFlags(&in_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+		if (!out_stream) CU(cudaStreamCreateWithFlags(&out_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+		if (!events) {
+			for (int i = 0; i < kMaxChunks; ++i) {
+				CU(cudaEventCreateWithFlags(&in_ev[i], cudaEventDisableTiming), "cudaEventCreate");
+				CU(cudaEventCreateWithFlags(&done_ev[i], cudaEventDisableTiming), "cudaEventCreate");
+			}
+			events = true;
+		}
 		if (bytes > dev_bytes) {
 			if (dev) cudaFree(dev);
 			dev = nullptr;
@@ -1229,6 +1243,12 @@ struct DevLayout { // device mirror of one host batch
 	}
 };
 
+// offsets of a chunk of groups, relative to the chunk's first row
+__global__ void rebase_offsets_kernel(const int64_t *__restrict__ in, int64_t n, int64_t r0, int64_t *__restrict__ out) {
+	const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) out[i] = in[i] - r0;
+}
+
 static int fit_host(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w,
                     const uint8_t *train, int64_t N, int p, const AnofoxB200FitOptions *opt,
                     const AnofoxB200FitOutputs *out, const AnofoxB200PredictOutputs *pred, AnofoxError *err,
@@ -1246,11 +1266,29 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 	HostContext &c = host_ctx();
 	std::lock_guard<std::mutex> lock(c.mu);
 	DeviceInfo &di = device_info();
+	// Chunks of whole groups, balanced by rows: the copy of chunk i + 1 to the device, the kernels of chunk i and
+	// the copy of chunk i - 1's results back to the host run on three streams (PCIe is full duplex and the
+	// kernels are ~2 % of a host-to-host call, so the call approaches the one-way transfer time of its inputs).
+	int nch = 1;
+	const size_t in_bytes = (size_t)N * ((size_t)p + 1 + (w ? 1 : 0)) * 8;
+	if (G >= 1024 && in_bytes >= ((size_t)64 << 20)) nch = (int)std::min<size_t>(8, in_bytes >> 25);
+	int64_t gb[HostContext::kMaxChunks + 1];
+	gb[0] = 0;
+	for (int i = 1; i < nch; ++i) {
+		const int64_t target = (N / nch) * i;
+		const int64_t g = std::lower_bound(offsets, offsets + G + 1, target) - offsets;
+		gb[i] = std::min<int64_t>(G, std::max<int64_t>(g, gb[i - 1]));
+	}
+	gb[nch] = G;
 	Workspace wsz;
-	const size_t ws_bytes = carve(wsz, nullptr, G, N, p, di.sms);
+	size_t ws_bytes = carve(wsz, nullptr, G, N, p, di.sms);
+	if (nch > 1)
+		for (int i = 0; i < nch; ++i)
+			ws_bytes = std::max(ws_bytes, carve(wsz, nullptr, gb[i + 1] - gb[i], offsets[gb[i + 1]] - offsets[gb[i]], p, di.sms));
 	DevLayout L;
 	const int64_t G1 = std::max<int64_t>(G, 1), N1 = std::max<int64_t>(N, 1);
 	const size_t o_off = L.take((size_t)(G + 1) * 8), o_y = L.take((size_t)N1 * 8), o_x = L.take((size_t)N1 * p * 8);
+	const size_t o_off2 = L.take((size_t)(G + 1 + nch) * 8);
 	const size_t o_w = w ? L.take((size_t)N1 * 8) : 0, o_t = train ? L.take((size_t)N1) : 0;
 	const size_t o_gp = L.take((size_t)G1 * p * 8 * (inf ? 6 : 1));
 	const size_t o_g = L.take((size_t)G1 * 8 * 12);
@@ -1259,82 +1297,123 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 	int rc = c.ensure(L.off, err);
 	if (rc) return rc;
 	unsigned char *d = c.dev;
-	cudaStream_t st = c.stream;
-	CU(cudaMemcpyAsync(d + o_off, offsets, (size_t)(G + 1) * 8, cudaMemcpyHostToDevice, st), "H2D offsets");
-	if (N > 0) {
-		CU(cudaMemcpyAsync(d + o_y, y, (size_t)N * 8, cudaMemcpyHostToDevice, st), "H2D y");
-		CU(cudaMemcpyAsync(d + o_x, x, (size_t)N * p * 8, cudaMemcpyHostToDevice, st), "H2D x");
-		if (w) CU(cudaMemcpyAsync(d + o_w, w, (size_t)N * 8, cudaMemcpyHostToDevice, st), "H2D w");
-		if (train) CU(cudaMemcpyAsync(d + o_t, train, (size_t)N, cudaMemcpyHostToDevice, st), "H2D train");
-	}
-	AnofoxB200FitOutputs dout;
-	memset(&dout, 0, sizeof dout);
-	double *gp = (double *)(d + o_gp), *gs = (double *)(d + o_g);
-	dout.coefficients = gp;
-	if (inf) {
-		dout.std_errors = gp + (size_t)G1 * p * 1;
-		dout.t_values = gp + (size_t)G1 * p * 2;
-		dout.p_values = gp + (size_t)G1 * p * 3;
-		dout.ci_lower = gp + (size_t)G1 * p * 4;
-		dout.ci_upper = gp + (size_t)G1 * p * 5;
-	}
-	dout.intercept = gs + G1 * 0;
-	dout.r_squared = gs + G1 * 1;
-	dout.adj_r_squared = gs + G1 * 2;
-	dout.residual_std_error = gs + G1 * 3;
-	dout.n_observations = (int64_t *)(gs + G1 * 4);
-	dout.status = (int32_t *)(gs + G1 * 5);
-	dout.f_statistic = gs + G1 * 6;
-	dout.f_pvalue = gs + G1 * 7;
-	dout.has_inference = (uint8_t *)(gs + G1 * 8);
-	dout.aic = gs + G1 * 9;
-	dout.bic = gs + G1 * 10;
-	dout.rss = gs + G1 * 11;
-	AnofoxB200PredictOutputs dpred;
-	memset(&dpred, 0, sizeof dpred);
-	if (pred) {
-		double *pp = (double *)(d + o_pred);
-		dpred.yhat = pp;
-		dpred.yhat_lower = pp + N1;
-		dpred.yhat_upper = pp + 2 * N1;
-		dpred.is_training = (uint8_t *)(pp + 3 * N1);
-	}
-	rc = fit_device((const int64_t *)(d + o_off), G, (const double *)(d + o_y), (const double *)(d + o_x),
-	                w ? (const double *)(d + o_w) : nullptr, train ? (const uint8_t *)(d + o_t) : nullptr, N, p, opt, dout,
-	                pred ? &dpred : nullptr, d + o_ws, ws_bytes, st, err, min_state_rows);
-	if (rc) return rc;
-	auto back = [&](void *dst, const void *src, size_t bytes) {
-		return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
-	};
-	if (out && G > 0) {
-		CU(back(out->coefficients, dout.coefficients, (size_t)G * p * 8), "D2H");
-		CU(back(out->intercept, dout.intercept, (size_t)G * 8), "D2H");
-		CU(back(out->r_squared, dout.r_squared, (size_t)G * 8), "D2H");
-		CU(back(out->adj_r_squared, dout.adj_r_squared, (size_t)G * 8), "D2H");
-		CU(back(out->residual_std_error, dout.residual_std_error, (size_t)G * 8), "D2H");
-		CU(back(out->n_observations, dout.n_observations, (size_t)G * 8), "D2H");
-		CU(back(out->status, dout.status, (size_t)G * 4), "D2H");
-		if (inf) {
-			CU(back(out->std_errors, dout.std_errors, (size_t)G * p * 8), "D2H");
-			CU(back(out->t_values, dout.t_values, (size_t)G * p * 8), "D2H");
-			CU(back(out->p_values, dout.p_values, (size_t)G * p * 8), "D2H");
-			CU(back(out->ci_lower, dout.ci_lower, (size_t)G * p * 8), "D2H");
-			CU(back(out->ci_upper, dout.ci_upper, (size_t)G * p * 8), "D2H");
-			CU(back(out->f_statistic, dout.f_statistic, (size_t)G * 8), "D2H");
-			CU(back(out->f_pvalue, dout.f_pvalue, (size_t)G * 8), "D2H");
-			CU(back(out->has_inference, dout.has_inference, (size_t)G), "D2H");
+	cudaStream_t st = c.stream, sin = nch > 1 ? c.in_stream : c.stream, sout = nch > 1 ? c.out_stream : c.stream;
+	// ---- host -> device: offsets first, then the chunks in order ----
+	CU(cudaMemcpyAsync(d + o_off, offsets, (size_t)(G + 1) * 8, cudaMemcpyHostToDevice, sin), "H2D offsets");
+	auto push = [&](int i) -> int { // chunk i's rows to the device
+		const int64_t r0 = offsets[gb[i]], nr = offsets[gb[i + 1]] - r0;
+		if (nr > 0) {
+			CU(cudaMemcpyAsync(d + o_y + (size_t)r0 * 8, y + r0, (size_t)nr * 8, cudaMemcpyHostToDevice, sin), "H2D y");
+			CU(cudaMemcpyAsync(d + o_x + (size_t)r0 * p * 8, x + r0 * p, (size_t)nr * p * 8, cudaMemcpyHostToDevice, sin), "H2D x");
+			if (w) CU(cudaMemcpyAsync(d + o_w + (size_t)r0 * 8, w + r0, (size_t)nr * 8, cudaMemcpyHostToDevice, sin), "H2D w");
+			if (train) CU(cudaMemcpyAsync(d + o_t + (size_t)r0, train + r0, (size_t)nr, cudaMemcpyHostToDevice, sin), "H2D train");
 		}
-		CU(back(out->aic, dout.aic, (size_t)G * 8), "D2H");
-		CU(back(out->bic, dout.bic, (size_t)G * 8), "D2H");
-		CU(back(out->rss, dout.rss, (size_t)G * 8), "D2H");
+		if (nch > 1) CU(cudaEventRecord(c.in_ev[i], sin), "event");
+		return 0;
+	};
+	// two chunks ahead of the kernels (pinned host memory: the calls return at once; pageable memory: the staged
+	// copy of chunk i + 2 overlaps the kernels of chunk i)
+	for (int i = 0; i < std::min(nch, 2); ++i)
+		if ((rc = push(i))) return rc;
+	double *gp = (double *)(d + o_gp), *gs = (double *)(d + o_g);
+	auto back = [&](void *dst, const void *src, size_t bytes) {
+		return (dst && bytes) ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, sout) : cudaSuccess;
+	};
+	for (int i = 0; i < nch; ++i) {
+		const int64_t g0 = gb[i], Gc = gb[i + 1] - g0;
+		const int64_t r0 = offsets[g0], Nc = offsets[gb[i + 1]] - r0;
+		if (Gc <= 0) {
+			if (i + 2 < nch && (rc = push(i + 2))) return rc;
+			continue;
+		}
+		// device views of this chunk: every per-group array starts at group g0, every per-row array at row r0
+		AnofoxB200FitOutputs dout;
+		memset(&dout, 0, sizeof dout);
+		dout.coefficients = gp + (size_t)g0 * p;
+		if (inf) {
+			dout.std_errors = gp + (size_t)G1 * p * 1 + (size_t)g0 * p;
+			dout.t_values = gp + (size_t)G1 * p * 2 + (size_t)g0 * p;
+			dout.p_values = gp + (size_t)G1 * p * 3 + (size_t)g0 * p;
+			dout.ci_lower = gp + (size_t)G1 * p * 4 + (size_t)g0 * p;
+			dout.ci_upper = gp + (size_t)G1 * p * 5 + (size_t)g0 * p;
+		}
+		dout.intercept = gs + G1 * 0 + g0;
+		dout.r_squared = gs + G1 * 1 + g0;
+		dout.adj_r_squared = gs + G1 * 2 + g0;
+		dout.residual_std_error = gs + G1 * 3 + g0;
+		dout.n_observations = (int64_t *)(gs + G1 * 4) + g0;
+		dout.status = (int32_t *)(gs + G1 * 5) + g0;
+		dout.f_statistic = gs + G1 * 6 + g0;
+		dout.f_pvalue = gs + G1 * 7 + g0;
+		dout.has_inference = (uint8_t *)(gs + G1 * 8) + g0;
+		dout.aic = gs + G1 * 9 + g0;
+		dout.bic = gs + G1 * 10 + g0;
+		dout.rss = gs + G1 * 11 + g0;
+		AnofoxB200PredictOutputs dpred;
+		memset(&dpred, 0, sizeof dpred);
+		if (pred) {
+			double *pp = (double *)(d + o_pred);
+			dpred.yhat = pp + r0;
+			dpred.yhat_lower = pp + N1 + r0;
+			dpred.yhat_upper = pp + 2 * N1 + r0;
+			dpred.is_training = (uint8_t *)(pp + 3 * N1) + r0;
+		}
+		const int64_t *doff = (const int64_t *)(d + o_off) + g0;
+		if (nch > 1) {
+			CU(cudaStreamWaitEvent(st, c.in_ev[i], 0), "wait");
+			int64_t *reb = (int64_t *)(d + o_off2) + g0 + i;
+			rebase_offsets_kernel<<<(unsigned)((Gc + 1 + 255) / 256), 256, 0, st>>>(doff, Gc + 1, r0, reb);
+			LAUNCHED();
+			CU(cudaGetLastError(), "rebase_offsets_kernel");
+			doff = reb;
+		}
+		rc = fit_device(doff, Gc, (const double *)(d + o_y) + r0, (const double *)(d + o_x) + r0 * p,
+		                w ? (const double *)(d + o_w) + r0 : nullptr, train ? (const uint8_t *)(d + o_t) + r0 : nullptr, Nc, p,
+		                opt, dout, pred ? &dpred : nullptr, d + o_ws, ws_bytes, st, err, min_state_rows);
+		if (rc) {
+			cudaDeviceSynchronize();
+			return rc;
+		}
+		if (i + 2 < nch && (rc = push(i + 2))) return rc;
+		if (nch > 1) {
+			CU(cudaEventRecord(c.done_ev[i], st), "event");
+			CU(cudaStreamWaitEvent(sout, c.done_ev[i], 0), "wait");
+		}
+		// ---- device -> host: this chunk's slice of every output array ----
+		if (out) {
+			const size_t gpn = (size_t)Gc * p * 8, gn = (size_t)Gc * 8;
+			auto at = [&](double *h, size_t k) { return h ? h + (size_t)g0 * k : nullptr; };
+			CU(back(at(out->coefficients, p), dout.coefficients, gpn), "D2H");
+			CU(back(at(out->intercept, 1), dout.intercept, gn), "D2H");
+			CU(back(at(out->r_squared, 1), dout.r_squared, gn), "D2H");
+			CU(back(at(out->adj_r_squared, 1), dout.adj_r_squared, gn), "D2H");
+			CU(back(at(out->residual_std_error, 1), dout.residual_std_error, gn), "D2H");
+			CU(back(out->n_observations ? out->n_observations + g0 : nullptr, dout.n_observations, gn), "D2H");
+			CU(back(out->status ? out->status + g0 : nullptr, dout.status, (size_t)Gc * 4), "D2H");
+			if (inf) {
+				CU(back(at(out->std_errors, p), dout.std_errors, gpn), "D2H");
+				CU(back(at(out->t_values, p), dout.t_values, gpn), "D2H");
+				CU(back(at(out->p_values, p), dout.p_values, gpn), "D2H");
+				CU(back(at(out->ci_lower, p), dout.ci_lower, gpn), "D2H");
+				CU(back(at(out->ci_upper, p), dout.ci_upper, gpn), "D2H");
+				CU(back(at(out->f_statistic, 1), dout.f_statistic, gn), "D2H");
+				CU(back(at(out->f_pvalue, 1), dout.f_pvalue, gn), "D2H");
+				CU(back(out->has_inference ? out->has_inference + g0 : nullptr, dout.has_inference, (size_t)Gc), "D2H");
+			}
+			CU(back(at(out->aic, 1), dout.aic, gn), "D2H");
+			CU(back(at(out->bic, 1), dout.bic, gn), "D2H");
+			CU(back(at(out->rss, 1), dout.rss, gn), "D2H");
+		}
+		if (pred && Nc > 0) {
+			CU(back(pred->yhat + r0, dpred.yhat, (size_t)Nc * 8), "D2H");
+			CU(back(pred->yhat_lower + r0, dpred.yhat_lower, (size_t)Nc * 8), "D2H");
+			CU(back(pred->yhat_upper + r0, dpred.yhat_upper, (size_t)Nc * 8), "D2H");
+			CU(back(pred->is_training + r0, dpred.is_training, (size_t)Nc), "D2H");
+		}
 	}
-	if (pred && N > 0) {
-		CU(back(pred->yhat, dpred.yhat, (size_t)N * 8), "D2H");
-		CU(back(pred->yhat_lower, dpred.yhat_lower, (size_t)N * 8), "D2H");
-		CU(back(pred->yhat_upper, dpred.yhat_upper, (size_t)N * 8), "D2H");
-		CU(back(pred->is_training, dpred.is_training, (size_t)N), "D2H");
-	}
+	CU(cudaStreamSynchronize(sin), "sync");
 	CU(cudaStreamSynchronize(st), "sync");
+	if (sout != st) CU(cudaStreamSynchronize(sout), "sync");
 	return 0;
 }
 

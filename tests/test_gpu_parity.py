@@ -697,6 +697,48 @@ def test_device_pointer_api_matches_host_api(lib):
         assert np.array_equal(v.cpu().numpy(), host[k], equal_nan=True), k  # same kernels, same bits
 
 
+def test_host_api_chunked_pipeline(lib, oracle):
+    """Host-pointer calls above 64 MB run as chunks of whole groups on three streams (copy in / kernels / copy
+    out). The results must not depend on the chunking: same bits as the one-shot device-pointer call, and parity
+    with the oracle on a sample of the groups. Covers fit and fit_predict."""
+    import torch
+    rng = np.random.default_rng(12)
+    c = make_case(rng, 45_000, 30, 90, 5, dirty=True, weights=True)
+    G, N = len(c["offsets"]) - 1, len(c["y"])
+    assert N * 7 * 8 > 64 << 20
+    opt = dict(method="wls", compute_inference=True)
+    host = lib.fit_batch_host(c["offsets"], c["y"], c["x"], c["w"], **opt)
+    f = lib.DeviceFit(G, N, 5, inference=True)
+    t = {k: torch.tensor(c[k], device="cuda") for k in ("offsets", "y", "x", "w")}
+    out = f.fit(t["offsets"], t["y"], t["x"], t["w"], **opt)
+    torch.cuda.synchronize()
+    for k, v in out.items():
+        assert np.array_equal(v.cpu().numpy(), host[k], equal_nan=True), k
+    # oracle parity on the groups around the chunk boundaries and at both ends
+    sel = np.unique(np.concatenate([np.arange(0, 50), np.arange(G // 3 - 200, G // 3 + 200),
+                                    np.arange(G // 2 - 200, G // 2 + 200), np.arange(2 * G // 3 - 200, 2 * G // 3 + 200),
+                                    np.arange(G - 50, G)]))
+    for a, b in [(sel[0], sel[49] + 1), (G // 3 - 200, G // 3 + 200), (G - 50, G)]:
+        off = c["offsets"][a:b + 1]
+        r0, r1 = off[0], off[-1]
+        ora = oracle.fit_batch(off - r0, c["y"][r0:r1], c["x"][r0:r1], c["w"][r0:r1], **opt)
+        dev = {k: v[a:b] for k, v in host.items()}
+        assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label=f"chunked host groups {a}:{b}")
+    # fit_predict through the same pipeline
+    y2 = c["y"].copy()
+    y2[rng.uniform(size=N) < 0.2] = np.nan
+    pd, fd = lib.fit_predict_batch_host(c["offsets"], y2, c["x"], None, None)
+    a, b = G // 2 - 100, G // 2 + 100
+    off = c["offsets"][a:b + 1]
+    r0, r1 = off[0], off[-1]
+    po, fo = oracle.fit_predict_batch(off - r0, y2[r0:r1], c["x"][r0:r1], None, None)
+    assert_fit_parity({k: v[a:b] for k, v in fd.items()}, fo, rtol=1e-9, label="chunked predict fit")
+    m = np.isfinite(po["yhat_upper"])
+    assert np.array_equal(np.isnan(pd["yhat_upper"][r0:r1]), ~m)
+    assert np.allclose(pd["yhat_upper"][r0:r1][m], po["yhat_upper"][m], rtol=1e-9, atol=0)
+    assert np.array_equal(pd["is_training"][r0:r1], po["is_training"])
+
+
 def test_full_size_properties_config2(lib):
     """BASELINE config 2 at full size (1 M groups x 50 rows x 5 features, inference on): size-independent
     properties instead of an oracle run -- scale equivariance, group-permutation invariance of the results,
