@@ -359,6 +359,19 @@ __device__ __forceinline__ void lane_pointers(const SmemGroup &g, int p, int lan
 	}
 }
 
+// Bank swizzle for rows that are a multiple of 128 bytes (p % 16 == 0): the four rows of a step then start in
+// the same bank, and the 8-byte loads of one tile touch only half of the banks four times over. Lanes of odd
+// rows therefore load tile t ^ 1 in the slot of tile t (their pointers are swapped once, at set-up) and swap
+// the two values back here: every load instruction covers all 32 banks, two wavefronts instead of four.
+template <int NT> __device__ __forceinline__ void swizzle_pairs(double (&v)[NT], bool swz) {
+#pragma unroll
+	for (int t = 0; t + 1 < NT; t += 2) {
+		const double a = v[t], b = v[t + 1];
+		v[t] = swz ? b : a;
+		v[t + 1] = swz ? a : b;
+	}
+}
+
 // c0 / c1: the DMMA accumulator set this step adds into (A's own, or one of the extra sets the ring kernel
 // rotates through to break the DMMA -> DMMA dependency between consecutive steps).
 // TRACKNC: keep the exact per-element constant-column flag (one DSETP per tile and step).
@@ -366,13 +379,14 @@ template <int NT, bool SIDE, bool HASW, bool HAST, bool TAIL, bool TRACKNC, bool
 __device__ __forceinline__ void mma_step(WarpAcc<NT, SIDE> &A, double (&c0)[NT * (NT + 1) / 2],
                                          double (&c1)[NT * (NT + 1) / 2], uint32_t (&pa)[NT], const uint32_t (&st)[NT],
                                          uint32_t &py, uint32_t &pw, uint32_t &pt, const double (&sh)[NT], double shy,
-                                         bool in_range) {
+                                         bool in_range, bool swz = false) {
 	double v[NT];
 #pragma unroll
 	for (int t = 0; t < NT; ++t) {
 		v[t] = lds_f64(pa[t]);
 		pa[t] += st[t];
 	}
+	swizzle_pairs<NT>(v, swz);
 	bool ok = true;
 	double wv = 1.0, yv = 0.0;
 	if (SIDE) {

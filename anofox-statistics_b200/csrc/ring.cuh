@@ -280,6 +280,19 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			s[t] = t < NT - 1 ? st0 : stL;
 		}
 	};
+	// rows of a multiple of 128 bytes: odd rows load the tiles of a pair in swapped order (swizzle_pairs)
+	const bool swz = (p % 16 == 0) && (rl & 1);
+	auto tile_ptrs_swz = [&](uint32_t (&b)[NT], uint32_t (&s)[NT]) {
+		tile_ptrs(b, s);
+		if (p % 16 == 0) {
+#pragma unroll
+			for (int t = 0; t + 1 < NT; t += 2) {
+				const uint32_t lo = b[t], hi = b[t + 1];
+				b[t] = swz ? hi : lo;
+				b[t + 1] = swz ? lo : hi;
+			}
+		}
+	};
 	uint32_t n_comb = 0; // team combines so far (parity of dep_bar / rel_bar)
 	int64_t g = ga + team;
 	int64_t nr0 = 0, nr1 = 0;
@@ -417,16 +430,16 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			} else {
 				// many warps per SM hide the shared-memory latency by themselves: plain steps
 				uint32_t pa[NT], st[NT];
-				tile_ptrs(pa, st);
+				tile_ptrs_swz(pa, st);
 #pragma unroll
 				for (int t = 0; t < NT; ++t) pa[t] += (uint32_t)rp * (st[t] >> 2);
 				do {
 #pragma unroll
 					for (int s = 0; s < NSET; ++s) {
 						if (s == 0)
-							mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true);
+							mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, A.c0, A.c1, pa, st, py, pw, pt, sh, shy, true, swz);
 						else
-							mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true);
+							mma_step<NT, SIDE, HASW, HAST, false, HASW, false>(A, e0[s - 1], e1[s - 1], pa, st, py, pw, pt, sh, shy, true, swz);
 					}
 #pragma unroll
 					for (int t = 0; t < NT; ++t) pa[t] += skip_rows * (st[t] >> 2);

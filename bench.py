@@ -417,9 +417,16 @@ def main():
     acc_launch_ms = acc_ms / max(calls, 1)
     acc_bytes = N * (8 * (p + 1) + (8 if method == "wls" else 0)) + 8 * (G + 1)
     achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
-    roofline = {"bound": "hbm", "kernel": "acc_resident_kernel (segmented moment accumulation)",
+    path, lanes = pkg.plan(G, N, p, method == "wls", predict)
+    if path == "fused":
+        kname = "fit_small_kernel<%d> (rows -> transposed moment records, %d lanes per group, TMA-staged)" % (p, lanes)
+    else:
+        kname = "acc_ring_kernel (streaming ring of TMA windows, FP64 DMMA moment accumulation)"
+    # measured traffic of the same kernel from the committed ncu --set full capture (profiles/), per launch
+    traffic = {"C2": 2.74e9, "C3r": 27.9e9}.get(args.workload)
+    roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                 "algorithmic_bytes_per_launch": acc_bytes, "avg_launch_ms": acc_launch_ms,
                 "solve_stage_ms": solve_ms / max(calls, 1), "solve_share_of_step": (solve_ms / max(calls, 1)) / ms_per_step,
                 "step_algorithmic_gbs": (inp + outb) / (ms_per_step * 1e-3) / 1e9}
