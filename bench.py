@@ -19,6 +19,8 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+# stdout carries exactly one JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION/INFO on some boxes) out of it
+os.environ["NCCL_DEBUG"] = os.environ.get("ANOFOX_B200_NCCL_DEBUG", "WARN")
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
