@@ -118,7 +118,7 @@ template <int NT, bool SIDE, bool CHECKX>
 __device__ __forceinline__ void acc_rows(WarpAcc<NT, SIDE> &A, const double *__restrict__ xs,
                                          const double *__restrict__ ys, const double *__restrict__ ws,
                                          const uint8_t *__restrict__ ts, int r_begin, int r_end, int p, int lane,
-                                         const double (&sh)[NT], double shy) {
+                                         const double (&sh)[NT], double shy, bool nan_unflags = false) {
 	const int rl = lane & 3, cl = lane >> 2;
 	const bool has_w = ws != nullptr;
 	for (int base = r_begin; base < r_end; base += 4) {
@@ -134,14 +134,24 @@ __device__ __forceinline__ void acc_rows(WarpAcc<NT, SIDE> &A, const double *__r
 			xv[t] = (c < p) ? xs[(int64_t)rc * p + c] : 0.0;
 		}
 		bool ok = (r < r_end) && row_ok_yw(yv, wv, tr, has_w);
+		bool counted = r < r_end && tr != 0;
 		if (CHECKX) {
-			bool bad = false;
+			bool bad = false, nanx = false;
 #pragma unroll
-			for (int t = 0; t < NT; ++t) bad = bad || !finite_f64(xv[t]);
+			for (int t = 0; t < NT; ++t) {
+				bad = bad || !finite_f64(xv[t]);
+				nanx = nanx || isnan(xv[t]);
+			}
 			const unsigned mb = __ballot_sync(0xffffffffu, bad);
 			ok = ok && ((mb & (0x11111111u << rl)) == 0u);
+			if (nan_unflags) {
+				// default training flags derived from y alone (fit_device): a row with a missing feature is not a
+				// training row (ols_predict_aggregate.cpp:216-239) -- it does not count towards the state either
+				const unsigned mn = __ballot_sync(0xffffffffu, nanx);
+				counted = counted && ((mn & (0x11111111u << rl)) == 0u);
+			}
 		}
-		A.ns += (r < r_end && tr != 0) ? 1 : 0;
+		A.ns += counted ? 1 : 0;
 		A.nv += ok ? 1 : 0;
 		const double weff = ok ? wv : 0.0;
 		const double dy = ok ? yv - shy : 0.0;
@@ -848,6 +858,7 @@ struct StreamArgs {
 	const int *run_if;
 	const double *ring_partials;
 	int ring_n_part;
+	int flags_from_y; // the train flags say "y present" only: rows with a NaN feature do not count as state rows
 };
 
 __device__ __forceinline__ bool row_valid_full(const StreamArgs &a, int64_t r) {
@@ -916,7 +927,7 @@ template <int NT, bool SIDE, int NW> __global__ void __launch_bounds__(32 * NW) 
 		for (int64_t cb = wb; cb < we; cb += (1 << 20)) {
 			const int64_t ce = cb + (1 << 20) < we ? cb + (1 << 20) : we;
 			acc_rows<NT, SIDE, true>(A, a.x + cb * p, a.y + cb, a.w ? a.w + cb : nullptr, a.train ? a.train + cb : nullptr,
-			                         0, (int)(ce - cb), p, lane, sh, shy);
+			                         0, (int)(ce - cb), p, lane, sh, shy, a.flags_from_y != 0);
 		}
 		store_record<NT, SIDE>(A, part, p, lane, sh, shy, -1);
 	}

@@ -156,10 +156,21 @@ __global__ void default_train_kernel(const double *__restrict__ y, const double 
 	flag[r] = tr ? 1 : 0;
 }
 
+// The same rule without the features: "y present". Used with the ring kernel for unweighted fits, where a
+// training row with a NaN feature poisons its group's sums and sends the group through the checked path
+// (redo_kernel, flags_from_y), which applies the feature half of the rule; the is_training OUTPUT gets the full
+// rule from the predict kernels, which read every feature anyway. Saves one full pass over X.
+__global__ void default_train_y_kernel(const double *__restrict__ y, int64_t n_rows, uint8_t *__restrict__ flag) {
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r < n_rows) flag[r] = isnan(y[r]) ? 0 : 1;
+}
+
 // One warp per group: yhat and the simplified interval of anofox_predict_with_interval
 // (lib.rs:2292-2347) for every row of the group, in input order.
+// flags_y != null: also write is_training[r] = flags_y[r] && no NaN feature in row r.
 __global__ void predict_kernel(const int64_t *__restrict__ offsets, int64_t n_groups, const double *__restrict__ x,
-                               int p, FitParams P, AnofoxB200FitOutputs fit, AnofoxB200PredictOutputs out) {
+                               int p, FitParams P, AnofoxB200FitOutputs fit, AnofoxB200PredictOutputs out,
+                               const uint8_t *__restrict__ flags_y) {
 	const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int lane = threadIdx.x & 31;
 	if (g >= n_groups) return;
@@ -185,6 +196,11 @@ __global__ void predict_kernel(const int64_t *__restrict__ offsets, int64_t n_gr
 	}
 	for (int64_t r = r0 + lane; r < r1; r += 32) {
 		double yh = nanv, lo = nanv, hi = nanv;
+		if (flags_y) {
+			bool tr = flags_y[r] != 0;
+			for (int j = 0; tr && j < p; ++j) tr = !isnan(x[r * p + j]);
+			out.is_training[r] = tr ? 1 : 0;
+		}
 		if (ok) {
 			double s = b0;
 			for (int j = 0; j < p; ++j) {
@@ -209,7 +225,8 @@ __global__ void predict_kernel(const int64_t *__restrict__ offsets, int64_t n_gr
 template <int P>
 __global__ void __launch_bounds__(256) predict_flat_kernel(const int64_t *__restrict__ offsets, int64_t n_groups,
                                                            const double *__restrict__ x, FitParams Pm,
-                                                           AnofoxB200FitOutputs fit, AnofoxB200PredictOutputs out) {
+                                                           AnofoxB200FitOutputs fit, AnofoxB200PredictOutputs out,
+                                                           const uint8_t *__restrict__ flags_y) {
 	constexpr int LPR = P / 2, RPW = 32 / LPR; // lanes per row, rows per warp-wide load
 	const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int lane = threadIdx.x & 31;
@@ -254,6 +271,11 @@ __global__ void __launch_bounds__(256) predict_flat_kernel(const int64_t *__rest
 			double s = (n0 ? 0.0 : c0 * v[u].x) + (n1 ? 0.0 : c1 * v[u].y);
 #pragma unroll
 			for (int m = 1; m < LPR; m <<= 1) s += __shfl_xor_sync(0xffffffffu, s, m);
+			if (flags_y) { // is_training = y present and no NaN feature (the lanes of a row vote)
+				const unsigned nb = __ballot_sync(0xffffffffu, isnan(v[u].x) || isnan(v[u].y));
+				const unsigned rowmask = (LPR == 32 ? 0xffffffffu : ((1u << LPR) - 1u)) << (rw * LPR);
+				if (sub == 0 && r < r1) out.is_training[r] = (flags_y[r] != 0 && (nb & rowmask) == 0u) ? 1 : 0;
+			}
 			if (sub == 0 && r < r1) {
 				double yh = nanv, lo = nanv, hi = nanv;
 				s += b0;
@@ -989,14 +1011,22 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	}
 
 	const uint8_t *train_use = nullptr;
+	bool y_only_flags = false;
 	if (pred) {
 		if (train) {
 			train_use = train;
 			if (pred->is_training) CU(cudaMemcpyAsync(pred->is_training, train, (size_t)N, cudaMemcpyDeviceToDevice, st), "copy train");
 		} else {
-			uint8_t *flags = pred->is_training ? pred->is_training : ws.train_tmp;
+			// unweighted fit through the ring kernel: flags from y alone (default_train_y_kernel), the feature half
+			// of the rule is applied by the checked path and by the predict kernels
+			const SmallGeom sm0 = small_geometry(p, wuse != nullptr, true, N, G);
+			y_only_flags = !wuse && !sm0.use && g_force_path.load() != 3 && pred->is_training != nullptr;
+			uint8_t *flags = (pred->is_training && !y_only_flags) ? pred->is_training : ws.train_tmp;
 			if (N > 0) {
-				default_train_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(y, x, N, p, flags);
+				if (y_only_flags)
+					default_train_y_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(y, N, flags);
+				else
+					default_train_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(y, x, N, p, flags);
 				LAUNCHED();
 				CU(cudaGetLastError(), "default_train_kernel");
 			}
@@ -1046,6 +1076,7 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		r.tile_g0 = ws.tile_g0;
 		r.records = ws.records;
 		r.shift_common = nullptr;
+		r.flags_from_y = y_only_flags ? 1 : 0;
 		r.big_list = ws.big_list;
 		r.big_count = ws.big_count;
 		r.big_rows = rg.big_rows;
@@ -1135,6 +1166,7 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 			s.run_if = nullptr;
 			s.ring_partials = nullptr;
 			s.ring_n_part = 0;
+			s.flags_from_y = y_only_flags ? 1 : 0;
 			first_valid_kernel<<<nb, 32, 0, st>>>(s);
 			LAUNCHED();
 			CU(cudaGetLastError(), "first_valid_kernel");
@@ -1174,16 +1206,17 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		const int threads = 256;
 		const unsigned blocks = (unsigned)((G * 32 + threads - 1) / threads);
 		const bool flat = (((uintptr_t)x) & 15) == 0;
+		const uint8_t *fy = y_only_flags ? train_use : nullptr;
 		if (flat && p == 2)
-			predict_flat_kernel<2><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred);
+			predict_flat_kernel<2><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred, fy);
 		else if (flat && p == 4)
-			predict_flat_kernel<4><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred);
+			predict_flat_kernel<4><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred, fy);
 		else if (flat && p == 8)
-			predict_flat_kernel<8><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred);
+			predict_flat_kernel<8><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred, fy);
 		else if (flat && p == 16)
-			predict_flat_kernel<16><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred);
+			predict_flat_kernel<16><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred, fy);
 		else
-			predict_kernel<<<blocks, threads, 0, st>>>(offsets, G, x, p, P, fo, *pred);
+			predict_kernel<<<blocks, threads, 0, st>>>(offsets, G, x, p, P, fo, *pred, fy);
 		LAUNCHED();
 		CU(cudaGetLastError(), "predict_kernel");
 	}
@@ -1860,6 +1893,7 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	r.tile_g0 = ws.slice_off + units + 1;
 	r.records = ws.ring_partials;
 	r.shift_common = shift;
+	r.flags_from_y = 0;
 	r.big_list = ws.big_list;
 	r.big_count = ws.big_count;
 	r.big_rows = (int64_t)1 << 40;
@@ -1891,6 +1925,7 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	s.rec_gs = rec_len(p);
 	s.rec_es = 1;
 	s.run_if = ws.redo_count;
+	s.flags_from_y = 0;
 	s.ring_partials = ws.ring_partials;
 	s.ring_n_part = units * ncw;
 	timer_mark(st);

@@ -51,6 +51,7 @@ struct RingArgs {
 	int win_rows, n_win;    // SR (multiple of 16), NS
 	int team;               // TW: warps per unit, a power of two dividing the consumer warp count
 	uint32_t x_off, y_off, w_off, t_off, slot_off; // byte offsets of the regions in dynamic shared memory
+	int flags_from_y; // train = "y present" only: redo_kernel drops rows with a NaN feature from the state count
 };
 
 // Number of deposited values per lane when a team combines through shared memory.
@@ -633,7 +634,8 @@ template <int NT, bool SIDE> __global__ void __launch_bounds__(256) redo_kernel(
 		// without a valid row every row is masked below (the shift is irrelevant); the pass still counts n_state
 		for (int64_t cb = 0; cb < n; cb += (1 << 20)) {
 			const int cn = (int)(n - cb < (1 << 20) ? n - cb : (1 << 20));
-			acc_rows<NT, SIDE, true>(A, xs + cb * p, ys + cb, ws ? ws + cb : nullptr, ts ? ts + cb : nullptr, 0, cn, p, lane, sh, shy);
+			acc_rows<NT, SIDE, true>(A, xs + cb * p, ys + cb, ws ? ws + cb : nullptr, ts ? ts + cb : nullptr, 0, cn, p, lane, sh, shy,
+			                         a.flags_from_y != 0);
 		}
 		if (f < 0) {
 			int ns = A.ns + __shfl_xor_sync(0xffffffffu, A.ns, 1);

@@ -492,8 +492,9 @@ def test_exact_fit_groups_use_the_residual_pass(lib, oracle, path):
 def test_fit_predict_parity(lib, oracle, path):
     """Engine of ols/ridge/wls_fit_predict_by: every row predicted, held-out rows (y NULL) not trained on."""
     rng = np.random.default_rng(9)
-    for method, p in [("ols", 3), ("ols", 8), ("ridge", 5), ("wls", 4)]:
-        c = make_case(rng, 120, 8, 90, p, dirty=True, weights=(method == "wls"), collinear=True)
+    # p > 8 always takes the ring kernel: default training flags from y alone + the checked path for NaN features
+    for method, p in [("ols", 3), ("ols", 8), ("ridge", 5), ("wls", 4), ("ols", 16), ("ridge", 12), ("wls", 9)]:
+        c = make_case(rng, 120, 8, 90 if p <= 8 else 300, p, dirty=True, weights=(method == "wls"), collinear=True)
         N = len(c["y"])
         hold = rng.uniform(size=N) < 0.2
         c["y"][hold] = np.nan
