@@ -161,8 +161,17 @@ __global__ void default_train_kernel(const double *__restrict__ y, const double 
 // (redo_kernel, flags_from_y), which applies the feature half of the rule; the is_training OUTPUT gets the full
 // rule from the predict kernels, which read every feature anyway. Saves one full pass over X.
 __global__ void default_train_y_kernel(const double *__restrict__ y, int64_t n_rows, uint8_t *__restrict__ flag) {
-	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (r < n_rows) flag[r] = isnan(y[r]) ? 0 : 1;
+	// eight rows per thread: the flags leave as one 8-byte store when the slice is complete and aligned
+	const int64_t r0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+	if (r0 >= n_rows) return;
+	if (r0 + 8 <= n_rows && (((uintptr_t)(flag + r0)) & 7) == 0) {
+		unsigned long long bits = 0ull;
+#pragma unroll
+		for (int i = 0; i < 8; ++i) bits |= (unsigned long long)(isnan(y[r0 + i]) ? 0 : 1) << (8 * i);
+		*reinterpret_cast<unsigned long long *>(flag + r0) = bits;
+	} else {
+		for (int64_t r = r0; r < n_rows && r < r0 + 8; ++r) flag[r] = isnan(y[r]) ? 0 : 1;
+	}
 }
 
 // One warp per group: yhat and the simplified interval of anofox_predict_with_interval
@@ -260,10 +269,19 @@ __global__ void __launch_bounds__(256) predict_flat_kernel(const int64_t *__rest
 	constexpr int U = 4; // independent loads in flight per lane
 	for (int64_t rb = r0; rb < r1; rb += (int64_t)RPW * U) {
 		double2 v[U];
+		unsigned nanb[U];
+		constexpr int NF = (RPW * U + 31) / 32; // flag bytes per lane and pass, loaded with the rows (not after them)
+		unsigned fl[NF];
+#pragma unroll
+		for (int i = 0; i < NF; ++i) {
+			const int64_t r = rb + lane + 32 * i;
+			fl[i] = (flags_y && lane + 32 * i < RPW * U && r < r1) ? (unsigned)__ldg(flags_y + r) : 0u;
+		}
 #pragma unroll
 		for (int u = 0; u < U; ++u) {
 			const int64_t r = rb + u * RPW + rw;
 			v[u] = r < r1 ? __ldg(xv + (r * P) / 2 + sub) : make_double2(0.0, 0.0);
+			nanb[u] = 0u;
 		}
 #pragma unroll
 		for (int u = 0; u < U; ++u) {
@@ -271,11 +289,7 @@ __global__ void __launch_bounds__(256) predict_flat_kernel(const int64_t *__rest
 			double s = (n0 ? 0.0 : c0 * v[u].x) + (n1 ? 0.0 : c1 * v[u].y);
 #pragma unroll
 			for (int m = 1; m < LPR; m <<= 1) s += __shfl_xor_sync(0xffffffffu, s, m);
-			if (flags_y) { // is_training = y present and no NaN feature (the lanes of a row vote)
-				const unsigned nb = __ballot_sync(0xffffffffu, isnan(v[u].x) || isnan(v[u].y));
-				const unsigned rowmask = (LPR == 32 ? 0xffffffffu : ((1u << LPR) - 1u)) << (rw * LPR);
-				if (sub == 0 && r < r1) out.is_training[r] = (flags_y[r] != 0 && (nb & rowmask) == 0u) ? 1 : 0;
-			}
+			if (flags_y) nanb[u] = __ballot_sync(0xffffffffu, isnan(v[u].x) || isnan(v[u].y)); // the lanes of a row vote
 			if (sub == 0 && r < r1) {
 				double yh = nanv, lo = nanv, hi = nanv;
 				s += b0;
@@ -287,6 +301,22 @@ __global__ void __launch_bounds__(256) predict_flat_kernel(const int64_t *__rest
 				out.yhat[r] = yh;
 				out.yhat_lower[r] = lo;
 				out.yhat_upper[r] = hi;
+			}
+		}
+		if (flags_y) {
+			// is_training = y present and no NaN feature, for the RPW * U consecutive rows of this pass: one
+			// coalesced byte per lane instead of scattered single-byte stores from the rows' first lanes
+#pragma unroll
+			for (int i = 0; i < NF; ++i) {
+				const int j = lane + 32 * i;
+				const int64_t r = rb + j;
+				if (j < RPW * U && r < r1) {
+					const unsigned rowmask = (LPR == 32 ? 0xffffffffu : ((1u << LPR) - 1u)) << ((j % RPW) * LPR);
+					unsigned nb = nanb[0];
+#pragma unroll
+					for (int u = 1; u < U; ++u) nb = (j / RPW == u) ? nanb[u] : nb;
+					out.is_training[r] = (fl[i] != 0u && (nb & rowmask) == 0u) ? 1 : 0;
+				}
 			}
 		}
 	}
@@ -1024,7 +1054,7 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 			uint8_t *flags = (pred->is_training && !y_only_flags) ? pred->is_training : ws.train_tmp;
 			if (N > 0) {
 				if (y_only_flags)
-					default_train_y_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(y, N, flags);
+					default_train_y_kernel<<<(unsigned)((N + 2047) / 2048), 256, 0, st>>>(y, N, flags);
 				else
 					default_train_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(y, x, N, p, flags);
 				LAUNCHED();
