@@ -619,6 +619,10 @@ SHARD_CASES = [
     (33, 120_000, "ols", True),
     (8, 77, "ols", False),
     (48, 150_000, "ridge", False),
+    # more slice-kernel shapes: non-SIDE (y and the 1-column ride in the last tile), p % 16 == 8, ragged tails
+    (34, 90_003, "ols", True),
+    (40, 100_001, "ols", False),
+    (64, 70_007, "ols", True),
 ]
 
 
