@@ -938,7 +938,9 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 	w.records = (double *)take((size_t)std::max<int64_t>(G, 1) * L * 8);
 	w.tile_g0 = (int64_t *)take((size_t)(std::max<int64_t>(n_tiles, sms) + 2) * 8);
 	w.big_list = (int64_t *)take((size_t)(w.nbig_max + 1) * 8);
-	w.big_count = (int *)take(256);
+	w.big_count = (int *)take(768); // the three counters of a call sit together: one memset clears them
+	w.refine_count = w.big_count ? w.big_count + 64 : nullptr;
+	w.redo_count = w.big_count ? w.big_count + 128 : nullptr;
 	w.shift = (double *)take((size_t)(w.nbig_max + 1) * (p + 1) * 8);
 	w.first_ok = (int *)take((size_t)(w.nbig_max + 1) * 4);
 	// partial records of the streaming path: one per (big group, warp). Bounded by capping how many
@@ -948,9 +950,7 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 	w.ring_partials = (double *)take(G == 1 ? (size_t)sms * 16 * L * 8 : 0);
 	w.slice_off = (int64_t *)take((size_t)(2 * sms + 4) * 8);
 	w.refine_list = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
-	w.refine_count = (int *)take(256);
 	w.redo_list = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
-	w.redo_count = (int *)take(256);
 	w.train_tmp = (uint8_t *)take((size_t)std::max<int64_t>(N, 1));
 	w.f_coef = (double *)take((size_t)std::max<int64_t>(G, 1) * p * 8);
 	w.f_icpt = (double *)take((size_t)std::max<int64_t>(G, 1) * 8);
@@ -1082,9 +1082,7 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	// pre-ring DMMA kernel, kept for A/B runs)
 	const bool use_ring = !small.use && g_force_path.load() != 3;
 	const StageGeom sg = small.use ? small.sg : stage_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
-	CU(cudaMemsetAsync(ws.big_count, 0, 256, st), "memset");
-	CU(cudaMemsetAsync(ws.refine_count, 0, 256, st), "memset");
-	CU(cudaMemsetAsync(ws.redo_count, 0, 256, st), "memset");
+	CU(cudaMemsetAsync(ws.big_count, 0, 768, st), "memset"); // big_count | refine_count | redo_count
 	const bool fused = small.use && g_force_path.load() == 2;
 	const bool transposed = small.use && !fused; // record element (g, i) at records[g + i * G]
 	const int64_t rec_gs = transposed ? 1 : rec_len(p), rec_es = transposed ? G : 1;

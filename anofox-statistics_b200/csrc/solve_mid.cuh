@@ -29,21 +29,13 @@ __global__ void __launch_bounds__(64) solve_mid_kernel(const double *__restrict_
 	const int ng = (int)(n_groups - g0 < T ? n_groups - g0 : T);
 	// ---- stage the CTA's records: element e of the block is field e % L of group e / L -------------------
 	{
-		const double *src = records + g0 * L;
-		const int total = ng * L;
-		int f = threadIdx.x, grp = 0;
-		while (f >= L) {
-			f -= L;
-			++grp;
-		}
-		for (int e = threadIdx.x; e < total; e += T) {
-			// asynchronous 8-byte copies: hundreds in flight per thread instead of one dependent load at a time
-			asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(&ws_all[f * TS + grp])), "l"(src + e) : "memory");
-			f += T;
-			while (f >= L) {
-				f -= L;
-				++grp;
-			}
+		// a warp stages one group at a time, lane l the fields l, l + 32, ...: coalesced reads of the record,
+		// conflict-free transposed writes (field stride TS is odd); hundreds of 8-byte copies in flight per thread
+		const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = (T + 31) >> 5;
+		for (int grp = warp; grp < ng; grp += nwarps) {
+			const double *src = records + (g0 + grp) * L;
+			for (int f = lane; f < L; f += 32)
+				asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(&ws_all[f * TS + grp])), "l"(src + f) : "memory");
 		}
 	}
 	asm volatile("cp.async.wait_all;" ::: "memory");
@@ -333,21 +325,15 @@ __global__ void __launch_bounds__(kFixT) solve_fixed_kernel(const double *__rest
 	for (int e = threadIdx.x; e < FL::LEN * TS; e += kFixT) ws_all[e] = 0.0;
 	__syncthreads();
 	{
-		const double *src = records + g0 * L;
-		const int total = ng * L;
-		int f = threadIdx.x, grp = 0;
-		while (f >= L) {
-			f -= L;
-			++grp;
-		}
-		for (int e = threadIdx.x; e < total; e += kFixT) {
-			const int m = fmap[f];
-			if (m >= 0)
-				asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(&ws_all[m * TS + grp])), "l"(src + e) : "memory");
-			f += kFixT;
-			while (f >= L) {
-				f -= L;
-				++grp;
+		// a warp stages one group at a time, lane l the fields l, l + 32, ...: coalesced 256-byte reads of the
+		// record, conflict-free transposed writes (field stride TS = 65 doubles), three address updates per element
+		const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+		for (int grp = warp; grp < ng; grp += kFixT / 32) {
+			const double *src = records + (g0 + grp) * L;
+			for (int f = lane; f < L; f += 32) {
+				const int m = fmap[f];
+				if (m >= 0)
+					asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(&ws_all[m * TS + grp])), "l"(src + f) : "memory");
 			}
 		}
 	}
