@@ -110,7 +110,8 @@ def cpu_reference_run(wl, host, steps, warmup, threads, budget_s=12.0):
     import oracle  # test infrastructure, allowed here as the timed CPU baseline only
     G, n, p, method, inference, extra = wl
     opt = dict(method=method, compute_inference=inference, alpha=extra.get("alpha", 0.0))
-    threads = threads or oracle.max_threads()
+    # every host core this process may use -- not omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1
+    threads = threads or len(os.sched_getaffinity(0)) or oracle.max_threads()
     # pilot to size the sample
     gs = min(G, 2000)
     t0 = time.perf_counter()
