@@ -435,7 +435,7 @@ def main():
                 "step_algorithmic_gbs": (inp + outb) / (ms_per_step * 1e-3) / 1e9}
 
     cpu = None
-    if not args.no_cpu:
+    if not args.no_cpu and world == 1:  # the CPU baseline leg runs at N = 1 only (task contract)
         gs = min(G, 200_000)
         host = {"offsets": d["offsets"][:gs + 1].cpu().numpy(), "y": d["y"][:gs * n].cpu().numpy(),
                 "x": d["x"][:gs * n].cpu().numpy(), "w": d["w"][:gs * n].cpu().numpy() if d["w"] is not None else None}
