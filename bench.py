@@ -19,8 +19,16 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-# stdout carries exactly one JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION/INFO on some boxes) out of it
-os.environ["NCCL_DEBUG"] = os.environ.get("ANOFOX_B200_NCCL_DEBUG", "WARN")
+# stdout carries exactly one JSON line. Libraries print there too (NCCL's version banner on boxes that export
+# NCCL_DEBUG), so file descriptor 1 is pointed at stderr for the life of the process and the JSON line goes to the
+# saved descriptor of the real stdout.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(obj):
+    os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
+
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
@@ -250,7 +258,7 @@ def run_c4(args, rank, world, local):
                 "fits_per_sec": 1.0 / (ms_per_step * 1e-3), "identical_on_all_ranks": same,
                 "status": int(out["status"][0].item()), "n_observations": int(out["n_observations"][0].item()),
                 "clocks": clocks, "e2e": None, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": None}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -312,7 +320,7 @@ def main():
                                  "sample": f"{used} groups x {n} rows per step (oracle f64, OpenMP over groups; "
                                            "the reference's Rust crates cannot be built here)"},
                 "e2e": {"value": v, "unit": "fits/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return
 
     # ------------------------------------------------------------------ our arm (GPU)
@@ -448,7 +456,7 @@ def main():
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
             "rows_per_sec": value * n, "groups_fitted_ok": n_ok, "clocks": clocks, "e2e": e2e,
             "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
