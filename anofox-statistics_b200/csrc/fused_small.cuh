@@ -669,8 +669,11 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 
 // One thread per group: moments from the transposed record (coalesced: consecutive lanes read consecutive
 // groups of the same field), then the same solve as the fused kernel with every array in registers.
+#ifndef ANOFOX_SOLVE_SMALL_MINB
+#define ANOFOX_SOLVE_SMALL_MINB 4
+#endif
 template <int P>
-__global__ void __launch_bounds__(128) solve_small_kernel(const double *__restrict__ records, int64_t n_groups, FitParams Pm,
+__global__ void __launch_bounds__(128, ANOFOX_SOLVE_SMALL_MINB) solve_small_kernel(const double *__restrict__ records, int64_t n_groups, FitParams Pm,
                                                           AnofoxB200FitOutputs o, int *refine_count,
                                                           int64_t *refine_list) {
 	constexpr int K = P + 1;

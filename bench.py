@@ -211,6 +211,13 @@ def run_c4(args, rank, world, local):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_per_step = float(t.item()) / args.steps
+    # the accumulate kernel's launch time on every rank: a slow step with equal kernel times is the exchange, a slow
+    # rank shows here
+    acc_all = torch.tensor([acc_ms / max(calls, 1)], dtype=torch.float64, device="cuda")
+    acc_ranks = [acc_all.clone() for _ in range(world)]
+    if world > 1:
+        dist.all_gather(acc_ranks, acc_all)
+    acc_ranks = [float(a.item()) for a in acc_ranks]
     total_rows = world * rows
     value = total_rows / (ms_per_step * 1e-3)
     # every rank must hold the same result (replicated solve on identical reduced blocks)
@@ -238,9 +245,12 @@ def run_c4(args, rank, world, local):
                                                  "split-role warps, TMA-fed ring)",
                     "achieved": tf, "peak": dmma_peak,
                     "peak_source": "measured FP64 DMMA m8n8k4 rate, tools/microbench.cu (nominal 40)",
-                    "unit": "TFLOP/s", "frac": (tf / dmma_peak) if tf else None, "traffic": None,
+                    "unit": "TFLOP/s", "frac": (tf / dmma_peak) if tf else None,
+                    # ncu capture of this kernel at 1/10 of the rows (profiles/r01d_c4_acc_slice_summary.txt): 6.5014 GB
+                    # read + 4.2 MB written for 6.5000 GB algorithmic; scaled by the row count here
+                    "traffic": acc_bytes * (6.501365e9 + 4.2e6) / 6.5e9,
                     "algorithmic_flops_per_launch": flops, "algorithmic_bytes_per_launch": acc_bytes,
-                    "avg_launch_ms": acc_launch_ms,
+                    "avg_launch_ms": acc_launch_ms, "avg_launch_ms_per_rank": acc_ranks,
                     "hbm_achieved_gbs": achieved, "hbm_peak_gbs": peak, "hbm_peak_source": peak_src,
                     "hbm_frac": (achieved / peak) if achieved else None,
                     "note": "algorithmic flops = rows * k(k+1), k = p + 2 (symmetric Gram with the y and 1 columns); "
@@ -434,7 +444,7 @@ def main():
     else:
         kname = "acc_ring_kernel (streaming ring of TMA windows, FP64 DMMA moment accumulation)"
     # measured traffic of the same kernel from the committed ncu --set full capture (profiles/), per launch
-    traffic = {"C2": 2.74e9, "C3r": 27.9e9}.get(args.workload)
+    traffic = {"C2": 2.74e9, "C3r": 28.9e9, "C5": 7.37e9}.get(args.workload)  # dram read + write, r01d_*_summary.txt
     roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": traffic,
