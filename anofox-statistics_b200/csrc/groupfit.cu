@@ -231,8 +231,14 @@ __global__ void predict_kernel(const int64_t *__restrict__ offsets, int64_t n_gr
 // Same predictions for p = 2, 4, 8, 16 with fully coalesced reads: P/2 lanes share a row (one 16-byte load
 // each, a warp-wide load instruction covers 512 contiguous bytes), the row's dot product meets in a shuffle
 // tree and the row's first lane writes the three outputs. x must be 16-byte aligned.
+#ifndef ANOFOX_PREDICT_MINB
+#define ANOFOX_PREDICT_MINB 3
+#endif
+#ifndef ANOFOX_PREDICT_U
+#define ANOFOX_PREDICT_U 8
+#endif
 template <int P>
-__global__ void __launch_bounds__(256) predict_flat_kernel(const int64_t *__restrict__ offsets, int64_t n_groups,
+__global__ void __launch_bounds__(256, ANOFOX_PREDICT_MINB) predict_flat_kernel(const int64_t *__restrict__ offsets, int64_t n_groups,
                                                            const double *__restrict__ x, FitParams Pm,
                                                            AnofoxB200FitOutputs fit, AnofoxB200PredictOutputs out,
                                                            const uint8_t *__restrict__ flags_y) {
@@ -266,7 +272,7 @@ __global__ void __launch_bounds__(256) predict_flat_kernel(const int64_t *__rest
 		n1 = isnan(c1);
 	}
 	const double2 *xv = reinterpret_cast<const double2 *>(x);
-	constexpr int U = 4; // independent loads in flight per lane
+	constexpr int U = ANOFOX_PREDICT_U; // independent loads in flight per lane
 	for (int64_t rb = r0; rb < r1; rb += (int64_t)RPW * U) {
 		double2 v[U];
 		unsigned nanb[U];
