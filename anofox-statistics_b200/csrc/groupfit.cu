@@ -791,8 +791,11 @@ static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	while (T < 32 && mean_bytes > 700.0 * T) T *= 2;
 	r.T = T;
 	const int gpw = 32 / T;
-	r.max_groups = std::min(kSmallStageGroups, 2 * gpw); // two rounds per stage
-	const int64_t budget = 196 * 1024;
+	// tuning hooks (tools/sweep_small.sh): rounds of 32 lanes per stage and the shared-memory budget of the ring
+	static const int env_rounds = getenv("ANOFOX_B200_SMALL_ROUNDS") ? atoi(getenv("ANOFOX_B200_SMALL_ROUNDS")) : 0;
+	static const int env_small_kb = getenv("ANOFOX_B200_SMALL_KB") ? atoi(getenv("ANOFOX_B200_SMALL_KB")) : 0;
+	r.max_groups = std::min(kSmallStageGroups, (env_rounds > 0 ? env_rounds : 2) * gpw); // two rounds per stage
+	const int64_t budget = (env_small_kb > 0 ? env_small_kb : 196) * 1024;
 	int64_t cap = (int64_t)std::ceil(std::max((double)r.max_groups, 4.0) * std::max(mean_rows, 1.0)) + 8;
 	if (cap * row_bytes > 96 * 1024) cap = 96 * 1024 / row_bytes;
 	if (cap * row_bytes < 8 * 1024) cap = 8 * 1024 / row_bytes;
