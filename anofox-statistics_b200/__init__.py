@@ -22,6 +22,7 @@ HEADER_SYMBOLS = [
     "anofox_compute_bic", "anofox_b200_workspace_bytes", "anofox_b200_fit_batch_device",
     "anofox_b200_fit_batch_host", "anofox_b200_fit_predict_batch_device", "anofox_b200_fit_predict_batch_host",
     "anofox_b200_moment_block_len", "anofox_b200_first_valid_row_device", "anofox_b200_moments_device", "anofox_b200_solve_moments_device",
+    "anofox_b200_solve_moments_refine_device", "anofox_b200_shard_residual_device",
     "anofox_b200_device_check", "anofox_b200_launch_count", "anofox_b200_version",
 ]
 
@@ -80,6 +81,15 @@ def load_library():
     lib.anofox_b200_solve_moments_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                                      C.POINTER(abi.B200FitOptions), C.POINTER(abi.B200FitOutputs),
                                                      C.c_void_p, E]
+    lib.anofox_b200_solve_moments_refine_device.restype = C.c_int32
+    lib.anofox_b200_solve_moments_refine_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                                            C.POINTER(abi.B200FitOptions),
+                                                            C.POINTER(abi.B200FitOutputs), C.c_void_p, C.c_void_p,
+                                                            C.c_void_p, E]
+    lib.anofox_b200_shard_residual_device.restype = C.c_int32
+    lib.anofox_b200_shard_residual_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
+                                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                      C.c_size_t, C.c_void_p, E]
     lib.anofox_b200_device_check.restype = C.c_int32
     lib.anofox_b200_device_check.argtypes = [E]
     lib.anofox_b200_launch_count.restype = C.c_int64
@@ -93,6 +103,8 @@ def load_library():
     lib.anofox_b200_stage_timing_read.argtypes = [abi.c_double_p, abi.c_double_p]
     lib.anofox_b200_force_path.restype = None
     lib.anofox_b200_force_path.argtypes = [C.c_int32]
+    lib.anofox_b200_debug_counters.restype = C.c_int32
+    lib.anofox_b200_debug_counters.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, abi.c_int32_p]
     lib.anofox_b200_plan.restype = C.c_int32
     lib.anofox_b200_plan.argtypes = [C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, abi.c_int32_p]
     _LIB = lib
@@ -250,6 +262,15 @@ class DeviceFit:
         _check(rc, err)
         return self.out
 
+    def counters(self):
+        """Device-side counters of the last call: big groups, exact-residual refinements, checked redos, huge
+        groups, QR-fallback groups (synchronises)."""
+        out = (C.c_int32 * 5)()
+        rc = load_library().anofox_b200_debug_counters(C.c_void_p(self.ws_ptr), self.G, self.N, self.p, out)
+        if rc != 0:
+            raise B200Error(rc, "debug_counters")
+        return dict(zip(("big", "refined", "redone", "huge", "qr"), [int(v) for v in out]))
+
     def fit_predict(self, offsets, y, x, w=None, train=None, stream=None, **opt):
         torch = self.torch
         o = abi.make_fit_options(**opt)
@@ -286,10 +307,23 @@ def fit_batch_host_into(offsets, y, x, w, out_struct, G, N, p, **opt):
     _check(rc, err)
 
 
+def fit_predict_batch_host_into(offsets, y, x, w, train, pred_struct, fit_struct, G, N, p, **opt):
+    """Host-pointer fit + predict call with caller-owned (e.g. pinned) buffers given as raw addresses."""
+    o = abi.make_fit_options(**opt)
+    err = abi.AnofoxError()
+    lib = load_library()
+    cast = lambda a, t: None if a is None else C.cast(a, t)  # noqa: E731
+    rc = lib.anofox_b200_fit_predict_batch_host(cast(offsets, abi.c_int64_p), G, cast(y, abi.c_double_p),
+                                                cast(x, abi.c_double_p), cast(w, abi.c_double_p),
+                                                cast(train, abi.c_uint8_p), N, p, C.byref(o), C.byref(pred_struct),
+                                                C.byref(fit_struct), C.byref(err))
+    _check(rc, err)
+
+
 def force_path(path):
     """Test / A-B hook: "auto", "record" (always the DMMA accumulation kernel + solve kernel) or "fused"
     (small groups through the single rows-to-results kernel instead of accumulate + register solve)."""
-    load_library().anofox_b200_force_path({"auto": 0, "record": 1, "fused": 2, "stages": 3}[path])
+    load_library().anofox_b200_force_path({"auto": 0, "record": 1, "fused": 2, "stages": 3, "ringslice": 4, "qr": 5}[path])
 
 
 def plan(G, N, p, has_w=False, has_train=False):

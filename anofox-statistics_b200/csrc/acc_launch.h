@@ -13,6 +13,7 @@ constexpr int kStreamWarps = 8;
 	cudaError_t launch_resident_nt##NT_(bool side, bool has_w, bool has_t, const AccArgs &a, int grid,               \
 	                                    cudaStream_t st);                                                            \
 	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st);                    \
+	cudaError_t launch_big_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st);                       \
 	cudaError_t launch_ring_nt##NT_(bool side, bool has_w, bool has_t, const RingArgs &a, int grid, size_t dyn,      \
 	                                cudaStream_t st);                                                                \
 	cudaError_t launch_redo_nt##NT_(bool side, const RingArgs &a, int grid, cudaStream_t st);                       \
@@ -109,6 +110,13 @@ cudaError_t launch_slice_t(const SliceArgs &a, int grid, size_t dyn, cudaStream_
 		                       : launch_slice_t<NT_, true, false>(a, grid, dyn, st);                                 \
 		return has_w ? launch_slice_t<NT_, false, true>(a, grid, dyn, st)                                            \
 		             : launch_slice_t<NT_, false, false>(a, grid, dyn, st);                                          \
+	}                                                                                                                \
+	cudaError_t launch_big_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st) {                      \
+		if (side)                                                                                                    \
+			acc_big_kernel<NT_, true, kStreamWarps><<<grid, 32 * kStreamWarps, 0, st>>>(a);                          \
+		else                                                                                                         \
+			acc_big_kernel<NT_, false, kStreamWarps><<<grid, 32 * kStreamWarps, 0, st>>>(a);                         \
+		return cudaGetLastError();                                                                                   \
 	}                                                                                                                \
 	cudaError_t launch_stream_nt##NT_(bool side, const StreamArgs &a, int grid, cudaStream_t st) {                   \
 		if (side)                                                                                                    \

@@ -859,6 +859,14 @@ struct StreamArgs {
 	const double *ring_partials;
 	int ring_n_part;
 	int flags_from_y; // the train flags say "y present" only: rows with a NaN feature do not count as state rows
+	// Group mode, decided on the device (no host round trip): big groups of at most huge_rows rows are taken one
+	// per CTA by acc_big_kernel; larger ones are appended to huge_list (as indices into big_list) by
+	// first_valid_kernel and go through acc_stream_kernel + reduce_partials_kernel in rounds of b_cap entries,
+	// round r covering huge_list[b_begin, b_begin + b_cap).
+	int64_t *huge_list;
+	int *huge_count;
+	int64_t huge_rows;
+	int b_begin, b_cap;
 };
 
 __device__ __forceinline__ bool row_valid_full(const StreamArgs &a, int64_t r) {
@@ -868,43 +876,48 @@ __device__ __forceinline__ bool row_valid_full(const StreamArgs &a, int64_t r) {
 }
 
 static __global__ void first_valid_kernel(const StreamArgs a) {
-	const int b = blockIdx.x;
-	if (b >= *a.big_count) return;
+	const int nbig = *a.big_count;
 	const int lane = threadIdx.x;
-	const int64_t g = a.big_list[b];
-	const int64_t r0 = a.offsets[g], r1 = a.offsets[g + 1];
-	int64_t f = -1;
-	for (int64_t base = r0; base < r1 && f < 0; base += 32) {
-		const int64_t r = base + lane;
-		const bool ok = r < r1 && row_valid_full(a, r);
-		const unsigned m = __ballot_sync(0xffffffffu, ok);
-		if (m) f = base + __ffs(m) - 1;
+	for (int b = blockIdx.x; b < nbig; b += gridDim.x) {
+		const int64_t g = a.big_list[b];
+		const int64_t r0 = a.offsets[g], r1 = a.offsets[g + 1];
+		int64_t f = -1;
+		for (int64_t base = r0; base < r1 && f < 0; base += 32) {
+			const int64_t r = base + lane;
+			const bool ok = r < r1 && row_valid_full(a, r);
+			const unsigned m = __ballot_sync(0xffffffffu, ok);
+			if (m) f = base + __ffs(m) - 1;
+		}
+		const int k = a.p + 1;
+		for (int c = lane; c < a.p; c += 32) a.shift[(int64_t)b * k + c] = f >= 0 ? a.x[f * a.p + c] : 0.0;
+		if (lane == 0) {
+			a.shift[(int64_t)b * k + a.p] = f >= 0 ? a.y[f] : 0.0;
+			a.first_ok[b] = f >= 0 ? 1 : 0;
+			if (r1 - r0 > a.huge_rows) a.huge_list[atomicAdd(a.huge_count, 1)] = b;
+		}
 	}
-	const int k = a.p + 1;
-	if (f >= 0) {
-		for (int c = lane; c < a.p; c += 32) a.shift[(int64_t)b * k + c] = a.x[f * a.p + c];
-		if (lane == 0) a.shift[(int64_t)b * k + a.p] = a.y[f];
-	}
-	if (lane == 0) a.first_ok[b] = f >= 0 ? 1 : 0;
 }
 
 template <int NT, bool SIDE, int NW> __global__ void __launch_bounds__(32 * NW) acc_stream_kernel(const StreamArgs a) {
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cl = lane >> 2;
 	const int p = a.p, k = p + 1, L = rec_len(p);
-	const int nbig = a.offsets ? *a.big_count : 1;
+	int nbig = 1;
+	if (a.offsets) {
+		nbig = *a.huge_count - a.b_begin;
+		nbig = nbig < a.b_cap ? nbig : a.b_cap;
+	}
 	if (a.run_if && *a.run_if == 0) return;
 	for (int b = 0; b < nbig; ++b) {
 		int64_t r0 = 0, r1 = a.fixed_rows;
+		int bb = 0; // index of the group in big_list / shift / first_ok
 		if (a.offsets) {
-			const int64_t g = a.big_list[b];
+			bb = (int)a.huge_list[a.b_begin + b];
+			const int64_t g = a.big_list[bb];
 			r0 = a.offsets[g];
 			r1 = a.offsets[g + 1];
 		}
 		double *part = a.partials + ((int64_t)b * a.n_part + (int64_t)blockIdx.x * NW + warp) * L;
-		if (a.first_ok && !a.first_ok[b]) {
-			store_empty_record(part, p, lane, 0);
-			continue;
-		}
+		// a group without any valid row still runs: every row is masked, the pass counts the state rows
 		// equal contiguous slices per warp, multiples of 4 rows
 		const int64_t nrows = r1 - r0;
 		const int64_t nw_total = (int64_t)gridDim.x * NW;
@@ -918,9 +931,9 @@ template <int NT, bool SIDE, int NW> __global__ void __launch_bounds__(32 * NW) 
 #pragma unroll
 		for (int t = 0; t < NT; ++t) {
 			const int c = 8 * t + cl;
-			sh[t] = (c < p) ? a.shift[(int64_t)b * k + c] : 0.0;
+			sh[t] = (c < p) ? a.shift[(int64_t)bb * k + c] : 0.0;
 		}
-		shy = a.shift[(int64_t)b * k + p];
+		shy = a.shift[(int64_t)bb * k + p];
 		WarpAcc<NT, SIDE> A;
 		A.clear();
 		// chunks keep the int row index of acc_rows in range
@@ -935,32 +948,76 @@ template <int NT, bool SIDE, int NW> __global__ void __launch_bounds__(32 * NW) 
 
 // Sum the partial records of each big group in a fixed order: n, sw, n_state, S1, S2 add; cdev
 // takes the max; the shift is common to all partials.
+// field i of the sum of n_part partial records
+// (no __restrict__ on part: acc_big_kernel reads partials its own CTA has just written)
+__device__ __forceinline__ double reduce_field(const double *part, int n_part, int L, int p, int i, const double *shift) {
+	double v = 0.0;
+	if (i >= rec_off_shift(p) && i < rec_off_cdev(p)) {
+		v = shift[i - rec_off_shift(p)];
+	} else if (i >= rec_off_cdev(p) && i < rec_off_cdev(p) + p) {
+		for (int q = 0; q < n_part; ++q) v = fmax(v, part[(int64_t)q * L + i]);
+	} else if ((i >= rec_off_cdev(p) && i < rec_off_s1(p)) || i == 3) {
+		v = 0.0; // pad
+	} else {
+		for (int q = 0; q < n_part; ++q) v += part[(int64_t)q * L + i];
+	}
+	return v;
+}
 static __global__ void reduce_partials_kernel(const StreamArgs a) {
 	const int b = blockIdx.y;
-	const int nbig = a.offsets ? *a.big_count : 1;
+	int nbig = 1;
+	if (a.offsets) {
+		nbig = *a.huge_count - a.b_begin;
+		nbig = nbig < a.b_cap ? nbig : a.b_cap;
+	}
 	if (b >= nbig) return;
 	const int p = a.p, L = rec_len(p);
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= L) return;
-	const int64_t g = a.offsets ? a.big_list[b] : 0;
+	const int bb = a.offsets ? (int)a.huge_list[a.b_begin + b] : 0;
+	const int64_t g = a.offsets ? a.big_list[bb] : 0;
 	const bool ring = a.run_if && *a.run_if == 0;
 	const int n_part = ring ? a.ring_n_part : a.n_part;
 	const double *part = ring ? a.ring_partials : a.partials + (int64_t)b * a.n_part * L;
-	double v;
-	if (i >= rec_off_shift(p) && i < rec_off_cdev(p)) {
-		v = a.shift[(int64_t)b * (p + 1) + (i - rec_off_shift(p))];
-	} else if (i >= rec_off_cdev(p) && i < rec_off_cdev(p) + p) {
-		v = 0.0;
-		for (int q = 0; q < n_part; ++q) v = fmax(v, part[(int64_t)q * L + i]);
-	} else if (i >= rec_off_cdev(p) && i < rec_off_s1(p)) {
-		v = 0.0; // pad
-	} else if (i == 3) {
-		v = 0.0;
-	} else {
-		v = 0.0;
-		for (int q = 0; q < n_part; ++q) v += part[(int64_t)q * L + i];
+	a.records[g * a.rec_gs + (int64_t)i * a.rec_es] = reduce_field(part, n_part, L, p, i, a.shift + (int64_t)bb * (p + 1));
+}
+
+// Big groups of at most huge_rows rows: one CTA per group (grid-stride over the device-side list), the CTA's
+// warps take equal row slices with the checked per-element filter, their partial records meet in a fixed order.
+template <int NT, bool SIDE, int NW> __global__ void __launch_bounds__(32 * NW) acc_big_kernel(const StreamArgs a) {
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cl = lane >> 2;
+	const int p = a.p, k = p + 1, L = rec_len(p);
+	const int nbig = *a.big_count;
+	double *parts = a.partials + (int64_t)blockIdx.x * NW * L;
+	for (int b = blockIdx.x; b < nbig; b += gridDim.x) {
+		const int64_t g = a.big_list[b];
+		const int64_t r0 = a.offsets[g], r1 = a.offsets[g + 1];
+		if (r1 - r0 > a.huge_rows) continue; // sliced over the whole grid instead (acc_stream_kernel)
+		int64_t per = (r1 - r0 + NW - 1) / NW;
+		per = (per + 3) & ~(int64_t)3;
+		int64_t wb = r0 + warp * per, we = wb + per;
+		if (wb > r1) wb = r1;
+		if (we > r1) we = r1;
+		double sh[NT], shy;
+#pragma unroll
+		for (int t = 0; t < NT; ++t) {
+			const int c = 8 * t + cl;
+			sh[t] = (c < p) ? a.shift[(int64_t)b * k + c] : 0.0;
+		}
+		shy = a.shift[(int64_t)b * k + p];
+		WarpAcc<NT, SIDE> A;
+		A.clear();
+		for (int64_t cb = wb; cb < we; cb += (1 << 20)) {
+			const int64_t ce = cb + (1 << 20) < we ? cb + (1 << 20) : we;
+			acc_rows<NT, SIDE, true>(A, a.x + cb * p, a.y + cb, a.w ? a.w + cb : nullptr, a.train ? a.train + cb : nullptr,
+			                         0, (int)(ce - cb), p, lane, sh, shy, a.flags_from_y != 0);
+		}
+		store_record<NT, SIDE>(A, parts + (int64_t)warp * L, p, lane, sh, shy, -1);
+		__syncthreads(); // partials visible to the block (global stores of this CTA, read by this CTA)
+		for (int i = threadIdx.x; i < L; i += 32 * NW)
+			a.records[g * a.rec_gs + (int64_t)i * a.rec_es] = reduce_field(parts, NW, L, p, i, a.shift + (int64_t)b * k);
+		__syncthreads();
 	}
-	a.records[g * a.rec_gs + (int64_t)i * a.rec_es] = v;
 }
 
 } // namespace b200

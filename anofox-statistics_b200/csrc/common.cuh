@@ -46,7 +46,33 @@ struct FitParams {
 	const double *co;     // [kSeriesTable] ... and for odd df
 	int predict_mode;    // 1: df for t-critical follows anofox_predict_with_interval
 	int min_state_rows;  // 2 = aggregate rule (ols_aggregate.cpp:263-267); 0 = direct anofox_*_fit call
+	// QR fallback queue (qr.cuh): groups whose Cholesky met a small pivot are appended here by the solve
+	// kernels and re-fitted from their ROWS by qr_fit_kernel. null = no queue (moment-only entry points).
+	int *qr_count;
+	int64_t *qr_list;
 };
+
+// ---- ill-conditioning probe of the Gram-Cholesky solve ("QR fallback") ---------------
+// The solve kernels factor the shifted Gram matrix, whose condition number is cond(X)^2. The ratio d / a0 of a
+// column's remaining pivot to its centred diagonal is 1 - R^2 of that column on the earlier ones; the smallest
+// ratio bounds the condition number of the equilibrated Gram from below by its reciprocal and, loosely, from
+// above by p times it. With unit roundoff 1.1e-16 and an error constant of ~10 a Cholesky solve keeps 1e-9 up
+// to cond(Gram) ~ 1e6: below kQrPivotRatio = 1e-5 it can no longer promise that. Such a group -- and any group
+// where a column's aliasing decision d >= 1e-14 * orig (R's tol = 1e-7, squared) sits within half a decade of its threshold, where the Gram's own
+// rounding could flip it -- is queued for the Householder QR on the rows themselves (cond(X), not cond(X)^2,
+// and the reference default is a decomposition of X: types.rs:121-130 SVD, "falls back to QR").
+constexpr double kQrPivotRatio = 1e-5;
+__device__ __forceinline__ bool chol_pivot_suspicious(double d, double a0, double orig, bool ridge) {
+	if (!(d > 0.0)) return false; // exactly dependent (or worse): aliased for certain
+	if (!ridge) {
+		if (d >= 3e-15 * orig && d < 3e-14 * orig) return true; // decision band around 1e-14 * orig
+		if (d < 1e-14 * orig) return false;                     // aliased, and clear of the band
+	}
+	return d < kQrPivotRatio * a0;
+}
+__device__ __forceinline__ void queue_qr(const FitParams &P, int64_t g) {
+	if (P.qr_count) P.qr_list[atomicAdd(P.qr_count, 1)] = g;
+}
 
 __device__ __forceinline__ bool finite_f64(double v) {
 	return (__double2hiint(v) & 0x7ff00000) != 0x7ff00000;

@@ -353,8 +353,10 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 	unsigned live = 0u;  // columns with a coefficient
 	double rinv[P];      // 1 / L_ii
 	int rank = 0;
+	bool suspicious = false;
 #pragma unroll
 	for (int i = 0; i < P; ++i) {
+		const double a0 = A[ltri(i, i)];
 #pragma unroll
 		for (int j = 0; j < i; ++j) {
 			double s = A[ltri(i, j)];
@@ -366,6 +368,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 #pragma unroll
 		for (int c = 0; c < i; ++c) d -= A[ltri(i, c)] * A[ltri(i, c)];
 		bool alias = ridge ? !(d > 0.0) : (!(d >= 1e-14 * orig[i]) || !(d > 0.0));
+		if ((nonconst >> i) & 1u) suspicious = suspicious || chol_pivot_suspicious(d, a0, orig[i], ridge);
 		alias = alias || !((nonconst >> i) & 1u);
 		if (alias) {
 #pragma unroll
@@ -380,6 +383,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 			++rank;
 		}
 	}
+	if (suspicious && q == 0) queue_qr(Pm, g);
 	// forward solve L v = b, back solve L^T beta = v (dead columns have zero rows/columns and rinv = 0)
 	double ess = 0.0;
 #pragma unroll

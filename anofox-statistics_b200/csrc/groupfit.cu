@@ -14,7 +14,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
 #include <mutex>
+#include <new>
 #include <vector>
 
 #include "acc_launch.h"
@@ -25,6 +27,7 @@
 #include "fused_launch.h"
 #include "solve.cuh"
 #include "specfun.cuh"
+#include "qr.cuh"
 
 namespace b200 {
 
@@ -72,12 +75,13 @@ __global__ void __launch_bounds__(128) solve_kernel(const double *__restrict__ r
 // fused kernel).
 template <int PMAX>
 __global__ void __launch_bounds__(128) solve_list_kernel(const double *__restrict__ records, const int64_t *__restrict__ list,
-                                                         int n_list, FitParams P, AnofoxB200FitOutputs o,
+                                                         const int *__restrict__ n_list, FitParams P, AnofoxB200FitOutputs o,
                                                          int *refine_count, int64_t *refine_list) {
-	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n_list) return;
-	const int64_t g = list[i];
-	solve_group<PMAX>(records + g * rec_len(P.p), 1, g, P, o, -1.0, nullptr, refine_count, refine_list);
+	const int n = *n_list; // decided on the device: the host never reads the count
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		const int64_t g = list[i];
+		solve_group<PMAX>(records + g * rec_len(P.p), 1, g, P, o, -1.0, nullptr, refine_count, refine_list);
+	}
 }
 
 // Exact residual pass for the groups the solve stage queued (residual sum of squares too small
@@ -366,6 +370,63 @@ __global__ void split_record_kernel(const double *__restrict__ rec, int p, doubl
 }
 
 
+// Residual pass of one row shard (row-sharded single group): sum w (y - b0 - x'b)^2 over the shard's valid rows
+// with the coefficients of the first solve (NaN = aliased, contributes nothing: lib.rs:2296-2303). One warp per
+// row, lane j holds columns j and j + 32; block partials are added in block order by the second kernel. Runs
+// only when *run_if != 0 (the first solve found rss <= 1e-5 tss: the moment form of RSS has cancelled).
+__global__ void __launch_bounds__(256) shard_residual_kernel(const double *__restrict__ y, const double *__restrict__ x,
+                                                             const double *__restrict__ w, int64_t n_rows, int p,
+                                                             const double *__restrict__ coef, const double *__restrict__ icpt,
+                                                             const int *__restrict__ run_if, double *__restrict__ partials) {
+	__shared__ double red[8];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	double acc = 0.0;
+	if (*run_if != 0) {
+		double b0 = icpt[0];
+		if (isnan(b0)) b0 = 0.0;
+		double c0 = lane < p ? coef[lane] : 0.0, c1 = lane + 32 < p ? coef[lane + 32] : 0.0;
+		if (isnan(c0)) c0 = 0.0;
+		if (isnan(c1)) c1 = 0.0;
+		const int64_t nw = (int64_t)gridDim.x * 8;
+		for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < n_rows; r += nw) {
+			const double x0 = lane < p ? x[r * p + lane] : 0.0, x1 = lane + 32 < p ? x[r * p + lane + 32] : 0.0;
+			const double yv = y[r], wv = w ? w[r] : 1.0;
+			const bool bad = !finite_f64(x0) || !finite_f64(x1);
+			const bool ok = row_ok_yw(yv, wv, 1, w != nullptr) && !__any_sync(0xffffffffu, bad);
+			double dot = fma(c0, x0, c1 * x1);
+#pragma unroll
+			for (int off = 16; off; off >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, off);
+			if (ok) {
+				const double e = yv - (b0 + dot);
+				acc = fma(wv * e, e, acc);
+			}
+		}
+	}
+	if (lane == 0) red[warp] = acc;
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		double t = 0.0;
+		for (int i = 0; i < 8; ++i) t += red[i];
+		partials[blockIdx.x] = t;
+	}
+}
+__global__ void shard_residual_sum_kernel(const double *__restrict__ partials, int n, double *__restrict__ out) {
+	if (threadIdx.x == 0 && blockIdx.x == 0) {
+		double t = 0.0;
+		for (int i = 0; i < n; ++i) t += partials[i];
+		*out = t;
+	}
+}
+// Second solve of the row-sharded group with the all-reduced exact residual sum of squares (only when flagged).
+__global__ void __launch_bounds__(kWideThreads) solve_wide_override_kernel(const double *__restrict__ rec, FitParams P,
+                                                                           AnofoxB200FitOutputs o, const int *__restrict__ flag,
+                                                                           const double *__restrict__ rss) {
+	extern __shared__ __align__(16) unsigned char wide_smem_raw2[];
+	if (*flag == 0) return;
+	WideSmem &S = *reinterpret_cast<WideSmem *>(wide_smem_raw2);
+	solve_group_wide(S, rec, 1, 0, P, o, fmax(*rss, 0.0), nullptr, nullptr);
+}
+
 // First valid row of one row shard (row-sharded single group, step 0): blocks scan disjoint chunks in
 // order and stop as soon as an earlier chunk has reported a hit; `best` ends as the smallest valid row.
 __global__ void shard_first_valid_kernel(const double *__restrict__ y, const double *__restrict__ x,
@@ -442,7 +503,26 @@ static cudaError_t launch_resident(const AccArgs &a, int grid, cudaStream_t st) 
 	return e;
 }
 
-// Big-group streaming: each warp owns an equal slice of every big group (partials = grid * warps).
+// Big groups, one CTA per group (device-side list)
+static cudaError_t launch_big(const StreamArgs &a, int grid, cudaStream_t st) {
+	const Shape s = shape_of(a.p);
+	cudaError_t e = cudaErrorInvalidValue;
+	switch (s.nt) {
+	case 1: e = launch_big_nt1(s.side, a, grid, st); break;
+	case 2: e = launch_big_nt2(s.side, a, grid, st); break;
+	case 3: e = launch_big_nt3(s.side, a, grid, st); break;
+	case 4: e = launch_big_nt4(s.side, a, grid, st); break;
+	case 5: e = launch_big_nt5(s.side, a, grid, st); break;
+	case 6: e = launch_big_nt6(s.side, a, grid, st); break;
+	case 7: e = launch_big_nt7(s.side, a, grid, st); break;
+	case 8: e = launch_big_nt8(s.side, a, grid, st); break;
+	case 9: e = launch_big_nt9(s.side, a, grid, st); break;
+	}
+	LAUNCHED();
+	return e;
+}
+
+// Huge-group streaming: each warp owns an equal slice of every listed group (partials = grid * warps).
 static cudaError_t launch_stream(const StreamArgs &a, int grid, cudaStream_t st) {
 	const Shape s = shape_of(a.p);
 	cudaError_t e = cudaErrorInvalidValue;
@@ -556,12 +636,12 @@ static cudaError_t launch_solve(const double *records, int64_t G, const FitParam
 	return cudaGetLastError();
 }
 
-static cudaError_t launch_solve_list(const double *records, const int64_t *list, int n_list, const FitParams &P,
-                                     const AnofoxB200FitOutputs &o, int *refine_count, int64_t *refine_list,
-                                     cudaStream_t st) {
-	if (n_list <= 0) return cudaSuccess;
+static cudaError_t launch_solve_list(const double *records, const int64_t *list, const int *n_list, int64_t n_max,
+                                     const FitParams &P, const AnofoxB200FitOutputs &o, int *refine_count,
+                                     int64_t *refine_list, cudaStream_t st) {
+	if (n_max <= 0) return cudaSuccess;
 	const int threads = 128;
-	const unsigned blocks = (unsigned)((n_list + threads - 1) / threads);
+	const unsigned blocks = (unsigned)std::min<int64_t>((n_max + threads - 1) / threads, 592);
 	if (P.p <= 8)
 		solve_list_kernel<8><<<blocks, threads, 0, st>>>(records, list, n_list, P, o, refine_count, refine_list);
 	else if (P.p <= 16)
@@ -622,6 +702,17 @@ static cudaError_t launch_refine(const RefineArgs &a, const FitParams &P, const 
 	return cudaGetLastError();
 }
 
+static cudaError_t launch_qr(QrArgs &a, const FitParams &P, const AnofoxB200FitOutputs &o, int grid, cudaStream_t st) {
+	size_t dyn = 0;
+	qr_geometry(P.p, a.B, a.LD, dyn);
+	if (grid < 1) grid = 1;
+	cudaError_t e = cudaFuncSetAttribute(qr_fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+	if (e != cudaSuccess) return e;
+	qr_fit_kernel<<<grid, kQrThreads, dyn, st>>>(a, P, o);
+	LAUNCHED();
+	return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------------
 // Device properties / stage geometry
 // ---------------------------------------------------------------------------------------------
@@ -632,33 +723,41 @@ struct DeviceInfo {
 	bool ok = false;
 	char why[200] = {0};
 };
+// One entry per CUDA device, filled on first use from a thread whose current device it is (the SM count sizes
+// every grid and workspace, so it must be the calling thread's device, not whichever device came first).
 static DeviceInfo &device_info() {
-	static DeviceInfo info;
-	static std::once_flag once;
-	std::call_once(once, [] {
-		int n = 0;
-		cudaError_t e = cudaGetDeviceCount(&n);
-		if (e != cudaSuccess || n == 0) {
-			snprintf(info.why, sizeof info.why, "no CUDA device: %s", e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
-			return;
-		}
-		int dev = 0;
-		cudaGetDevice(&dev);
-		cudaDeviceProp pr;
-		if ((e = cudaGetDeviceProperties(&pr, dev)) != cudaSuccess) {
-			snprintf(info.why, sizeof info.why, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
-			return;
-		}
-		info.sms = pr.multiProcessorCount;
-		info.cc_major = pr.major;
-		info.smem_optin = pr.sharedMemPerBlockOptin;
-		if (pr.major != 10) {
-			snprintf(info.why, sizeof info.why, "device %s is sm_%d%d; this library is built for sm_100a only", pr.name,
-			         pr.major, pr.minor);
-			return;
-		}
-		info.ok = true;
-	});
+	static std::mutex mu;
+	static DeviceInfo infos[64];
+	static bool filled[64];
+	static DeviceInfo none;
+	std::lock_guard<std::mutex> lock(mu);
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) {
+		snprintf(none.why, sizeof none.why, "no CUDA device: %s", e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
+		none.ok = false;
+		return none;
+	}
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (dev < 0 || dev >= 64) dev = 0;
+	DeviceInfo &info = infos[dev];
+	if (filled[dev]) return info;
+	filled[dev] = true;
+	cudaDeviceProp pr;
+	if ((e = cudaGetDeviceProperties(&pr, dev)) != cudaSuccess) {
+		snprintf(info.why, sizeof info.why, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+		return info;
+	}
+	info.sms = pr.multiProcessorCount;
+	info.cc_major = pr.major;
+	info.smem_optin = pr.sharedMemPerBlockOptin;
+	if (pr.major != 10) {
+		snprintf(info.why, sizeof info.why, "device %s is sm_%d%d; this library is built for sm_100a only", pr.name,
+		         pr.major, pr.minor);
+		return info;
+	}
+	info.ok = true;
 	return info;
 }
 
@@ -914,15 +1013,24 @@ struct Workspace {
 	int *refine_count;
 	int64_t *redo_list;
 	int *redo_count;
+	int64_t *huge_list; // indices into big_list of the groups with more than kHugeRows rows
+	int *huge_count;
+	int64_t *qr_list;   // groups queued for the QR fallback (qr.cuh)
+	int *qr_count;
 	uint8_t *train_tmp;
 	// fit outputs used internally by the predict path when the caller passes none
 	double *f_coef, *f_icpt, *f_r2, *f_adj, *f_rse;
 	int64_t *f_nobs;
 	int32_t *f_status;
 	size_t bytes;
-	int64_t nbig_max;
+	int64_t nbig_max, nhuge_max;
 	int n_part;
 };
+
+// Big groups above this many rows are sliced over the whole grid (acc_stream_kernel, rounds of kHugeRound groups);
+// up to it one CTA streams the group (acc_big_kernel). Both decided on the device.
+constexpr int64_t kHugeRows = (int64_t)1 << 20;
+constexpr int kHugeRound = 64;
 
 static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int p, int sms) {
 	size_t off = 0;
@@ -947,14 +1055,19 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 	w.records = (double *)take((size_t)std::max<int64_t>(G, 1) * L * 8);
 	w.tile_g0 = (int64_t *)take((size_t)(std::max<int64_t>(n_tiles, sms) + 2) * 8);
 	w.big_list = (int64_t *)take((size_t)(w.nbig_max + 1) * 8);
-	w.big_count = (int *)take(768); // the three counters of a call sit together: one memset clears them
+	w.big_count = (int *)take(768); // the counters of a call sit together: one memset clears them
 	w.refine_count = w.big_count ? w.big_count + 64 : nullptr;
 	w.redo_count = w.big_count ? w.big_count + 128 : nullptr;
+	w.huge_count = w.big_count ? w.big_count + 144 : nullptr;
+	w.qr_count = w.big_count ? w.big_count + 160 : nullptr;
+	w.nhuge_max = std::min<int64_t>(w.nbig_max, N / kHugeRows + 1);
+	w.huge_list = (int64_t *)take((size_t)(w.nhuge_max + 1) * 8);
+	w.qr_list = (int64_t *)take((size_t)std::max<int64_t>(G, 1) * 8);
 	w.shift = (double *)take((size_t)(w.nbig_max + 1) * (p + 1) * 8);
 	w.first_ok = (int *)take((size_t)(w.nbig_max + 1) * 4);
 	// partial records of the streaming path: one per (big group, warp). Bounded by capping how many
 	// big groups one call may hold (see fit_device); sized here for that cap.
-	const int64_t part_groups = std::min<int64_t>(w.nbig_max, 64);
+	const int64_t part_groups = std::max<int64_t>(1, std::min<int64_t>(w.nhuge_max, kHugeRound));
 	w.partials = (double *)take((size_t)part_groups * w.n_part * L * 8);
 	w.ring_partials = (double *)take(G == 1 ? (size_t)sms * 16 * L * 8 : 0);
 	w.slice_off = (int64_t *)take((size_t)(2 * sms + 4) * 8);
@@ -1011,6 +1124,38 @@ static int validate_common(const int64_t *offsets, int64_t G, const double *y, c
 	return 0;
 }
 
+// The seven core arrays are written unconditionally by the solve kernels, the inference block when inference
+// is on: a partially filled struct would be a device-side NULL dereference.
+static int check_outputs(const AnofoxB200FitOutputs *out, bool inference, AnofoxError *err) {
+	if (!out->coefficients || !out->intercept || !out->r_squared || !out->adj_r_squared || !out->residual_std_error ||
+	    !out->n_observations || !out->status) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "a required output array is NULL (coefficients .. status)");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (inference && (!out->std_errors || !out->t_values || !out->p_values || !out->ci_lower || !out->ci_upper ||
+	                  !out->f_statistic || !out->f_pvalue)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "compute_inference needs the inference arrays (std_errors .. f_pvalue)");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	return 0;
+}
+
+// No C++ exception may cross the C boundary into DuckDB (the reference wraps every fit in catch_unwind and
+// reports "Internal panic", lib.rs:144-156): every extern "C" body below runs inside this guard.
+template <class F> static int32_t guarded(AnofoxError *err, const char *where, F &&f) noexcept {
+	try {
+		return f();
+	} catch (const std::bad_alloc &) {
+		set_error(err, ANOFOX_ERROR_ALLOCATION_FAILURE, "allocation failure");
+		return ANOFOX_ERROR_ALLOCATION_FAILURE;
+	} catch (...) {
+		char buf[160];
+		snprintf(buf, sizeof buf, "Internal exception in %s", where);
+		set_error(err, ANOFOX_ERROR_INTERNAL, buf);
+		return ANOFOX_ERROR_INTERNAL;
+	}
+}
+
 // The whole device pipeline for one batch. `train` non-null selects predict semantics.
 static int fit_device(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w,
                       const uint8_t *train, int64_t N, int p, const AnofoxB200FitOptions *opt,
@@ -1038,6 +1183,8 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	P.tcrit = P.gratio = P.rcp = P.ce = P.co = nullptr;
 	P.predict_mode = pred ? 1 : 0;
 	P.min_state_rows = min_state_rows;
+	P.qr_count = ws.qr_count;
+	P.qr_list = ws.qr_list;
 
 	if (P.compute_inference || pred) {
 		DfTables T;
@@ -1175,56 +1322,62 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		timer_mark(st);
 	}
 
-	// Big groups (rare): the count decides whether the streaming kernels run at all.
-	int nbig = 0;
+	// Big groups (rare): everything is decided on the device -- the call only enqueues work (no host read of
+	// the count). The kernels below look at *big_count themselves and return at once when it is zero.
 	if (N > big_threshold) {
-		CU(cudaMemcpyAsync(&nbig, ws.big_count, sizeof(int), cudaMemcpyDeviceToHost, st), "read big_count");
-		CU(cudaStreamSynchronize(st), "sync");
-		for (int b0 = 0; b0 < nbig; b0 += 64) {
-			const int nb = std::min(64, nbig - b0);
-			int *cnt = ws.big_count + 1; // scratch count for this slice
-			CU(cudaMemcpyAsync(cnt, &nb, sizeof(int), cudaMemcpyHostToDevice, st), "slice count");
-			StreamArgs s;
-			s.offsets = offsets;
-			s.big_list = ws.big_list + b0;
-			s.big_count = cnt;
-			s.fixed_rows = 0;
-			s.y = y;
-			s.x = x;
-			s.w = wuse;
-			s.train = train_use;
-			s.p = p;
-			s.shift = ws.shift;
-			s.first_ok = ws.first_ok;
-			s.partials = ws.partials;
-			s.n_part = ws.n_part;
-			s.records = ws.records;
-			s.rec_gs = rec_gs;
-			s.rec_es = rec_es;
-			s.run_if = nullptr;
-			s.ring_partials = nullptr;
-			s.ring_n_part = 0;
-			s.flags_from_y = y_only_flags ? 1 : 0;
-			first_valid_kernel<<<nb, 32, 0, st>>>(s);
-			LAUNCHED();
-			CU(cudaGetLastError(), "first_valid_kernel");
+		StreamArgs s;
+		s.offsets = offsets;
+		s.big_list = ws.big_list;
+		s.big_count = ws.big_count;
+		s.fixed_rows = 0;
+		s.y = y;
+		s.x = x;
+		s.w = wuse;
+		s.train = train_use;
+		s.p = p;
+		s.shift = ws.shift;
+		s.first_ok = ws.first_ok;
+		s.partials = ws.partials;
+		s.n_part = ws.n_part;
+		s.records = ws.records;
+		s.rec_gs = rec_gs;
+		s.rec_es = rec_es;
+		s.run_if = nullptr;
+		s.ring_partials = nullptr;
+		s.ring_n_part = 0;
+		s.flags_from_y = y_only_flags ? 1 : 0;
+		s.huge_list = ws.huge_list;
+		s.huge_count = ws.huge_count;
+		s.huge_rows = kHugeRows;
+		s.b_begin = 0;
+		s.b_cap = kHugeRound;
+		const int64_t nbig_max = std::min<int64_t>(G, N / std::max<int64_t>(big_threshold, 1) + 1);
+		first_valid_kernel<<<(unsigned)std::min<int64_t>(nbig_max, (int64_t)di.sms * 8), 32, 0, st>>>(s);
+		LAUNCHED();
+		CU(cudaGetLastError(), "first_valid_kernel");
+		CU(launch_big(s, (int)std::min<int64_t>(nbig_max, ws.n_part / kStreamWarps), st), "acc_big_kernel");
+		// groups above kHugeRows rows: at most N / kHugeRows of them, sliced over the whole grid in rounds
+		const int64_t nhuge_max = std::min<int64_t>(nbig_max, N / kHugeRows);
+		for (int64_t b0 = 0; b0 < nhuge_max; b0 += kHugeRound) {
+			s.b_begin = (int)b0;
 			CU(launch_stream(s, ws.n_part / kStreamWarps, st), "acc_stream_kernel");
-			dim3 rg((unsigned)((rec_len(p) + 127) / 128), (unsigned)nb);
+			dim3 rg((unsigned)((rec_len(p) + 127) / 128), (unsigned)kHugeRound);
 			reduce_partials_kernel<<<rg, 128, 0, st>>>(s);
 			LAUNCHED();
 			CU(cudaGetLastError(), "reduce_partials_kernel");
-			CU(cudaStreamSynchronize(st), "sync"); // nb lives on the host stack
 		}
 	}
 
 	if (fused) {
-		if (nbig > 0) CU(launch_solve_list(ws.records, ws.big_list, nbig, P, fo, ws.refine_count, ws.refine_list, st), "solve_list_kernel");
+		const int64_t nbig_max = N > big_threshold ? std::min<int64_t>(G, N / std::max<int64_t>(big_threshold, 1) + 1) : 0;
+		CU(launch_solve_list(ws.records, ws.big_list, ws.big_count, nbig_max, P, fo, ws.refine_count, ws.refine_list, st),
+		   "solve_list_kernel");
 	} else if (transposed) {
 		CU(launch_solve_small(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_small_kernel");
 	} else {
 		CU(launch_solve(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_kernel");
 	}
-	if (!fused || nbig > 0) {
+	if (!fused || N > big_threshold) {
 		RefineArgs ra;
 		ra.offsets = offsets;
 		ra.y = y;
@@ -1237,6 +1390,21 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		ra.refine_count = ws.refine_count;
 		ra.refine_list = ws.refine_list;
 		CU(launch_refine(ra, P, fo, di.sms, st), "refine_kernel");
+	}
+	{
+		// QR fallback for the groups whose Cholesky met a small pivot (qr.cuh); force_path 5: every group
+		QrArgs qa;
+		qa.offsets = offsets;
+		qa.y = y;
+		qa.x = x;
+		qa.w = wuse;
+		qa.train = train_use;
+		qa.flags_from_y = y_only_flags ? 1 : 0;
+		const bool all = g_force_path.load() == 5;
+		qa.count = all ? nullptr : ws.qr_count;
+		qa.list = all ? nullptr : ws.qr_list;
+		qa.n_all = G;
+		CU(launch_qr(qa, P, fo, (int)std::min<int64_t>(G, (int64_t)di.sms * 4), st), "qr_fit_kernel");
 	}
 	timer_mark(st);
 
@@ -1264,8 +1432,13 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 // ---------------------------------------------------------------------------------------------
 // Host-pointer path: library-owned device buffers
 // ---------------------------------------------------------------------------------------------
+// Library-owned device state of the host-pointer entry points: three streams, the chunk events and one arena.
+// DuckDB finalises from many threads at once (radix_partitioned_hashtable.cpp:990), so there is a small POOL of
+// these per device: a caller leases a free context (creating one while fewer than kCtxPerDevice exist, waiting
+// otherwise) and concurrent calls overlap their copies and kernels instead of queueing on one mutex.
 struct HostContext {
-	std::mutex mu;
+	int device = -1;
+	bool busy = false;
 	cudaStream_t stream = nullptr;           // compute
 	cudaStream_t in_stream = nullptr;        // host -> device copies of the chunks
 	cudaStream_t out_stream = nullptr;       // device -> host copies of finished chunks
@@ -1299,11 +1472,67 @@ struct HostContext {
 		}
 		return 0;
 	}
+	// every copy and kernel this context has enqueued is complete (error exits: the caller's host buffers must
+	// not be written or read after the call returns)
+	void drain() {
+		if (in_stream) cudaStreamSynchronize(in_stream);
+		if (stream) cudaStreamSynchronize(stream);
+		if (out_stream) cudaStreamSynchronize(out_stream);
+	}
 };
-static HostContext &host_ctx() {
-	static HostContext c;
-	return c;
+constexpr int kCtxPerDevice = 8;
+struct HostPool {
+	std::mutex mu;
+	std::condition_variable cv;
+	std::vector<HostContext *> all; // never freed: process lifetime
+};
+static HostPool &host_pool() {
+	static HostPool p;
+	return p;
 }
+struct HostLease {
+	HostContext *c = nullptr;
+	HostLease() {
+		HostPool &p = host_pool();
+		int dev = 0;
+		cudaGetDevice(&dev);
+		std::unique_lock<std::mutex> lock(p.mu);
+		for (;;) {
+			int have = 0;
+			for (HostContext *x : p.all)
+				if (x->device == dev) {
+					++have;
+					if (!x->busy) {
+						c = x;
+						break;
+					}
+				}
+			if (c) break;
+			if (have < kCtxPerDevice) {
+				c = new HostContext();
+				c->device = dev;
+				p.all.push_back(c);
+				break;
+			}
+			p.cv.wait(lock);
+		}
+		c->busy = true;
+	}
+	~HostLease() {
+		HostPool &p = host_pool();
+		{
+			std::lock_guard<std::mutex> lock(p.mu);
+			c->busy = false;
+		}
+		p.cv.notify_one();
+	}
+	HostLease(const HostLease &) = delete;
+	HostLease &operator=(const HostLease &) = delete;
+};
+struct DrainGuard { // drains the context's streams on every exit path of a host-pointer call
+	HostContext &c;
+	~DrainGuard() { c.drain(); }
+};
 
 struct DevLayout { // device mirror of one host batch
 	size_t off = 0;
@@ -1326,16 +1555,21 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
                     int min_state_rows = 2) {
 	const bool inf = !pred && opt->compute_inference;
 	if (out) {
-		if (!out->coefficients || !out->intercept || !out->r_squared || !out->adj_r_squared || !out->residual_std_error ||
-		    !out->n_observations || !out->status ||
-		    (inf && (!out->std_errors || !out->t_values || !out->p_values || !out->ci_lower || !out->ci_upper ||
-		             !out->f_statistic || !out->f_pvalue))) {
-			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "a required output array is NULL");
+		const int orc = check_outputs(out, inf, err);
+		if (orc) return orc;
+	}
+	// the CSR must be well formed before any pointer arithmetic is done with it
+	if (G > 0) {
+		bool ok = offsets[0] == 0 && offsets[G] == N;
+		for (int64_t g = 0; ok && g < G; ++g) ok = offsets[g] <= offsets[g + 1];
+		if (!ok) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "offsets must start at 0, be non-decreasing and end at n_rows");
 			return ANOFOX_ERROR_INVALID_INPUT;
 		}
 	}
-	HostContext &c = host_ctx();
-	std::lock_guard<std::mutex> lock(c.mu);
+	HostLease lease;
+	HostContext &c = *lease.c;
+	DrainGuard drain{c};
 	DeviceInfo &di = device_info();
 	// Chunks of whole groups, balanced by rows: the copy of chunk i + 1 to the device, the kernels of chunk i and
 	// the copy of chunk i - 1's results back to the host run on three streams (PCIe is full duplex and the
@@ -1441,10 +1675,7 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 		rc = fit_device(doff, Gc, (const double *)(d + o_y) + r0, (const double *)(d + o_x) + r0 * p,
 		                w ? (const double *)(d + o_w) + r0 : nullptr, train ? (const uint8_t *)(d + o_t) + r0 : nullptr, Nc, p,
 		                opt, dout, pred ? &dpred : nullptr, d + o_ws, ws_bytes, st, err, min_state_rows);
-		if (rc) {
-			cudaDeviceSynchronize();
-			return rc;
-		}
+		if (rc) return rc; // DrainGuard waits for the copies already in flight
 		if (i + 2 < nch && (rc = push(i + 2))) return rc;
 		if (nch > 1) {
 			CU(cudaEventRecord(c.done_ev[i], st), "event");
@@ -1642,8 +1873,9 @@ static int eval_specfun_host(int mode, int n, const double *a, const double *b, 
 		return ANOFOX_ERROR_INTERNAL;
 	}
 	if (n <= 0) return 0;
-	HostContext &ctx = host_ctx();
-	std::lock_guard<std::mutex> lock(ctx.mu);
+	HostLease lease;
+	HostContext &ctx = *lease.c;
+	DrainGuard drain{ctx};
 	const size_t bytes = (size_t)n * 8;
 	int rc = ctx.ensure(4 * ((bytes + 255) & ~(size_t)255), err);
 	if (rc) return rc;
@@ -1678,24 +1910,36 @@ extern "C" {
 
 bool anofox_ols_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxOlsOptions options,
                     AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference, AnofoxError *out_error) {
-	return single_fit(ANOFOX_B200_OLS, y, x, x_count, nullptr, options.fit_intercept, options.compute_inference,
-	                  options.confidence_level, 0.0, 0, (int)options.solver, (int)options.hc_type, out_core,
-	                  out_inference, out_error);
+	return guarded(out_error, "OLS fit", [&] {
+		       return single_fit(ANOFOX_B200_OLS, y, x, x_count, nullptr, options.fit_intercept, options.compute_inference,
+		                         options.confidence_level, 0.0, 0, (int)options.solver, (int)options.hc_type, out_core,
+		                         out_inference, out_error)
+		                  ? 0
+		                  : 1;
+	       }) == 0;
 }
 
 bool anofox_ridge_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxRidgeOptions options,
                       AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference, AnofoxError *out_error) {
-	return single_fit(ANOFOX_B200_RIDGE, y, x, x_count, nullptr, options.fit_intercept, options.compute_inference,
-	                  options.confidence_level, options.alpha, (int)options.lambda_scaling, (int)options.solver,
-	                  ANOFOX_HC_NONE, out_core, out_inference, out_error);
+	return guarded(out_error, "Ridge fit", [&] {
+		       return single_fit(ANOFOX_B200_RIDGE, y, x, x_count, nullptr, options.fit_intercept, options.compute_inference,
+		                         options.confidence_level, options.alpha, (int)options.lambda_scaling, (int)options.solver,
+		                         ANOFOX_HC_NONE, out_core, out_inference, out_error)
+		                  ? 0
+		                  : 1;
+	       }) == 0;
 }
 
 bool anofox_wls_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxDataArray weights,
                     AnofoxWlsOptions options, AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference,
                     AnofoxError *out_error) {
-	return single_fit(ANOFOX_B200_WLS, y, x, x_count, &weights, options.fit_intercept, options.compute_inference,
-	                  options.confidence_level, 0.0, 0, (int)options.solver, (int)options.hc_type, out_core,
-	                  out_inference, out_error);
+	return guarded(out_error, "WLS fit", [&] {
+		       return single_fit(ANOFOX_B200_WLS, y, x, x_count, &weights, options.fit_intercept, options.compute_inference,
+		                         options.confidence_level, 0.0, 0, (int)options.solver, (int)options.hc_type, out_core,
+		                         out_inference, out_error)
+		                  ? 0
+		                  : 1;
+	       }) == 0;
 }
 
 void anofox_free_result_core(AnofoxFitResultCore *result) {
@@ -1718,7 +1962,7 @@ double anofox_t_critical(double confidence_level, size_t df) {
 	if (df == 0 || !(confidence_level > 0.0) || !(confidence_level < 1.0)) return NAN; // lib.rs:2218-2220
 	double a = confidence_level, b = (double)df, out = NAN;
 	AnofoxError err;
-	if (eval_specfun_host(1, 1, &a, &b, nullptr, &out, &err) != 0) return NAN;
+	if (guarded(&err, "t_critical", [&] { return eval_specfun_host(1, 1, &a, &b, nullptr, &out, &err); }) != 0) return NAN;
 	return out;
 }
 
@@ -1787,31 +2031,32 @@ int32_t anofox_b200_fit_batch_device(const int64_t *offsets, int64_t n_groups, c
                                      const double *w, int64_t n_rows, int32_t n_features,
                                      const AnofoxB200FitOptions *options, const AnofoxB200FitOutputs *out,
                                      void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err) {
-	int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
-	if (rc) return rc;
-	if (!out || !out->coefficients || !out->status) {
-		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "outputs is NULL");
-		return ANOFOX_ERROR_INVALID_INPUT;
-	}
-	if (options->compute_inference && !out->std_errors) {
-		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "compute_inference needs the inference arrays");
-		return ANOFOX_ERROR_INVALID_INPUT;
-	}
-	return fit_device(offsets, n_groups, y, x, w, nullptr, n_rows, n_features, options, *out, nullptr, workspace,
-	                  workspace_bytes, (cudaStream_t)stream, err);
+	return guarded(err, "fit_batch_device", [&]() -> int32_t {
+		int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+		if (rc) return rc;
+		if (!out) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "outputs is NULL");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		if ((rc = check_outputs(out, options->compute_inference != 0, err))) return rc;
+		return fit_device(offsets, n_groups, y, x, w, nullptr, n_rows, n_features, options, *out, nullptr, workspace,
+		                  workspace_bytes, (cudaStream_t)stream, err);
+	});
 }
 
 int32_t anofox_b200_fit_batch_host(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
                                    const double *w, int64_t n_rows, int32_t n_features,
                                    const AnofoxB200FitOptions *options, const AnofoxB200FitOutputs *out,
                                    AnofoxError *err) {
-	int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
-	if (rc) return rc;
-	if (!out) {
-		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "outputs is NULL");
-		return ANOFOX_ERROR_INVALID_INPUT;
-	}
-	return fit_host(offsets, n_groups, y, x, w, nullptr, n_rows, n_features, options, out, nullptr, err);
+	return guarded(err, "fit_batch_host", [&]() -> int32_t {
+		int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+		if (rc) return rc;
+		if (!out) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "outputs is NULL");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		return fit_host(offsets, n_groups, y, x, w, nullptr, n_rows, n_features, options, out, nullptr, err);
+	});
 }
 
 int32_t anofox_b200_fit_predict_batch_device(const int64_t *offsets, int64_t n_groups, const double *y,
@@ -1821,16 +2066,19 @@ int32_t anofox_b200_fit_predict_batch_device(const int64_t *offsets, int64_t n_g
                                              const AnofoxB200PredictOutputs *pred, const AnofoxB200FitOutputs *fit,
                                              void *workspace, size_t workspace_bytes, void *stream,
                                              AnofoxError *err) {
-	int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
-	if (rc) return rc;
-	if (!pred || !pred->yhat || !pred->yhat_lower || !pred->yhat_upper) {
-		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "prediction outputs are NULL");
-		return ANOFOX_ERROR_INVALID_INPUT;
-	}
-	AnofoxB200FitOutputs none;
-	memset(&none, 0, sizeof none);
-	return fit_device(offsets, n_groups, y, x, w, train, n_rows, n_features, options, fit ? *fit : none, pred,
-	                  workspace, workspace_bytes, (cudaStream_t)stream, err);
+	return guarded(err, "fit_predict_batch_device", [&]() -> int32_t {
+		int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+		if (rc) return rc;
+		if (!pred || !pred->yhat || !pred->yhat_lower || !pred->yhat_upper) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "prediction outputs are NULL");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		if (fit && fit->coefficients && (rc = check_outputs(fit, false, err))) return rc; // all seven, or none
+		AnofoxB200FitOutputs none;
+		memset(&none, 0, sizeof none);
+		return fit_device(offsets, n_groups, y, x, w, train, n_rows, n_features, options, fit ? *fit : none, pred,
+		                  workspace, workspace_bytes, (cudaStream_t)stream, err);
+	});
 }
 
 int32_t anofox_b200_fit_predict_batch_host(const int64_t *offsets, int64_t n_groups, const double *y,
@@ -1838,13 +2086,15 @@ int32_t anofox_b200_fit_predict_batch_host(const int64_t *offsets, int64_t n_gro
                                            int32_t n_features, const AnofoxB200FitOptions *options,
                                            const AnofoxB200PredictOutputs *pred, const AnofoxB200FitOutputs *fit,
                                            AnofoxError *err) {
-	int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
-	if (rc) return rc;
-	if (!pred || !pred->yhat || !pred->yhat_lower || !pred->yhat_upper || !pred->is_training) {
-		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "prediction outputs are NULL");
-		return ANOFOX_ERROR_INVALID_INPUT;
-	}
-	return fit_host(offsets, n_groups, y, x, w, train, n_rows, n_features, options, fit, pred, err);
+	return guarded(err, "fit_predict_batch_host", [&]() -> int32_t {
+		int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+		if (rc) return rc;
+		if (!pred || !pred->yhat || !pred->yhat_lower || !pred->yhat_upper || !pred->is_training) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "prediction outputs are NULL");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		return fit_host(offsets, n_groups, y, x, w, train, n_rows, n_features, options, fit, pred, err);
+	});
 }
 
 size_t anofox_b200_moment_block_len(int32_t n_features) {
@@ -1964,6 +2214,11 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	s.rec_es = 1;
 	s.run_if = ws.redo_count;
 	s.flags_from_y = 0;
+	s.huge_list = nullptr;
+	s.huge_count = nullptr;
+	s.huge_rows = 0;
+	s.b_begin = 0;
+	s.b_cap = 1;
 	s.ring_partials = ws.ring_partials;
 	s.ring_n_part = units * ncw;
 	timer_mark(st);
@@ -2010,9 +2265,12 @@ int32_t anofox_b200_moments_device(const double *y, const double *x, const doubl
 	return 0;
 }
 
-int32_t anofox_b200_solve_moments_device(const double *moments, const double *cdev, const double *shift,
-                                         int32_t n_features, const AnofoxB200FitOptions *options,
-                                         const AnofoxB200FitOutputs *out, void *stream, AnofoxError *err) {
+// Common body of the moment-block solves. needs_refine (device int32, may be NULL): set to 1 by the first solve
+// (rss_exact == NULL) when the residual sum of squares of the moment form has cancelled (rss <= 1e-5 tss); with
+// rss_exact (device double) the group is solved again with that value, only when *needs_refine != 0.
+static int solve_moments_impl(const double *moments, const double *cdev, const double *shift, int32_t n_features,
+                              const AnofoxB200FitOptions *options, const AnofoxB200FitOutputs *out, int32_t *needs_refine,
+                              const double *rss_exact, void *stream, AnofoxError *err) {
 	clear_error(err);
 	DeviceInfo &di = device_info();
 	if (!di.ok) {
@@ -2020,17 +2278,33 @@ int32_t anofox_b200_solve_moments_device(const double *moments, const double *cd
 		return ANOFOX_ERROR_INTERNAL;
 	}
 	const int p = n_features;
-	if (p <= 0 || p > kMaxFeatures || !moments || !cdev || !shift || !options || !out || !out->coefficients) {
+	if (p <= 0 || p > kMaxFeatures || !moments || !cdev || !shift || !options || !out || (rss_exact && !needs_refine)) {
 		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "invalid argument");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	// the same option checks as the batched calls (validate_common)
+	if (options->method < ANOFOX_B200_OLS || options->method > ANOFOX_B200_WLS) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "unknown method");
 		return ANOFOX_ERROR_INVALID_INPUT;
 	}
 	if (options->method == ANOFOX_B200_RIDGE && options->alpha < 0.0) {
 		set_error(err, ANOFOX_ERROR_INVALID_ALPHA, "Invalid alpha: must be >= 0");
 		return ANOFOX_ERROR_INVALID_ALPHA;
 	}
+	if (options->hc_type < ANOFOX_HC_NONE || options->hc_type > ANOFOX_HC_HC3) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "unknown hc_type");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (options->hc_type != ANOFOX_HC_NONE) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "hc_type: robust standard errors need the rows; not available from a moment block");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	const int orc = check_outputs(out, options->compute_inference != 0, err);
+	if (orc) return orc;
 	cudaStream_t st = (cudaStream_t)stream;
 	double *rec = nullptr;
-	CU(cudaMallocAsync(&rec, (size_t)rec_len(p) * 8, st), "cudaMallocAsync");
+	const int L = rec_len(p);
+	CU(cudaMallocAsync(&rec, (size_t)(L + 2) * 8, st), "cudaMallocAsync");
 	assemble_record_kernel<<<1, 256, 0, st>>>(moments, cdev, shift, p, rec);
 	LAUNCHED();
 	FitParams P;
@@ -2044,8 +2318,73 @@ int32_t anofox_b200_solve_moments_device(const double *moments, const double *cd
 	P.tcrit = P.gratio = P.rcp = P.ce = P.co = nullptr; // one group: evaluate the distribution functions directly
 	P.predict_mode = 0;
 	P.min_state_rows = 2;
-	CU(launch_solve(rec, 1, P, *out, nullptr, nullptr, st), "solve_kernel");
+	P.qr_count = nullptr; // no rows at hand here (the header says what a caller with rows can do)
+	P.qr_list = nullptr;
+	if (!rss_exact) {
+		if (needs_refine) CU(cudaMemsetAsync(needs_refine, 0, sizeof(int32_t), st), "memset");
+		CU(launch_solve(rec, 1, P, *out, needs_refine, needs_refine ? (int64_t *)(rec + L) : nullptr, st), "solve_kernel");
+	} else {
+		const size_t dyn = sizeof(WideSmem);
+		CU(cudaFuncSetAttribute(solve_wide_override_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn), "attr");
+		solve_wide_override_kernel<<<1, kWideThreads, dyn, st>>>(rec, P, *out, needs_refine, rss_exact);
+		LAUNCHED();
+		CU(cudaGetLastError(), "solve_wide_override_kernel");
+	}
 	CU(cudaFreeAsync(rec, st), "cudaFreeAsync");
+	return 0;
+}
+
+int32_t anofox_b200_solve_moments_device(const double *moments, const double *cdev, const double *shift,
+                                         int32_t n_features, const AnofoxB200FitOptions *options,
+                                         const AnofoxB200FitOutputs *out, void *stream, AnofoxError *err) {
+	return guarded(err, "solve_moments_device", [&]() -> int32_t {
+		return solve_moments_impl(moments, cdev, shift, n_features, options, out, nullptr, nullptr, stream, err);
+	});
+}
+
+int32_t anofox_b200_solve_moments_refine_device(const double *moments, const double *cdev, const double *shift,
+                                                int32_t n_features, const AnofoxB200FitOptions *options,
+                                                const AnofoxB200FitOutputs *out, int32_t *needs_refine,
+                                                const double *rss_exact, void *stream, AnofoxError *err) {
+	return guarded(err, "solve_moments_refine_device", [&]() -> int32_t {
+		if (!needs_refine) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "needs_refine is NULL");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		return solve_moments_impl(moments, cdev, shift, n_features, options, out, needs_refine, rss_exact, stream, err);
+	});
+}
+
+int32_t anofox_b200_shard_residual_device(const double *y, const double *x, const double *w, int64_t n_rows,
+                                          int32_t n_features, const double *coefficients, const double *intercept,
+                                          const int32_t *run_if, double *rss_partial, void *workspace,
+                                          size_t workspace_bytes, void *stream, AnofoxError *err) {
+	clear_error(err);
+	DeviceInfo &di = device_info();
+	if (!di.ok) {
+		set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+		return ANOFOX_ERROR_INTERNAL;
+	}
+	const int p = n_features;
+	if (p <= 0 || p > kMaxFeatures || n_rows < 0 || !coefficients || !intercept || !run_if || !rss_partial ||
+	    (n_rows > 0 && (!x || !y))) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "invalid argument");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	Workspace ws;
+	const size_t need = carve(ws, (unsigned char *)workspace, 1, n_rows, p, di.sms);
+	if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 255)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "workspace too small or misaligned");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	cudaStream_t st = (cudaStream_t)stream;
+	const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)di.sms * 8, (n_rows + 7) / 8));
+	shard_residual_kernel<<<blocks, 256, 0, st>>>(y, x, w, n_rows, p, coefficients, intercept, run_if, ws.partials);
+	LAUNCHED();
+	CU(cudaGetLastError(), "shard_residual_kernel");
+	shard_residual_sum_kernel<<<1, 32, 0, st>>>(ws.partials, blocks, rss_partial);
+	LAUNCHED();
+	CU(cudaGetLastError(), "shard_residual_sum_kernel");
 	return 0;
 }
 
@@ -2093,8 +2432,29 @@ int64_t anofox_b200_stage_timing_read(double *accumulate_ms, double *solve_ms) {
 }
 
 // Test / A-B hook: 0 = choose the kernel path automatically, 1 = always the record path (DMMA accumulation
-// kernel + solve kernel), even where the fused small-group kernel would be chosen.
+// kernel + solve kernel), even where the fused small-group kernel would be chosen, 2 = fused small kernel,
+// 3 = whole-group stages, 4 = ring slices for wide shards, 5 = auto + every group re-fitted by the QR kernel.
 void anofox_b200_force_path(int32_t path) { g_force_path.store(path); }
+
+// Test / bench hook: the device-side counters of the last call that used `workspace` (synchronises the device):
+// out[0] big groups, [1] groups sent to the exact residual pass, [2] groups redone by the checked accumulation,
+// [3] groups above kHugeRows, [4] groups re-fitted by the QR fallback.
+int32_t anofox_b200_debug_counters(const void *workspace, int64_t n_groups, int64_t n_rows, int32_t n_features,
+                                   int32_t *out) {
+	if (!workspace || !out || n_features <= 0 || n_features > kMaxFeatures) return ANOFOX_ERROR_INVALID_INPUT;
+	DeviceInfo &di = device_info();
+	Workspace ws;
+	carve(ws, (unsigned char *)const_cast<void *>(workspace), n_groups, n_rows, n_features, di.sms > 0 ? di.sms : 148);
+	int h[192];
+	if (cudaDeviceSynchronize() != cudaSuccess) return ANOFOX_ERROR_INTERNAL;
+	if (cudaMemcpy(h, ws.big_count, sizeof h, cudaMemcpyDeviceToHost) != cudaSuccess) return ANOFOX_ERROR_INTERNAL;
+	out[0] = h[0];
+	out[1] = h[64];
+	out[2] = h[128];
+	out[3] = h[144];
+	out[4] = h[160];
+	return 0;
+}
 // Which path a batch of this shape takes: 1 = fused small-group kernel (lanes_per_group set), 0 = record path.
 int32_t anofox_b200_plan(int64_t n_groups, int64_t n_rows, int32_t n_features, int32_t has_w, int32_t has_train,
                          int32_t *lanes_per_group) {

@@ -200,7 +200,9 @@ __device__ void solve_group(const double *__restrict__ rec, int64_t rs, int64_t 
 	// ---- Cholesky, left to right, limited pivoting -----------------------------------------
 	bool dead[PMAX];
 	int rank = 0;
+	bool suspicious = false;
 	for (int i = 0; i < pe; ++i) {
+		const double a0 = A[lt_idx(i, i)];
 		for (int j = 0; j < i; ++j) {
 			if (dead[j]) {
 				A[lt_idx(i, j)] = 0.0;
@@ -213,6 +215,7 @@ __device__ void solve_group(const double *__restrict__ rec, int64_t rs, int64_t 
 		double d = A[lt_idx(i, i)];
 		for (int c = 0; c < i; ++c) d -= A[lt_idx(i, c)] * A[lt_idx(i, c)];
 		bool alias = ridge ? !(d > 0.0) : !(d >= 1e-14 * orig[i]) || !(d > 0.0);
+		suspicious = suspicious || chol_pivot_suspicious(d, a0, orig[i], ridge);
 		dead[i] = alias;
 		if (alias) {
 			for (int c = 0; c <= i; ++c) A[lt_idx(i, c)] = 0.0;
@@ -221,6 +224,7 @@ __device__ void solve_group(const double *__restrict__ rec, int64_t rs, int64_t 
 			++rank;
 		}
 	}
+	if (suspicious && rss_override < 0.0) queue_qr(P, g);
 	// forward solve L v = b
 	double ess = 0.0; // explained sum of squares |v|^2
 	for (int i = 0; i < pe; ++i) {

@@ -144,8 +144,10 @@ __global__ void __launch_bounds__(64) solve_mid_kernel(const double *__restrict_
 
 	// ---- Cholesky, left to right, limited pivoting (solve.cuh) ---------------------------------------------
 	int rank = 0;
+	bool suspicious = false;
 	for (int i = 0; i < p; ++i) {
 		const bool dead_i = (dead >> i) & 1u;
+		const double a0 = LL(i, i);
 		for (int j = 0; j < i; ++j) {
 			if (dead_i || ((dead >> j) & 1u)) {
 				LL(i, j) = 0.0;
@@ -164,6 +166,7 @@ __global__ void __launch_bounds__(64) solve_mid_kernel(const double *__restrict_
 #pragma unroll 4
 		for (int c = 0; c < i; ++c) d -= LL(i, c) * LL(i, c);
 		const bool alias = ridge ? !(d > 0.0) : !(d >= 1e-14 * ORIG(i)) || !(d > 0.0);
+		suspicious = suspicious || chol_pivot_suspicious(d, a0, ORIG(i), ridge);
 		if (alias) {
 			dead |= 1u << i;
 			for (int c = 0; c <= i; ++c) LL(i, c) = 0.0;
@@ -172,6 +175,7 @@ __global__ void __launch_bounds__(64) solve_mid_kernel(const double *__restrict_
 			++rank;
 		}
 	}
+	if (suspicious) queue_qr(P, g);
 	// forward solve L v = b, back solve L^T beta = v
 	double ess = 0.0;
 	for (int i = 0; i < p; ++i) {
@@ -441,9 +445,11 @@ __global__ void __launch_bounds__(kFixT) solve_fixed_kernel(const double *__rest
 	}
 	// ---- Cholesky, left to right, limited pivoting. L(i, c) lives in FU(c, i); 1 / L(i, i) replaces orig(i) --
 	int rank = 0;
+	bool suspicious = false;
 #pragma unroll
 	for (int i = 0; i < PM; ++i) {
 		if (i < p) {
+			const double a0 = FU(i, i);
 #pragma unroll
 			for (int j = 0; j < i; ++j) {
 				double s = FU(j, i);
@@ -455,6 +461,7 @@ __global__ void __launch_bounds__(kFixT) solve_fixed_kernel(const double *__rest
 #pragma unroll
 			for (int c = 0; c < i; ++c) d -= FU(c, i) * FU(c, i);
 			bool alias = ridge ? !(d > 0.0) : (!(d >= 1e-14 * FORIG(i)) || !(d > 0.0));
+			if (!((dead >> i) & 1u)) suspicious = suspicious || chol_pivot_suspicious(d, a0, FORIG(i), ridge);
 			alias = alias || ((dead >> i) & 1u);
 			if (alias) {
 				dead |= 1u << i;
@@ -472,6 +479,7 @@ __global__ void __launch_bounds__(kFixT) solve_fixed_kernel(const double *__rest
 			FORIG(i) = 0.0;
 		}
 	}
+	if (suspicious) queue_qr(P, g);
 	// forward solve L v = b, back solve L^T beta = v (dead columns: zero rows / columns, reciprocal 0)
 	double ess = 0.0;
 #pragma unroll

@@ -23,6 +23,7 @@ struct WideSmem {
 	int idx[kWideThreads];
 	int dead[kWideThreads];
 	int pe;
+	int suspicious; // a Cholesky pivot fell below the QR-fallback threshold (common.cuh)
 };
 
 __device__ __forceinline__ double wide_sum(WideSmem &S, double mine, int tid) {
@@ -153,6 +154,7 @@ __device__ void solve_group_wide(WideSmem &S, const double *__restrict__ rec, in
 	__syncthreads();
 
 	// ---- Cholesky, column by column, limited pivoting (same sums, in the same order, as solve_group) ----
+	if (tid == 0) S.suspicious = 0;
 	for (int j = 0; j < pe; ++j) {
 		double s = 0.0;
 		if (act && a >= j) {
@@ -160,7 +162,11 @@ __device__ void solve_group_wide(WideSmem &S, const double *__restrict__ rec, in
 			for (int c = 0; c < j; ++c) s -= S.L[a * kWideLd + c] * S.L[j * kWideLd + c];
 		}
 		__syncthreads(); // row j (read by all) is about to be rewritten by thread j
-		if (a == j) S.red[0] = s;
+		if (a == j) {
+			S.red[0] = s;
+			// thread j owns both the remaining pivot and the diagonal it started from: the ill-conditioning probe
+			if (rss_override < 0.0 && chol_pivot_suspicious(s, S.L[j * kWideLd + j], S.orig[j], ridge)) S.suspicious = 1;
+		}
 		__syncthreads();
 		const double d = S.red[0];
 		const bool alias = ridge ? !(d > 0.0) : !(d >= 1e-14 * S.orig[j]) || !(d > 0.0);
@@ -181,6 +187,7 @@ __device__ void solve_group_wide(WideSmem &S, const double *__restrict__ rec, in
 		}
 		__syncthreads();
 	}
+	if (tid == 0 && S.suspicious) queue_qr(P, g);
 	const bool live = act && !S.dead[a];
 	int rank = 0;
 	for (int i = 0; i < pe; ++i) rank += S.dead[i] ? 0 : 1;

@@ -9,6 +9,8 @@ the plumbing (NCCL on GPUs; the same code runs over gloo with a CPU backend in t
   1. every rank accumulates the shifted moment block of its rows       -> moments [L], cdev [p]
   2. all_reduce(moments, SUM); all_reduce(cdev, MAX)                   (~35 KB at p = 64: latency-bound)
   3. every rank solves from the reduced block: identical inputs => identical results on every rank
+  4. exact fits: when the first solve reports rss <= 1e-5 tss (device flag, no host read) every rank sums the
+     squared residuals of its rows, all_reduce(SUM) of ONE double, and the group is solved again with it
 
 The reference cannot run this case at all: its aggregate state would hold 520 GB of raw rows in one
 std::vector (SURVEY.md section 5).
@@ -66,12 +68,30 @@ class CudaBackend:
         self._check(rc, err)
         return m, cd
 
-    def solve(self, moments, cdev, shift, options, out_struct):
+    def solve(self, moments, cdev, shift, options, out_struct, flag=None, rss=None):
+        """flag (int32[1]) given: the refining form -- first solve (rss None) or second solve with the exact RSS."""
         err = abi.AnofoxError()
-        rc = self.lib.anofox_b200_solve_moments_device(self._p(moments), self._p(cdev), self._p(shift), self.p,
-                                                       C.byref(options), C.byref(out_struct), self._stream(),
-                                                       C.byref(err))
+        if flag is None:
+            rc = self.lib.anofox_b200_solve_moments_device(self._p(moments), self._p(cdev), self._p(shift), self.p,
+                                                           C.byref(options), C.byref(out_struct), self._stream(),
+                                                           C.byref(err))
+        else:
+            rc = self.lib.anofox_b200_solve_moments_refine_device(self._p(moments), self._p(cdev), self._p(shift),
+                                                                  self.p, C.byref(options), C.byref(out_struct),
+                                                                  self._p(flag), self._p(rss), self._stream(),
+                                                                  C.byref(err))
         self._check(rc, err)
+
+    def residual(self, y, x, w, coefficients, intercept, flag):
+        """This shard's sum w (y - b0 - x'b)^2 (device f64[1]); zero, at no cost, when flag[0] == 0."""
+        out = self.torch.zeros(1, dtype=self.torch.float64, device=self.device)
+        err = abi.AnofoxError()
+        rc = self.lib.anofox_b200_shard_residual_device(self._p(y), self._p(x), self._p(w), y.numel(), self.p,
+                                                        self._p(coefficients), self._p(intercept), self._p(flag),
+                                                        self._p(out), C.c_void_p(self.ws_ptr), self.ws_bytes,
+                                                        self._stream(), C.byref(err))
+        self._check(rc, err)
+        return out
 
 
 def choose_shift(gathered):
@@ -113,9 +133,17 @@ class ShardedSingleGroupFit:
         self.dist, self.group = dist, group
         self.backend = CudaBackend(n_rows_local_max, p, torch.device(device))
         self.fit_out = DeviceFit(1, 1, p, inference=inference, device=device)
+        self.flag = torch.zeros(1, dtype=torch.int32, device=device)
 
     def fit(self, y, x, w=None, **opt):
         o = abi.make_fit_options(**opt)
         m, cd, shift = sharded_moments(self.backend, y, x, w, self.dist, self.group)
-        self.backend.solve(m, cd, shift, o, self.fit_out.out_struct)
-        return self.fit_out.out
+        out = self.fit_out.out
+        self.backend.solve(m, cd, shift, o, self.fit_out.out_struct, flag=self.flag)
+        # exact-fit guard (no host read of the flag: the kernels look at it themselves)
+        rss = self.backend.residual(y, x, w, out["coefficients"], out["intercept"], self.flag)
+        dist = self.dist
+        if dist is not None and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(rss, op=dist.ReduceOp.SUM, group=self.group)
+        self.backend.solve(m, cd, shift, o, self.fit_out.out_struct, flag=self.flag, rss=rss)
+        return out

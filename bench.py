@@ -168,9 +168,6 @@ def run_c4(args, rank, world, local):
     import torch.distributed as dist
     from importlib import import_module
     from __graft_entry__ import load_package
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = load_package()
     pkg.device_check()
     D = import_module("anofox_statistics_b200.distributed")
@@ -244,11 +241,11 @@ def run_c4(args, rank, world, local):
         roofline = {"bound": "tensor", "kernel": "acc_slice_kernel<8,SIDE> (FP64 DMMA Gram of one row shard, "
                                                  "split-role warps, TMA-fed ring)",
                     "achieved": tf, "peak": dmma_peak,
-                    "peak_source": "measured FP64 DMMA m8n8k4 rate, tools/microbench.cu (nominal 40)",
+                    "peak_source": "builder-measured FP64 DMMA m8n8k4 issue rate (tools/microbench.cu, profiles/r01d_microbench.txt); "
+                                   "MEASURED_PEAKS.json has no FP64 figure; nominal 40 TFLOP/s quoted beside it",
                     "unit": "TFLOP/s", "frac": (tf / dmma_peak) if tf else None,
-                    # ncu capture of this kernel at 1/10 of the rows (profiles/r01d_c4_acc_slice_summary.txt): 6.5014 GB
-                    # read + 4.2 MB written for 6.5000 GB algorithmic; scaled by the row count here
-                    "traffic": acc_bytes * (6.501365e9 + 4.2e6) / 6.5e9,
+                    "traffic": None, "traffic_source": load_traffic().get("C4"),  # captured at 1/10 of the rows: not per-launch here
+                    "frac_of_nominal_40_tflops": (tf / 40.0) if tf else None,
                     "algorithmic_flops_per_launch": flops, "algorithmic_bytes_per_launch": acc_bytes,
                     "avg_launch_ms": acc_launch_ms, "avg_launch_ms_per_rank": acc_ranks,
                     "hbm_achieved_gbs": achieved, "hbm_peak_gbs": peak, "hbm_peak_source": peak_src,
@@ -268,9 +265,208 @@ def run_c4(args, rank, world, local):
                 "fits_per_sec": 1.0 / (ms_per_step * 1e-3), "identical_on_all_ranks": same,
                 "status": int(out["status"][0].item()), "n_observations": int(out["n_observations"][0].item()),
                 "clocks": clocks, "e2e": None, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": None}
-        emit(line)
+        return line
+    return None
+
+
+def bind_to_gpu_numa(local):
+    """Pin this process to the CPU cores NVML reports as closest to its GPU, so that the pinned host buffers of the
+    e2e leg are first-touched on that GPU's NUMA node. Returns a short description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (w >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        use = sorted(cpus & allowed)
+        if use:
+            os.sched_setaffinity(0, use)
+            return "nvml cpu affinity of gpu %d: %d cores (%d..%d)" % (local, len(use), use[0], use[-1])
+        return "nvml affinity disjoint from the cpuset (%d allowed cores): unchanged" % len(allowed)
+    except Exception as e:  # NVML missing or not permitted: report, do not fail the bench
+        return "unchanged (%s)" % type(e).__name__
+
+
+def load_traffic():
+    """profiles/traffic.json: dram bytes per launch of each workload's dominant kernel from an `ncu --set full`
+    capture, written by tools/ncu_traffic.py together with the capture's own kernel duration and source file."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
+
+
+NAMES = {"C1": "ols_fit_agg 10k groups x 100 rows x 3 features",
+         "C2": "ols_fit_agg 1M groups x 50 rows x 5 features, full inference",
+         "C3r": "ridge_fit_agg(lambda=1) 1M groups x 200 rows x 16 features incl. rank-deficient groups",
+         "C3w": "wls_fit_agg 1M groups x 200 rows x 16 features incl. rank-deficient groups",
+         "C5": "ols_fit_predict_by 100k groups x 1k rows x 8 features, 20% held-out"}
+
+
+def run_group_workload(args, wname, rank, world, local, steps, warmup, headline, data_cache=None):
+    """One group-sharded workload on this rank (weak scaling: every rank fits its own copy of the shape).
+    Returns the result dict on rank 0 (None elsewhere)."""
+    import torch
+    import torch.distributed as dist
+    from importlib import import_module
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    synth = import_module("anofox_statistics_b200.synth")
+    G, n, p, method, inference, extra = WORKLOADS[wname]
+    G = max(64, int(G * args.scale))
+    N = G * n
+    predict = bool(extra.get("predict"))
+    key = (G, n, p, bool(extra.get("rank_deficient")), extra.get("holdout", 0.0))
+    if data_cache is not None and data_cache.get("key") == key:
+        d = data_cache["d"]
+    else:
+        if data_cache is not None:
+            data_cache.clear()
+            torch.cuda.empty_cache()
+        # C3r and C3w share one data set (the weights are simply unused by ridge)
+        d = synth.make_torch(G, n, p, seed=2 + rank, weights=bool(extra.get("weights")) or wname.startswith("C3"),
+                             rank_deficient=extra.get("rank_deficient", False), holdout=extra.get("holdout", 0.0))
+        if data_cache is not None:
+            data_cache.update(key=key, d=d)
+    w_in = d["w"] if method == "wls" else None
+    fit = pkg.DeviceFit(G, N, p, inference=inference, predict=predict)
+    opt = dict(method=method, compute_inference=inference, alpha=extra.get("alpha", 0.0))
+
+    def step():
+        if predict:
+            fit.fit_predict(d["offsets"], d["y"], d["x"], w_in, None, **opt)
+        else:
+            fit.fit(d["offsets"], d["y"], d["x"], w_in, **opt)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    pkg.stage_timing(True)
+    l0 = pkg.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = pkg.launch_count() - l0
+    calls, acc_ms, solve_ms = pkg.stage_timing_read()
+    pkg.stage_timing(False)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
-        dist.destroy_process_group()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t.item()) / steps
+    value = world * G / (ms_per_step * 1e-3)
+    n_ok = int((fit.out["status"] == 0).sum().item())
+    counters = fit.counters()
+
+    # ------------------------------------------------------------------ e2e through the host-pointer C ABI
+    e2e = None
+    if headline and not args.no_e2e:
+        import ctypes as C
+        abi = pkg.abi
+        pin = lambda tt: tt.cpu().pin_memory()  # noqa: E731
+        h = {k: (pin(d[k]) if d[k] is not None else None) for k in ("offsets", "y", "x")}
+        h["w"] = pin(w_in) if w_in is not None else None
+        ho = {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in fit.out.items()}
+        hs = abi.B200FitOutputs()
+        for nm, ctype in abi.B200FitOutputs._fields_:
+            setattr(hs, nm, None if nm not in ho else C.cast(ho[nm].data_ptr(), ctype))
+        hp, hps = None, None
+        if predict:
+            hp = {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in fit.pred.items()}
+            hps = abi.B200PredictOutputs()
+            for nm, ctype in abi.B200PredictOutputs._fields_:
+                setattr(hps, nm, C.cast(hp[nm].data_ptr(), ctype))
+        ptr = lambda tt: None if tt is None else tt.data_ptr()  # noqa: E731
+        e2e_steps = max(1, min(steps, 5))
+
+        def e2e_step():
+            if predict:
+                pkg.fit_predict_batch_host_into(ptr(h["offsets"]), ptr(h["y"]), ptr(h["x"]), ptr(h["w"]), None, hps, hs, G, N, p, **opt)
+            else:
+                pkg.fit_batch_host_into(ptr(h["offsets"]), ptr(h["y"]), ptr(h["x"]), ptr(h["w"]), hs, G, N, p, **opt)
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        barrier()
+        dt = (time.perf_counter() - t0) / e2e_steps
+        # the copies alone, from the same pinned buffers on one stream: what the PCIe / host-memory path gives this rank
+        dev_in = [torch.empty_like(d[k]) for k in ("y", "x")]
+        torch.cuda.synchronize()
+        c0 = time.perf_counter()
+        for _ in range(2):
+            dev_in[0].copy_(h["y"], non_blocking=True)
+            dev_in[1].copy_(h["x"], non_blocking=True)
+        torch.cuda.synchronize()
+        h2d_gbs = 2 * (h["y"].numel() + h["x"].numel()) * 8 / (time.perf_counter() - c0) / 1e9
+        del dev_in
+        tt = torch.tensor([dt, -h2d_gbs], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt[0].item())
+        h2d = sum(v.numel() * v.element_size() for v in h.values() if v is not None)
+        d2h = sum(v.numel() * v.element_size() for v in ho.values())
+        if hp:
+            d2h += sum(v.numel() * v.element_size() for v in hp.values())
+        same = bool(torch.equal(ho["status"], fit.out["status"].cpu()))
+        e2e = {"value": world * G / dt, "unit": "fits/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": dt * 1e3, "steps": e2e_steps, "matches_device_path": same,
+               "h2d_only_gbs_slowest_rank": -float(tt[1].item()),
+               "call_gbs_per_rank": (h2d + d2h) / dt / 1e9}
+        del h, ho, hp
+
+    if rank != 0:
+        return None
+    peak, peak_src = measured_peak_gbs()
+    inp, outb = algorithmic_bytes(G, N, p, method, inference, predict)
+    acc_launch_ms = acc_ms / max(calls, 1)
+    acc_bytes = N * (8 * (p + 1) + (8 if method == "wls" else 0)) + 8 * (G + 1)
+    achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
+    path, lanes = pkg.plan(G, N, p, method == "wls", predict)
+    if path == "fused":
+        kname = "fit_small_kernel<%d> (rows -> moment records, %d lanes per group, TMA-staged)" % (p, lanes)
+    else:
+        kname = "acc_ring_kernel (streaming ring of TMA windows, FP64 DMMA moment accumulation)"
+    tr = load_traffic().get(wname) if args.scale == 1.0 else None
+    roofline = {"bound": "hbm", "kernel": kname,
+                "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                "frac": (achieved / peak) if achieved else None,
+                "traffic": (tr["dram_read_bytes"] + tr["dram_write_bytes"]) if tr else None,
+                "traffic_source": ({k: tr.get(k) for k in ("file", "kernel", "capture_duration_us", "commit")} if tr else None),
+                "algorithmic_bytes_per_launch": acc_bytes, "avg_launch_ms": acc_launch_ms,
+                "solve_stage_ms": solve_ms / max(calls, 1), "solve_share_of_step": (solve_ms / max(calls, 1)) / ms_per_step,
+                "step_algorithmic_gbs": (inp + outb) / (ms_per_step * 1e-3) / 1e9,
+                "step_frac_of_peak": (inp + outb) / (ms_per_step * 1e-3) / 1e9 / peak}
+    cpu = None
+    if headline and not args.no_cpu and world == 1:  # the CPU baseline leg runs at N = 1 only (task contract)
+        gs = min(G, 200_000)
+        host = {"offsets": d["offsets"][:gs + 1].cpu().numpy(), "y": d["y"][:gs * n].cpu().numpy(),
+                "x": d["x"][:gs * n].cpu().numpy(), "w": w_in[:gs * n].cpu().numpy() if w_in is not None else None}
+        v, dt, used, threads = cpu_reference_run((gs, n, p, method, inference, extra), host, 3, 1, 0, budget_s=12.0)
+        cpu = {"value": v, "unit": "fits/s", "cores": threads, "kind": "port",
+               "sample": f"{used} groups x {n} rows per step, 3 steps (oracle f64 build, OpenMP over groups)"}
+    return {"value": value, "ms_per_step": ms_per_step, "rows_per_sec": value * n, "groups_fitted_ok": n_ok,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+            "device_counters": counters, "G": G, "n": n, "p": p, "method": method, "inference": inference, "N": N,
+            "steps": steps}
 
 
 def main():
@@ -283,6 +479,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the groups (smoke runs only)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the other BASELINE configs after the headline")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -290,38 +487,41 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.workload == "C4" and args.impl == "ours":
-        return run_c4(args, rank, world, local)
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        if world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        line = run_c4(args, rank, world, local)
+        if rank == 0:
+            emit(line)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     G, n, p, method, inference, extra = WORKLOADS[args.workload]
     G = max(64, int(G * args.scale))
-    wl = (G, n, p, method, inference, extra)
     N = G * n
-    name = {"C1": "ols_fit_agg 10k groups x 100 rows x 3 features",
-            "C2": "ols_fit_agg 1M groups x 50 rows x 5 features, full inference",
-            "C3r": "ridge_fit_agg(lambda=1) 1M groups x 200 rows x 16 features incl. rank-deficient groups",
-            "C3w": "wls_fit_agg 1M groups x 200 rows x 16 features incl. rank-deficient groups",
-            "C5": "ols_fit_predict_by 100k groups x 1k rows x 8 features, 20% held-out"}[args.workload]
-    config = {"workload": name, "groups_per_gpu": G, "rows_per_group": n, "features": p, "method": method,
+    config = {"workload": NAMES[args.workload], "groups_per_gpu": G, "rows_per_group": n, "features": p, "method": method,
               "inference": inference, "sharding": "group-range per rank, no collective",
               "l2_policy": "inputs (%.2f GB/step) exceed the 126 MB L2" % (N * 8 * (p + 1) / 1e9)}
 
-    import numpy as np
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
         if rank != 0:
             return
-        from __graft_entry__ import load_package
-        synth = __import__("importlib").import_module("anofox_statistics_b200.synth") if False else None
-        pkg = load_package()
         from importlib import import_module
+        from __graft_entry__ import load_package
+        load_package()
         synth = import_module("anofox_statistics_b200.synth")
         gs = min(G, 200_000)
         d = synth.make_numpy(gs, n, p, seed=2, weights=extra.get("weights", False),
                              rank_deficient=extra.get("rank_deficient", False))
         wl_s = (gs, n, p, method, inference, extra)
-        v, dt, used, threads = cpu_reference_run(wl_s, d, max(args.steps, 1), args.warmup, 0,
-                                                 budget_s=60.0)
+        v, dt, used, threads = cpu_reference_run(wl_s, d, max(args.steps, 1), args.warmup, 0, budget_s=60.0)
+        # the arm times a bounded sample of the workload (throughput-normalised): say so in the config
+        config = dict(config, groups_timed_per_step=used, sample_of_workload="first %d of %d groups, same generator" % (used, G))
         line = {"impl": "reference", "metric": "fits_per_sec", "value": v, "unit": "fits/s", "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
@@ -337,136 +537,47 @@ def main():
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local)
+    affinity = bind_to_gpu_numa(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    from importlib import import_module
     from __graft_entry__ import load_package
     pkg = load_package()
     pkg.device_check()
-    synth = import_module("anofox_statistics_b200.synth")
-    predict = bool(extra.get("predict"))
-    d = synth.make_torch(G, n, p, seed=2 + rank, weights=extra.get("weights", False),
-                         rank_deficient=extra.get("rank_deficient", False), holdout=extra.get("holdout", 0.0))
-    fit = pkg.DeviceFit(G, N, p, inference=inference, predict=predict)
-    opt = dict(method=method, compute_inference=inference, alpha=extra.get("alpha", 0.0))
-
-    def step():
-        if predict:
-            fit.fit_predict(d["offsets"], d["y"], d["x"], d["w"], None, **opt)
-        else:
-            fit.fit(d["offsets"], d["y"], d["x"], d["w"], **opt)
-
-    def barrier():
+    cache = {}
+    r = run_group_workload(args, args.workload, rank, world, local, args.steps, args.warmup, True, cache)
+    secondary = {}
+    if not args.no_secondary and args.workload == "C2" and args.scale == 1.0:
+        # the other BASELINE configs, a few steps each, so that the driver's BENCH / SCALE records time them too
+        for wn in ("C1", "C3r", "C3w", "C5"):
+            s = run_group_workload(args, wn, rank, world, local, 5, 3, False, cache)
+            if rank == 0:
+                secondary[wn] = {"workload": NAMES[wn], "ms_per_step": s["ms_per_step"], "fits_per_sec": s["value"],
+                                 "rows_per_sec": s["rows_per_sec"], "steps": s["steps"],
+                                 "accumulate_kernel_ms": s["roofline"]["avg_launch_ms"],
+                                 "accumulate_frac_of_peak": s["roofline"]["frac"],
+                                 "solve_share_of_step": s["roofline"]["solve_share_of_step"],
+                                 "step_frac_of_peak": s["roofline"]["step_frac_of_peak"],
+                                 "gpu_launches": s["gpu_launches"], "device_counters": s["device_counters"],
+                                 "groups_fitted_ok": s["groups_fitted_ok"], "clocks": s["clocks"]}
+        cache.clear()
+        torch.cuda.empty_cache()
         if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
-        step()
-    barrier()
-    sampler = ClockSampler(local)
+            # C4: the single huge group, 125 M rows x 64 features per GPU, three NCCL collectives per fit
+            a4 = argparse.Namespace(**vars(args))
+            a4.steps, a4.warmup = 5, 3
+            c4 = run_c4(a4, rank, world, local)
+            if rank == 0:
+                secondary["C4"] = {k: c4[k] for k in ("value", "unit", "ms_per_step", "identical_on_all_ranks",
+                                                      "n_observations", "roofline", "config", "gpu_launches")}
     if rank == 0:
-        sampler.start()
-    pkg.stage_timing(True)
-    l0 = pkg.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
-    launches = pkg.launch_count() - l0
-    calls, acc_ms, solve_ms = pkg.stage_timing_read()
-    pkg.stage_timing(False)
-    clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    ms_per_step = ms_max / args.steps
-    value = world * G / (ms_per_step * 1e-3)
-
-    # sanity of what was timed: every group fitted
-    st = fit.out["status"]
-    n_ok = int((st == 0).sum().item())
-
-    # ------------------------------------------------------------------ e2e through the host-pointer C ABI
-    e2e = None
-    if not args.no_e2e and not predict:
-        import ctypes as C
-        abi = pkg.abi
-        pin = lambda tt: tt.cpu().pin_memory()  # noqa: E731
-        h = {k: (pin(d[k]) if d[k] is not None else None) for k in ("offsets", "y", "x", "w")}
-        ho = {}
-        for k, v in fit.out.items():
-            ho[k] = torch.empty(v.shape, dtype=v.dtype).pin_memory()
-        hs = abi.B200FitOutputs()
-        for nm, ctype in abi.B200FitOutputs._fields_:
-            setattr(hs, nm, None if nm not in ho else C.cast(ho[nm].data_ptr(), ctype))
-        ptr = lambda tt: None if tt is None else tt.data_ptr()  # noqa: E731
-        e2e_steps = max(1, min(args.steps, 5))
-
-        def e2e_step():
-            pkg.fit_batch_host_into(ptr(h["offsets"]), ptr(h["y"]), ptr(h["x"]), ptr(h["w"]), hs, G, N, p, **opt)
-
-        e2e_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            e2e_step()
-        barrier()
-        dt = (time.perf_counter() - t0) / e2e_steps
-        tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dt = float(tt.item())
-        h2d = sum(v.numel() * v.element_size() for v in h.values() if v is not None)
-        d2h = sum(v.numel() * v.element_size() for v in ho.values())
-        same = bool(torch.equal(ho["status"], fit.out["status"].cpu()))
-        e2e = {"value": world * G / dt, "unit": "fits/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "ms_per_step": dt * 1e3, "steps": e2e_steps, "matches_device_path": same}
-
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-
-    peak, peak_src = measured_peak_gbs()
-    inp, outb = algorithmic_bytes(G, N, p, method, inference, predict)
-    acc_launch_ms = acc_ms / max(calls, 1)
-    acc_bytes = N * (8 * (p + 1) + (8 if method == "wls" else 0)) + 8 * (G + 1)
-    achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
-    path, lanes = pkg.plan(G, N, p, method == "wls", predict)
-    if path == "fused":
-        kname = "fit_small_kernel<%d> (rows -> transposed moment records, %d lanes per group, TMA-staged)" % (p, lanes)
-    else:
-        kname = "acc_ring_kernel (streaming ring of TMA windows, FP64 DMMA moment accumulation)"
-    # measured traffic of the same kernel from the committed ncu --set full capture (profiles/), per launch
-    traffic = {"C2": 2.74e9, "C3r": 28.9e9, "C5": 7.37e9}.get(args.workload)  # dram read + write, r01d_*_summary.txt
-    roofline = {"bound": "hbm", "kernel": kname,
-                "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": traffic,
-                "algorithmic_bytes_per_launch": acc_bytes, "avg_launch_ms": acc_launch_ms,
-                "solve_stage_ms": solve_ms / max(calls, 1), "solve_share_of_step": (solve_ms / max(calls, 1)) / ms_per_step,
-                "step_algorithmic_gbs": (inp + outb) / (ms_per_step * 1e-3) / 1e9}
-
-    cpu = None
-    if not args.no_cpu and world == 1:  # the CPU baseline leg runs at N = 1 only (task contract)
-        gs = min(G, 200_000)
-        host = {"offsets": d["offsets"][:gs + 1].cpu().numpy(), "y": d["y"][:gs * n].cpu().numpy(),
-                "x": d["x"][:gs * n].cpu().numpy(), "w": d["w"][:gs * n].cpu().numpy() if d["w"] is not None else None}
-        v, dt, used, threads = cpu_reference_run((gs, n, p, method, inference, extra), host, 3, 1, 0, budget_s=12.0)
-        cpu = {"value": v, "unit": "fits/s", "cores": threads, "kind": "port",
-               "sample": f"{used} groups x {n} rows per step, 3 steps (oracle f64 build, OpenMP over groups)"}
-
-    line = {"metric": "fits_per_sec", "value": value, "unit": "fits/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-            "rows_per_sec": value * n, "groups_fitted_ok": n_ok, "clocks": clocks, "e2e": e2e,
-            "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
-    emit(line)
+        line = {"metric": "fits_per_sec", "value": r["value"], "unit": "fits/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "rows_per_sec": r["rows_per_sec"], "groups_fitted_ok": r["groups_fitted_ok"], "clocks": r["clocks"],
+                "e2e": r["e2e"], "gpu_launches": r["gpu_launches"], "roofline": r["roofline"],
+                "cpu_baseline": r["cpu_baseline"], "device_counters": r["device_counters"],
+                "host_affinity": affinity, "secondary": secondary or None}
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

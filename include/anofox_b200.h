@@ -317,6 +317,29 @@ int32_t anofox_b200_solve_moments_device(const double *moments, const double *cd
                                          int32_t n_features, const AnofoxB200FitOptions *options,
                                          const AnofoxB200FitOutputs *out, void *stream, AnofoxError *err);
 
+/* Exact-residual refinement of the row-sharded path. R^2, the residual standard error and everything derived
+ * from them come from RSS = TSS - ESS of the moment block; for (nearly) exact fits that difference cancels, and
+ * the batched calls then recompute the residuals from the rows (refine_kernel). Across ranks the same takes one
+ * more tiny collective, with no host synchronisation anywhere:
+ *   a. anofox_b200_solve_moments_refine_device(..., needs_refine, rss_exact = NULL): first solve; sets
+ *      *needs_refine (device int32) to 1 when rss <= 1e-5 tss.
+ *   b. every rank: anofox_b200_shard_residual_device with the coefficients / intercept just written (device) and
+ *      run_if = needs_refine: its rows' sum w (y - b0 - x'b)^2 -> rss_partial (device f64; 0 when not flagged,
+ *      the kernel then returns at once).
+ *   c. ncclAllReduce(rss_partial, SUM).
+ *   d. anofox_b200_solve_moments_refine_device(..., needs_refine, rss_exact = reduced value): solves again with
+ *      the exact RSS when flagged, does nothing otherwise.
+ * A moment block carries no rows, so the QR fallback of the batched calls (ill-conditioned groups) is not
+ * available behind these entry points; hc_type must be NONE. */
+int32_t anofox_b200_solve_moments_refine_device(const double *moments, const double *cdev, const double *shift,
+                                                int32_t n_features, const AnofoxB200FitOptions *options,
+                                                const AnofoxB200FitOutputs *out, int32_t *needs_refine,
+                                                const double *rss_exact, void *stream, AnofoxError *err);
+int32_t anofox_b200_shard_residual_device(const double *y, const double *x, const double *w, int64_t n_rows,
+                                          int32_t n_features, const double *coefficients, const double *intercept,
+                                          const int32_t *run_if, double *rss_partial, void *workspace,
+                                          size_t workspace_bytes, void *stream, AnofoxError *err);
+
 /* Library / device probe: 0 when a CUDA device of compute capability 10.x is usable. */
 int32_t anofox_b200_device_check(AnofoxError *err);
 /* How many kernels this library has launched since load (bench.py's gpu_launches). */

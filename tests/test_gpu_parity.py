@@ -23,10 +23,11 @@ def lib(b200):
     return b200
 
 
-@pytest.fixture(params=["auto", "record", "fused", "stages"])
+@pytest.fixture(params=["auto", "record", "fused", "stages", "qr"])
 def path(request, lib):
-    """Both kernel paths: "auto" takes the fused small-group kernel where it applies (p <= 8, small groups),
-    "record" forces the DMMA accumulation kernel + solve kernel everywhere."""
+    """The kernel paths: "auto" takes the small-group kernels where they apply (p <= 8, small groups), "record"
+    forces the DMMA accumulation kernel + solve kernel everywhere, "fused" / "stages" are the A/B variants, and
+    "qr" is "auto" followed by the QR fallback kernel (csrc/qr.cuh) re-fitting EVERY group from its rows."""
     lib.force_path(request.param)
     yield request.param
     lib.force_path("auto")
@@ -311,7 +312,7 @@ CASES = [
 @pytest.mark.parametrize("method,p,icpt,inf,nr,G", CASES,
                          ids=[f"{c[0]}-p{c[1]}-{'i' if c[2] else 'noi'}-{'inf' if c[3] else 'core'}" for c in CASES])
 def test_batch_parity_vs_oracle(lib, oracle, path, method, p, icpt, inf, nr, G):
-    if path != "auto" and p > 8:
+    if path not in ("auto", "qr") and p > 8:
         pytest.skip("p > 8 always takes the record path")
     rng = np.random.default_rng(1000 + p * 7 + len(method))
     c = make_case(rng, G, nr[0], nr[1], p, dirty=True, weights=(method == "wls"))
@@ -648,6 +649,36 @@ def test_row_sharded_clean_shards(lib, oracle, p, N, method, const):
     dev2 = _fit_from_row_shards(lib, x, y, w, [0, N // 2, N], **opt)
     m = np.isfinite(dev["coefficients"])
     assert np.allclose(dev["coefficients"][m], dev2["coefficients"][m], rtol=1e-10, atol=0)
+
+
+def test_row_sharded_exact_fits_are_refined(lib, oracle):
+    """Row-sharded group whose fit is exact or nearly exact (R^2 = 1, 1 - 1e-9): RSS = TSS - ESS of the reduced
+    moment block cancels; the refine protocol (flag -> per-shard residual sums -> SUM -> second solve) must restore
+    r_squared, the residual standard error and every statistic derived from them."""
+    import torch
+    from importlib import import_module
+    D = import_module(lib.__name__ + ".distributed")
+    rng = np.random.default_rng(31)
+    for p, N, noise, method in [(6, 50_000, 0.0, "ols"), (64, 30_000, 1e-6, "ols"), (12, 40_000, 3e-5, "wls"), (5, 9_000, 0.0, "ridge")]:
+        x = rng.normal(size=(N, p)) * 3.0 + 1.0
+        beta = rng.uniform(-2, 2, size=p)
+        y = 0.75 + x @ beta + noise * rng.normal(size=N)
+        w = rng.uniform(0.5, 1.5, size=N) if method == "wls" else None
+        f = D.ShardedSingleGroupFit(N, p, inference=True)
+        t = lambda v: None if v is None else torch.tensor(v, device="cuda")  # noqa: E731
+        opt = dict(method=method, compute_inference=True, alpha=1e-9 if method == "ridge" else 0.0)
+        out = f.fit(t(y), t(x), t(w), **opt)
+        torch.cuda.synchronize()
+        assert int(f.flag[0]) == 1, (p, noise)
+        dev = {k: v.cpu().numpy() for k, v in out.items()}
+        ora = oracle.fit_batch(np.array([0, N], dtype=np.int64), y, x, w, **opt)
+        assert abs(dev["r_squared"][0] - ora["r_squared"][0]) < 1e-13
+        if noise > 0:
+            assert_fit_parity(dev, ora, rtol=1e-7, inference=True, check_ic=False, label=f"sharded exact p={p} noise={noise}")
+        else:
+            # pure rounding-level residuals: only their size is determined
+            assert dev["residual_std_error"][0] < 1e-10 * np.abs(y).max()
+            assert np.allclose(dev["coefficients"][0], ora["coefficients"][0], rtol=1e-9, atol=1e-12)
 
 
 def test_sharded_single_group_fit_class(lib, oracle):
