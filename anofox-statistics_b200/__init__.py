@@ -89,7 +89,7 @@ def load_library():
     lib.anofox_b200_shard_residual_device.restype = C.c_int32
     lib.anofox_b200_shard_residual_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                                      C.c_size_t, C.c_void_p, E]
+                                                      C.c_void_p, C.c_size_t, C.c_void_p, E]
     lib.anofox_b200_device_check.restype = C.c_int32
     lib.anofox_b200_device_check.argtypes = [E]
     lib.anofox_b200_launch_count.restype = C.c_int64

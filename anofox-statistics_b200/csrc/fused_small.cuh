@@ -227,18 +227,23 @@ __device__ __forceinline__ double small_exact_cdev(const SmallGroupView &v, int 
 }
 
 // sum w (y - b0 - x'beta)^2 over the valid rows with the coefficients just computed (NaN = aliased:
-// contributes nothing, lib.rs:2296-2303).
+// contributes nothing, lib.rs:2296-2303). With an intercept (shifted = true) the residual is evaluated about the
+// shift row: e = (y - sh_y) - b0s - sum beta (x - sh), every term of the size of the data's variation.
 template <int P, bool HASW, bool HAST>
 __device__ __forceinline__ double small_exact_rss(const SmallGroupView &v, const double (&beta)[P], unsigned live,
-                                                  double b0) {
+                                                  double b0s, const double (&sh)[P + 1], bool shifted) {
 	double rss = 0.0;
 	for (int i = v.q; i < v.n; i += v.T) {
 		if (!small_row_valid_full<P, HASW, HAST>(v, i)) continue;
-		double fit = b0;
+		double fit = b0s;
 #pragma unroll
 		for (int c = 0; c < P; ++c)
-			if ((live >> c) & 1u) fit = fma(beta[c], lds_f64(v.sg.x + (uint32_t)(i * P + c) * 8u), fit);
-		const double e = lds_f64(v.sg.y + (uint32_t)i * 8u) - fit;
+			if ((live >> c) & 1u) {
+				const double xv = lds_f64(v.sg.x + (uint32_t)(i * P + c) * 8u);
+				fit = fma(beta[c], shifted ? xv - sh[c] : xv, fit);
+			}
+		const double yv = lds_f64(v.sg.y + (uint32_t)i * 8u);
+		const double e = (shifted ? yv - sh[P] : yv) - fit;
 		const double wv = HASW ? lds_f64(v.sg.w + (uint32_t)i * 8u) : 1.0;
 		rss = fma(wv * e, e, rss);
 	}
@@ -412,7 +417,14 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 	if (!(rss > 1e-5 * tss)) {
 		// tss - ess keeps ~16 - log10(tss/rss) digits: take the residuals from the rows themselves
 		if (ROWS) {
-			rss = small_exact_rss<P, HASW, HAST>(v, b, live, ic ? b0 : 0.0);
+			double b0s = 0.0; // intercept in the shifted frame: (S1_y - sum beta S1_j) / sum w
+			if (ic) {
+				b0s = s1y;
+#pragma unroll
+				for (int i = 0; i < P; ++i) b0s -= b[i] * M.s1[i];
+				b0s *= inv_sw;
+			}
+			rss = small_exact_rss<P, HASW, HAST>(v, b, live, b0s, sh, ic != 0);
 		} else if (v.refine_count) {
 			const int slot = atomicAdd(v.refine_count, 1);
 			v.refine_list[slot] = g;
@@ -470,6 +482,43 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		const int idf = (int)dfr;
 		tcrit = (Pm.tcrit && idf <= kTcritTable) ? Pm.tcrit[idf] : t_critical_dev(Pm.level, dfr);
 	}
+	if (!ROWS) {
+		// thread-per-group (solve_small_kernel): the P t tests and the F test share dfr, so their incomplete-beta
+		// tails are evaluated together (pvalues_same_df, specfun.cuh): P + 1 independent Horner chains per
+		// coefficient load instead of P + 1 dependent ones in sequence
+		double t2[P];
+#pragma unroll
+		for (int j = 0; j < P; ++j) {
+			const int64_t oj = g * P + j;
+			if ((live >> j) & 1u) {
+				const double se = sqrt(sigma2 * vdiag[j]);
+				const double t = b[j] / se;
+				o.coefficients[oj] = b[j];
+				o.std_errors[oj] = se;
+				o.t_values[oj] = t;
+				o.ci_lower[oj] = b[j] - tcrit * se;
+				o.ci_upper[oj] = b[j] + tcrit * se;
+				t2[j] = t * t;
+			} else {
+				o.coefficients[oj] = nanv;
+				o.std_errors[oj] = nanv;
+				o.t_values[oj] = nanv;
+				o.ci_lower[oj] = nanv;
+				o.ci_upper[oj] = nanv;
+				t2[j] = nanv;
+			}
+		}
+		double fs = nanv;
+		if (dfm > 0.0 && dfr > 0.0) fs = ((tss - rss) / dfm) / sigma2;
+		double pt[P], pf;
+		pvalues_same_df<P>(t2, live, fs, dfm, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co}, pt, pf);
+#pragma unroll
+		for (int j = 0; j < P; ++j) o.p_values[g * P + j] = ((live >> j) & 1u) ? pt[j] : nanv;
+		o.f_statistic[g] = fs;
+		o.f_pvalue[g] = pf;
+		if (o.has_inference) o.has_inference[g] = 1;
+		return;
+	}
 	// ... then lane q takes coefficients q, q+T, ...: the same instruction stream on different data.
 	// The p-values themselves (the expensive part) are evaluated after the round by all 32 lanes of the
 	// warp from the statistics deposited in v.pv: t^2 per coefficient and the F statistic.
@@ -492,20 +541,14 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 				o.t_values[oj] = t;
 				o.ci_lower[oj] = bj - tcrit * se;
 				o.ci_upper[oj] = bj + tcrit * se;
-				if (ROWS)
-					v.pv[j] = t * t;
-				else
-					o.p_values[oj] = pvalue_f(t * t, 1.0, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
+				v.pv[j] = t * t;
 			} else {
 				o.coefficients[oj] = nanv;
 				o.std_errors[oj] = nanv;
 				o.t_values[oj] = nanv;
 				o.ci_lower[oj] = nanv;
 				o.ci_upper[oj] = nanv;
-				if (ROWS)
-					v.pv[j] = nanv;
-				else
-					o.p_values[oj] = nanv;
+				v.pv[j] = nanv;
 			}
 		}
 	}
@@ -514,13 +557,9 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		if (dfm > 0.0 && dfr > 0.0) fs = ((tss - rss) / dfm) / sigma2;
 		o.f_statistic[g] = fs;
 		if (o.has_inference) o.has_inference[g] = 1;
-		if (ROWS) {
-			v.pv[P] = fs;
-			v.pv[P + 1] = dfm; // > 0 marks "p-values wanted" for this slot
-			v.pv[P + 2] = dfr;
-		} else {
-			o.f_pvalue[g] = pvalue_f(fs, dfm, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
-		}
+		v.pv[P] = fs;
+		v.pv[P + 1] = dfm; // > 0 marks "p-values wanted" for this slot
+		v.pv[P + 2] = dfr;
 	}
 }
 

@@ -107,8 +107,23 @@ __global__ void __launch_bounds__(256) refine_kernel(RefineArgs a, FitParams P, 
 		const int64_t g = a.refine_list[q];
 		const int64_t r0 = a.offsets[g], r1 = a.offsets[g + 1];
 		const double icpt = o.intercept[g];
-		const double b0 = isnan(icpt) ? 0.0 : icpt;
+		const bool ic = !isnan(icpt);
 		const double *coef = o.coefficients + g * p;
+		// With an intercept the residuals are evaluated about the group's shift row (the record's origin):
+		// e = (y - sh_y) - b0' - sum beta (x - sh), b0' = (S1_y - sum beta S1_j) / sum w. Every term then has the
+		// size of the data's variation instead of its offset.
+		const double *rec = a.records + g * a.rec_gs;
+		const double *shf = rec + (int64_t)rec_off_shift(p) * a.rec_es, *s1 = rec + (int64_t)rec_off_s1(p) * a.rec_es;
+		double b0 = 0.0, shy = 0.0;
+		if (ic) {
+			shy = shf[(int64_t)p * a.rec_es];
+			double t = s1[(int64_t)p * a.rec_es];
+			for (int j = 0; j < p; ++j) {
+				const double c = coef[j];
+				if (!isnan(c)) t -= c * s1[(int64_t)j * a.rec_es];
+			}
+			b0 = t / rec[a.rec_es];
+		}
 		double rss = 0.0;
 		for (int64_t r = r0 + lane; r < r1; r += 32) {
 			const double yv = a.y[r];
@@ -119,10 +134,10 @@ __global__ void __launch_bounds__(256) refine_kernel(RefineArgs a, FitParams P, 
 				const double xv = a.x[r * p + j];
 				ok = ok && finite_f64(xv);
 				const double c = coef[j];
-				if (!isnan(c)) fit = fma(c, xv, fit);
+				if (!isnan(c)) fit = fma(c, ic ? xv - shf[(int64_t)j * a.rec_es] : xv, fit);
 			}
 			if (ok) {
-				const double e = yv - fit;
+				const double e = (yv - shy) - fit;
 				rss = fma(wv * e, e, rss);
 			}
 		}
@@ -377,27 +392,40 @@ __global__ void split_record_kernel(const double *__restrict__ rec, int p, doubl
 __global__ void __launch_bounds__(256) shard_residual_kernel(const double *__restrict__ y, const double *__restrict__ x,
                                                              const double *__restrict__ w, int64_t n_rows, int p,
                                                              const double *__restrict__ coef, const double *__restrict__ icpt,
-                                                             const int *__restrict__ run_if, double *__restrict__ partials) {
+                                                             const double *__restrict__ shift, const int *__restrict__ run_if,
+                                                             double *__restrict__ partials) {
 	__shared__ double red[8];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	double acc = 0.0;
 	if (*run_if != 0) {
 		double b0 = icpt[0];
-		if (isnan(b0)) b0 = 0.0;
+		const bool ic = !isnan(b0);
+		if (!ic) b0 = 0.0;
 		double c0 = lane < p ? coef[lane] : 0.0, c1 = lane + 32 < p ? coef[lane + 32] : 0.0;
 		if (isnan(c0)) c0 = 0.0;
 		if (isnan(c1)) c1 = 0.0;
+		// residuals about the common shift row when an intercept is fitted (see refine_kernel): the constant
+		// b0 - sh_y + sum beta sh is formed once, its rounding is common to all rows
+		const bool sf = ic && shift != nullptr;
+		const double sh0 = (sf && lane < p) ? shift[lane] : 0.0, sh1 = (sf && lane + 32 < p) ? shift[lane + 32] : 0.0;
+		const double shy = sf ? shift[p] : 0.0;
+		if (sf) {
+			double t = fma(c0, sh0, c1 * sh1);
+#pragma unroll
+			for (int off = 16; off; off >>= 1) t += __shfl_xor_sync(0xffffffffu, t, off);
+			b0 = (b0 - shy) + t;
+		}
 		const int64_t nw = (int64_t)gridDim.x * 8;
 		for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < n_rows; r += nw) {
 			const double x0 = lane < p ? x[r * p + lane] : 0.0, x1 = lane + 32 < p ? x[r * p + lane + 32] : 0.0;
 			const double yv = y[r], wv = w ? w[r] : 1.0;
 			const bool bad = !finite_f64(x0) || !finite_f64(x1);
 			const bool ok = row_ok_yw(yv, wv, 1, w != nullptr) && !__any_sync(0xffffffffu, bad);
-			double dot = fma(c0, x0, c1 * x1);
+			double dot = fma(c0, x0 - sh0, c1 * (x1 - sh1));
 #pragma unroll
 			for (int off = 16; off; off >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, off);
 			if (ok) {
-				const double e = yv - (b0 + dot);
+				const double e = (yv - shy) - (b0 + dot);
 				acc = fma(wv * e, e, acc);
 			}
 		}
@@ -940,8 +968,7 @@ static int cuda_fail(AnofoxError *err, cudaError_t e, const char *where) {
 struct TableEntry {
 	int device;
 	double level;
-	double *buf; // [tcrit | gratio | rcp]
-	cudaEvent_t ready;
+	double *buf; // [tcrit | gratio | rcp | ce | co]
 };
 struct TableCache {
 	std::mutex mu;
@@ -951,48 +978,52 @@ static TableCache &table_cache() {
 	static TableCache c;
 	return c;
 }
-// Returns the tables for `level` on the current device; work on `st` is ordered after their fill.
-static int get_tables(double level, cudaStream_t st, DfTables &T, AnofoxError *err) {
+// Returns the tables for `level` on the current device. A new (device, level) pair is filled on a private stream
+// and waited for on the host, once per process: afterwards a call adds no dependency to the caller's stream at
+// all (so that batched calls can be captured in a CUDA graph).
+static int get_tables(double level, cudaStream_t, DfTables &T, AnofoxError *err) {
 	TableCache &c = table_cache();
 	std::lock_guard<std::mutex> lock(c.mu);
 	int dev = 0;
 	cudaGetDevice(&dev);
 	const size_t n1 = kTcritTable + 1, n3 = kRcpTable + 1, n4 = kSeriesTable;
+	auto point = [&](double *buf) {
+		T.tcrit = buf;
+		T.gratio = buf + n1;
+		T.rcp = buf + 2 * n1;
+		T.ce = buf + 2 * n1 + n3;
+		T.co = buf + 2 * n1 + n3 + n4;
+	};
 	for (auto &e : c.entries)
 		if (e.device == dev && (e.level == level || (std::isnan(e.level) && std::isnan(level)))) {
-			CU(cudaStreamWaitEvent(st, e.ready, 0), "cudaStreamWaitEvent");
-			T.tcrit = e.buf;
-			T.gratio = e.buf + n1;
-			T.rcp = e.buf + 2 * n1;
-			T.ce = e.buf + 2 * n1 + n3;
-			T.co = e.buf + 2 * n1 + n3 + n4;
+			point(e.buf);
 			return 0;
 		}
-	if (c.entries.size() >= 64) { // unbounded growth guard: drop everything (after the device drains)
-		cudaDeviceSynchronize();
-		for (auto &e : c.entries) {
-			cudaFree(e.buf);
-			cudaEventDestroy(e.ready);
-		}
-		c.entries.clear();
+	// unbounded growth guard: the cache keeps at most 64 levels per process; beyond that the oldest tables stay
+	// allocated (a running kernel may still read them) and new levels are evaluated directly (T stays null)
+	if (c.entries.size() >= 64) {
+		T.tcrit = T.gratio = T.rcp = T.ce = T.co = nullptr;
+		return 0;
 	}
 	TableEntry e;
 	e.device = dev;
 	e.level = level;
 	e.buf = nullptr;
 	CU(cudaMalloc(&e.buf, (2 * n1 + n3 + 2 * n4) * sizeof(double)), "cudaMalloc tables");
-	CU(cudaEventCreateWithFlags(&e.ready, cudaEventDisableTiming), "cudaEventCreate");
-	df_tables_kernel<<<(unsigned)((n3 + 127) / 128), 128, 0, st>>>(level, e.buf, e.buf + n1, e.buf + 2 * n1,
+	cudaStream_t ts = nullptr;
+	CU(cudaStreamCreateWithFlags(&ts, cudaStreamNonBlocking), "cudaStreamCreate");
+	df_tables_kernel<<<(unsigned)((n3 + 127) / 128), 128, 0, ts>>>(level, e.buf, e.buf + n1, e.buf + 2 * n1,
 	                                                                e.buf + 2 * n1 + n3, e.buf + 2 * n1 + n3 + n4);
 	LAUNCHED();
-	CU(cudaGetLastError(), "df_tables_kernel");
-	CU(cudaEventRecord(e.ready, st), "cudaEventRecord");
+	cudaError_t ke = cudaGetLastError();
+	if (ke == cudaSuccess) ke = cudaStreamSynchronize(ts);
+	cudaStreamDestroy(ts);
+	if (ke != cudaSuccess) {
+		cudaFree(e.buf);
+		return cuda_fail(err, ke, "df_tables_kernel");
+	}
 	c.entries.push_back(e);
-	T.tcrit = e.buf;
-	T.gratio = e.buf + n1;
-	T.rcp = e.buf + 2 * n1;
-	T.ce = e.buf + 2 * n1 + n3;
-	T.co = e.buf + 2 * n1 + n3 + n4;
+	point(e.buf);
 	return 0;
 }
 
@@ -2357,8 +2388,8 @@ int32_t anofox_b200_solve_moments_refine_device(const double *moments, const dou
 
 int32_t anofox_b200_shard_residual_device(const double *y, const double *x, const double *w, int64_t n_rows,
                                           int32_t n_features, const double *coefficients, const double *intercept,
-                                          const int32_t *run_if, double *rss_partial, void *workspace,
-                                          size_t workspace_bytes, void *stream, AnofoxError *err) {
+                                          const double *shift, const int32_t *run_if, double *rss_partial,
+                                          void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err) {
 	clear_error(err);
 	DeviceInfo &di = device_info();
 	if (!di.ok) {
@@ -2379,7 +2410,7 @@ int32_t anofox_b200_shard_residual_device(const double *y, const double *x, cons
 	}
 	cudaStream_t st = (cudaStream_t)stream;
 	const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)di.sms * 8, (n_rows + 7) / 8));
-	shard_residual_kernel<<<blocks, 256, 0, st>>>(y, x, w, n_rows, p, coefficients, intercept, run_if, ws.partials);
+	shard_residual_kernel<<<blocks, 256, 0, st>>>(y, x, w, n_rows, p, coefficients, intercept, shift, run_if, ws.partials);
 	LAUNCHED();
 	CU(cudaGetLastError(), "shard_residual_kernel");
 	shard_residual_sum_kernel<<<1, 32, 0, st>>>(ws.partials, blocks, rss_partial);

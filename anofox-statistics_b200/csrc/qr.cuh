@@ -445,20 +445,25 @@ static __global__ void __launch_bounds__(kQrThreads) qr_fit_kernel(const QrArgs 
 			}
 		}
 		// ---------------- pass 3: residuals from the rows -------------------------------------------------------
+		// evaluated in the shifted frame when an intercept is fitted: e = (y - shy) - b0' - sum beta (x - sh). The
+		// terms then have the size of the data's variation, not of its offset, so a residual of 1e-6 next to values
+		// of 1e6 keeps its digits.
 		double rss;
 		{
 			const int m0 = lane < p ? S.colmap[lane] : -1, m1 = lane + 32 < p ? S.colmap[lane + 32] : -1;
 			double be0 = m0 >= 0 ? S.sol[m0] : nanv, be1 = m1 >= 0 ? S.sol[m1] : nanv;
 			if (isnan(be0)) be0 = 0.0; // aliased / constant: contributes nothing (lib.rs:2296-2303)
 			if (isnan(be1)) be1 = 0.0;
+			const double sh0 = (ic && lane < p) ? S.shift[lane] : 0.0, sh1 = (ic && lane + 32 < p) ? S.shift[lane + 32] : 0.0;
+			const double shy = ic ? S.shift[p] : 0.0, b0s = ic ? S.sol[0] : 0.0;
 			double acc = 0.0;
 			for (int64_t r = r0 + warp; r < r1; r += kQrWarps) {
 				double x0, x1, yv, wv;
 				bool valid, counted;
 				qr_row_load(a, p, r, lane, x0, x1, yv, wv, valid, counted);
 				if (valid) { // warp-uniform
-					const double dot = qr_warp_sum(fma(be0, x0, be1 * x1));
-					const double e = yv - (b0 + dot);
+					const double dot = qr_warp_sum(fma(be0, x0 - sh0, be1 * (x1 - sh1)));
+					const double e = (yv - shy) - (b0s + dot);
 					acc = fma((has_w ? wv : 1.0) * e, e, acc);
 				}
 			}

@@ -82,13 +82,13 @@ class CudaBackend:
                                                                   C.byref(err))
         self._check(rc, err)
 
-    def residual(self, y, x, w, coefficients, intercept, flag):
+    def residual(self, y, x, w, coefficients, intercept, shift, flag):
         """This shard's sum w (y - b0 - x'b)^2 (device f64[1]); zero, at no cost, when flag[0] == 0."""
         out = self.torch.zeros(1, dtype=self.torch.float64, device=self.device)
         err = abi.AnofoxError()
         rc = self.lib.anofox_b200_shard_residual_device(self._p(y), self._p(x), self._p(w), y.numel(), self.p,
-                                                        self._p(coefficients), self._p(intercept), self._p(flag),
-                                                        self._p(out), C.c_void_p(self.ws_ptr), self.ws_bytes,
+                                                        self._p(coefficients), self._p(intercept), self._p(shift),
+                                                        self._p(flag), self._p(out), C.c_void_p(self.ws_ptr), self.ws_bytes,
                                                         self._stream(), C.byref(err))
         self._check(rc, err)
         return out
@@ -141,7 +141,7 @@ class ShardedSingleGroupFit:
         out = self.fit_out.out
         self.backend.solve(m, cd, shift, o, self.fit_out.out_struct, flag=self.flag)
         # exact-fit guard (no host read of the flag: the kernels look at it themselves)
-        rss = self.backend.residual(y, x, w, out["coefficients"], out["intercept"], self.flag)
+        rss = self.backend.residual(y, x, w, out["coefficients"], out["intercept"], shift, self.flag)
         dist = self.dist
         if dist is not None and dist.is_initialized() and dist.get_world_size(self.group) > 1:
             dist.all_reduce(rss, op=dist.ReduceOp.SUM, group=self.group)

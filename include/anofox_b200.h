@@ -324,7 +324,7 @@ int32_t anofox_b200_solve_moments_device(const double *moments, const double *cd
  *   a. anofox_b200_solve_moments_refine_device(..., needs_refine, rss_exact = NULL): first solve; sets
  *      *needs_refine (device int32) to 1 when rss <= 1e-5 tss.
  *   b. every rank: anofox_b200_shard_residual_device with the coefficients / intercept just written (device) and
- *      run_if = needs_refine: its rows' sum w (y - b0 - x'b)^2 -> rss_partial (device f64; 0 when not flagged,
+ *      run_if = needs_refine: its rows' sum w (y - b0 - x'b)^2 (evaluated about `shift`) -> rss_partial (device f64; 0 when not flagged,
  *      the kernel then returns at once).
  *   c. ncclAllReduce(rss_partial, SUM).
  *   d. anofox_b200_solve_moments_refine_device(..., needs_refine, rss_exact = reduced value): solves again with
@@ -337,6 +337,7 @@ int32_t anofox_b200_solve_moments_refine_device(const double *moments, const dou
                                                 const double *rss_exact, void *stream, AnofoxError *err);
 int32_t anofox_b200_shard_residual_device(const double *y, const double *x, const double *w, int64_t n_rows,
                                           int32_t n_features, const double *coefficients, const double *intercept,
+                                          const double *shift /* the common shift row [p+1], may be NULL */,
                                           const int32_t *run_if, double *rss_partial, void *workspace,
                                           size_t workspace_bytes, void *stream, AnofoxError *err);
 

@@ -202,16 +202,17 @@ void info_criteria(double rss, size_t n, size_t k, double &aic, double &bic) {
 // Householder QR with LINPACK-dqrdc2 style limited pivoting on A (rows x m, column-major in `a`),
 // right-hand side b. On return: perm = column order, rank, R in the upper triangle of the permuted
 // columns, b overwritten with Q^T b. tol < 0 disables pivoting (ridge).
+// orig_given: the reference norms of the negligibility test when the columns of `a` are not the original ones.
 template <class R>
 void qr_limited(std::vector<R> &a, std::vector<R> &b, size_t rows, size_t m, R tol, std::vector<size_t> &perm,
-                size_t &rank) {
+                size_t &rank, const std::vector<R> *orig_given = nullptr) {
 	perm.resize(m);
 	for (size_t j = 0; j < m; ++j) perm[j] = j;
 	std::vector<R> orig(m);
 	for (size_t j = 0; j < m; ++j) {
 		R s = 0;
 		for (size_t i = 0; i < rows; ++i) s += a[j * rows + i] * a[j * rows + i];
-		orig[j] = std::sqrt(s);
+		orig[j] = orig_given ? (*orig_given)[j] : std::sqrt(s);
 		if (orig[j] == 0) orig[j] = 1;
 	}
 	size_t lup = m, l = 0;
@@ -387,6 +388,10 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 	std::vector<bool> aliased(pe, false);
 	R b0 = ic ? ybar : (R)0;
 	size_t rank_total; // estimated parameters incl. intercept
+	// frame the residuals are evaluated in: e = (y - cy) - b0c - sum beta (x - cx). With an intercept the centre is
+	// the origin the factorisation used, so that a residual of 1e-6 next to features of 1e6 keeps its digits.
+	std::vector<R> cx(pe, 0);
+	R cy = 0, b0c = 0;
 
 	if (lambda > 0.0) {
 		// Ridge (guides/02_technical_guide.md:129-138; validation/r_seesion_output.txt:668-671):
@@ -428,20 +433,40 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 		if (ic) {
 			b0 = ybar;
 			for (size_t c = 0; c < pe; ++c) b0 -= xbar[c] * beta[c];
+			cx = xbar;
+			cy = ybar;
+			b0c = 0;
 		}
 		rank_total = pe + ic;
 	} else {
 		// OLS / WLS: design [sqrt(w) | sqrt(w) x], dqrdc2 limited pivoting, tol 1e-7 (R lm.fit).
+		// With an intercept the feature columns and y enter the factorisation minus the first valid row (a shift lies
+		// in the span of the intercept column: same fit, same remaining norms) -- the working precision is then spent
+		// on the variation of the data instead of on a common offset. dqrdc2's reference norms stay those of the
+		// ORIGINAL columns, so the aliasing rule is the one lm.fit applies to the raw design.
 		size_t m = pe + ic;
-		std::vector<R> a(nv * m), b(nv);
-		for (size_t k = 0; k < nv; ++k) {
-			if (ic) a[k] = sqw[k];
-			for (size_t c = 0; c < pe; ++c) a[(c + ic) * nv + k] = sqw[k] * (R)d.X(valid[k], keep[c]);
-			b[k] = sqw[k] * (R)d.Y(valid[k]);
+		std::vector<R> a(nv * m), b(nv), shiftx(pe, 0), orig_norm(m, 0);
+		R shifty = 0;
+		if (ic) {
+			for (size_t c = 0; c < pe; ++c) shiftx[c] = (R)d.X(valid[0], keep[c]);
+			shifty = (R)d.Y(valid[0]);
 		}
+		for (size_t k = 0; k < nv; ++k) {
+			if (ic) {
+				a[k] = sqw[k];
+				orig_norm[0] += sqw[k] * sqw[k];
+			}
+			for (size_t c = 0; c < pe; ++c) {
+				R xv = (R)d.X(valid[k], keep[c]);
+				a[(c + ic) * nv + k] = sqw[k] * (xv - shiftx[c]);
+				orig_norm[c + ic] += (sqw[k] * xv) * (sqw[k] * xv);
+			}
+			b[k] = sqw[k] * ((R)d.Y(valid[k]) - shifty);
+		}
+		for (size_t j = 0; j < m; ++j) orig_norm[j] = std::sqrt(orig_norm[j]);
 		std::vector<size_t> perm;
 		size_t rank;
-		qr_limited<R>(a, b, nv, m, (R)1e-7, perm, rank);
+		qr_limited<R>(a, b, nv, m, (R)1e-7, perm, rank, &orig_norm);
 		std::vector<R> sol(m, std::numeric_limits<R>::quiet_NaN());
 		for (size_t q = rank; q-- > 0;) {
 			R s = b[q];
@@ -463,6 +488,16 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 			for (size_t c = r; c < rank; ++c) s += rinv[c * rank + r] * rinv[c * rank + r];
 			vd[perm[r]] = s;
 		}
+		if (ic) {
+			cx = shiftx;
+			cy = shifty;
+			b0c = sol[0];
+			// back on the unshifted scale: y - shifty = b0' + sum beta (x - shiftx)
+			R acc = sol[0] + shifty;
+			for (size_t c = 0; c < pe; ++c)
+				if (!std::isnan((double)sol[c + ic])) acc -= sol[c + ic] * shiftx[c];
+			sol[0] = acc;
+		}
 		if (ic) b0 = sol[0]; // the intercept column is never negligible
 		for (size_t c = 0; c < pe; ++c) {
 			beta[c] = sol[c + ic];
@@ -475,10 +510,10 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 	// Residuals from the raw rows (NaN coefficients contribute nothing)
 	R rss = 0;
 	for (size_t k = 0; k < nv; ++k) {
-		R fit = ic ? b0 : (R)0;
+		R fit = b0c;
 		for (size_t c = 0; c < pe; ++c)
-			if (!aliased[c]) fit += beta[c] * (R)d.X(valid[k], keep[c]);
-		R e = (R)d.Y(valid[k]) - fit;
+			if (!aliased[c]) fit += beta[c] * ((R)d.X(valid[k], keep[c]) - cx[c]);
+		R e = ((R)d.Y(valid[k]) - cy) - fit;
 		rss += sqw[k] * sqw[k] * e * e;
 	}
 

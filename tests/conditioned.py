@@ -57,19 +57,40 @@ def make_conditioned(rng, kind, level, G, n, p, noise=2.0, weights=False):
 
 
 def group_tolerances(c, ora, fit_intercept=True, floor=1e-9):
-    """Per-group tolerance max(floor, COND_C eps kappa_LS) from the data and the ORACLE's aliasing pattern."""
+    """Per-group tolerances from the data and the ORACLE's aliasing pattern -> dict for assert_fit_parity:
+    rtol       max(floor, COND_C eps kappa_LS)                                      (parity.conditioned_tolerance)
+    coef_scale largest |slope| of the group: slope errors are NOT measured against a large intercept
+    icpt_scale max(|b0|, largest |slope|, |ybar| + sum |xbar_j beta_j|): the intercept is the difference
+               ybar - sum xbar_j beta_j, and no f64 implementation resolves it below eps times those terms
+    rse_rtol   16 eps M / rse, M = largest per-row sum of |terms| of the (shifted) fitted value: the rounding floor
+               of the residuals themselves, which dominates for near-exact fits
+    """
+    from parity import EPS
     G = len(c["offsets"]) - 1
     tol = np.full(G, floor)
     kap = np.ones(G)
+    cs, isc, rr = np.ones(G), np.ones(G), np.zeros(G)
     for g in range(G):
         if ora["status"][g] != 0:
             continue
         a, b = c["offsets"][g], c["offsets"][g + 1]
-        live = np.isfinite(ora["coefficients"][g])
+        beta = ora["coefficients"][g]
+        live = np.isfinite(beta)
+        x, y = c["x"][a:b], c["y"][a:b]
+        w = None if c["w"] is None else c["w"][a:b]
+        bl = np.where(live, beta, 0.0)
+        cs[g] = max(np.abs(bl).max(), 1e-300)
+        ww = np.ones(len(y)) if w is None else w
+        xbar, ybar = (ww[:, None] * x).sum(0) / ww.sum(), (ww * y).sum() / ww.sum()
+        b0 = ora["intercept"][g]
+        isc[g] = max(abs(b0) if np.isfinite(b0) else 0.0, cs[g], abs(ybar) + np.abs(xbar * bl).sum())
+        xs, ys = (x - x[0], y - y[0]) if fit_intercept else (x, y)
+        M = (np.abs(ys) + np.abs(xs * bl).sum(1)).max()
+        rse = ora["residual_std_error"][g]
+        rr[g] = 16 * EPS * M / rse if np.isfinite(rse) and rse > 0 else 0.0
         if not live.any():
             continue
-        k, tn = ls_condition(c["x"][a:b], c["y"][a:b], None if c["w"] is None else c["w"][a:b], live, fit_intercept,
-                             ora["r_squared"][g])
+        k, tn = ls_condition(x, y, w, live, fit_intercept, ora["r_squared"][g])
         kap[g] = k
         tol[g] = conditioned_tolerance(k, tn, floor)
-    return tol, kap
+    return dict(rtol=tol, coef_scale=cs, icpt_scale=isc, rse_rtol=rr), kap

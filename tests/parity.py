@@ -51,12 +51,17 @@ def conditioned_tolerance(kappa, tan_theta, floor=1e-9):
     return max(floor, COND_C * EPS * (kappa + kappa * kappa * tan_theta))
 
 
-def assert_fit_parity(dev, ora, rtol=1e-9, inference=False, ptol=1e-8, check_ic=True, label=""):
+def assert_fit_parity(dev, ora, rtol=1e-9, inference=False, ptol=1e-8, check_ic=True, label="", coef_scale=None,
+                      icpt_scale=None, rse_rtol=None):
     """Device result dict vs oracle result dict (same SoA layout).
 
     Bit-exact: status (NULL-struct pattern), n_observations, NaN positions of every array.
     Relative tolerance rtol (north star: 1e-9 for well-conditioned f64) on values; p-values relative ptol.
     rtol may be an array with one tolerance per group (conditioned suites: conditioned_tolerance above).
+    coef_scale / icpt_scale [G]: the magnitudes the slope and intercept errors are taken relative to (default: the
+    group's largest |coefficient| incl. the intercept); rse_rtol [G]: relative tolerance of the residual standard
+    error and of what is proportional to it (SE, t, F) where the rounding floor of the residuals themselves --
+    eps * |terms of the fitted value| / |residual| -- exceeds rtol (near-exact fits).
     """
     G = len(ora["status"])
     rt = np.broadcast_to(np.asarray(rtol, dtype=np.float64), (G,))
@@ -81,10 +86,14 @@ def assert_fit_parity(dev, ora, rtol=1e-9, inference=False, ptol=1e-8, check_ic=
     c_dev, c_ora = dev["coefficients"], ora["coefficients"]
     scale = np.nanmax(np.abs(np.concatenate([c_ora, ora["intercept"][:, None]], axis=1)), axis=1, initial=0.0)
     scale = np.where(scale > 0, scale, 1.0)[:, None]
+    cs = scale if coef_scale is None else np.asarray(coef_scale, dtype=np.float64)[:, None]
+    isc = scale[:, 0] if icpt_scale is None else np.asarray(icpt_scale, dtype=np.float64)
+    rr = rt if rse_rtol is None else np.maximum(rt, np.asarray(rse_rtol, dtype=np.float64))
+    rr2 = rr[:, None]
     with np.errstate(invalid="ignore"):
-        q, i = worst(np.abs(c_dev - c_ora) / scale, rt2, np.isfinite(c_ora))
+        q, i = worst(np.abs(c_dev - c_ora) / cs, rt2, np.isfinite(c_ora))
         assert q <= 1.0, (label, "coefficients", q, "x tol at", i)
-        q, i = worst(np.abs(dev["intercept"] - ora["intercept"]) / scale[:, 0], rt, np.isfinite(ora["intercept"]))
+        q, i = worst(np.abs(dev["intercept"] - ora["intercept"]) / isc, rt, np.isfinite(ora["intercept"]))
         assert q <= 1.0, (label, "intercept", q, "x tol at group", i)
         for k in ["r_squared", "adj_r_squared"]:
             q, i = worst(np.abs(dev[k] - ora[k]), rt, np.isfinite(ora[k]))
@@ -92,7 +101,7 @@ def assert_fit_parity(dev, ora, rtol=1e-9, inference=False, ptol=1e-8, check_ic=
         b = ora["residual_std_error"]
         m = np.isfinite(b) & np.isfinite(dev["residual_std_error"])
         sc = max(np.abs(b[m]).max(), 1e-300) if m.any() else 1.0
-        q, i = worst(np.abs(dev["residual_std_error"] - b) / np.maximum(np.abs(b), 1e-12 * sc + 1e-300), rt, m)
+        q, i = worst(np.abs(dev["residual_std_error"] - b) / np.maximum(np.abs(b), 1e-12 * sc + 1e-300), rr, m)
         assert q <= 1.0, (label, "residual_std_error", q, "x tol at group", i)
         if inference:
             assert np.array_equal(dev["has_inference"], ora["has_inference"]), (label, "has_inference")
@@ -102,17 +111,17 @@ def assert_fit_parity(dev, ora, rtol=1e-9, inference=False, ptol=1e-8, check_ic=
                 a, b = dev[k], ora[k]
                 m = np.isfinite(a) & np.isfinite(b)
                 sc = max(np.abs(b[m]).max(), 1e-300) if m.any() else 1.0
-                tol = 10 * (rt2 if a.ndim == 2 else rt)
+                tol = 10 * (rr2 if a.ndim == 2 else rr)
                 q, i = worst(np.abs(a - b) / np.maximum(np.abs(b), 1e-12 * sc + 1e-300), tol, m)
                 assert q <= 1.0, (label, k, q, "x tol at", i)
             for k in ["ci_lower", "ci_upper"]:
-                q, i = worst(np.abs(dev[k] - ora[k]) / scale, 10 * rt2, np.isfinite(ora[k]))
+                q, i = worst(np.abs(dev[k] - ora[k]) / np.maximum(cs, np.abs(ora[k])), 10 * rr2, np.isfinite(ora[k]))
                 assert q <= 1.0, (label, k, q, "x tol at", i)
             for k in ["p_values", "f_pvalue"]:
                 a, b = dev[k], ora[k]
                 m = np.isfinite(b) & (b > 1e-290)
                 # a p-value moves by ~ (1 + t^2) times the relative error of its statistic
-                tol = ptol if scalar_tol else (rt2 if a.ndim == 2 else rt) * 10 * (1.0 + np.square(
+                tol = ptol if scalar_tol else (rr2 if a.ndim == 2 else rr) * 10 * (1.0 + np.square(
                     np.nan_to_num(ora["t_values"] if a.ndim == 2 else np.sqrt(np.abs(ora["f_statistic"])), nan=0.0, posinf=0.0)))
                 q, i = worst(np.abs(a - b) / np.where(m, b, 1.0), np.broadcast_to(tol, a.shape), m)
                 assert q <= 1.0, (label, k, q, "x tol at", i)

@@ -42,7 +42,7 @@ def test_conditioned_small_groups(lib, oracle, path, kind, level, noise):
     ora = oracle.fit_batch(c["offsets"], c["y"], c["x"], None, **opt)
     assert (ora["status"] == 0).all()
     tol, kap = group_tolerances(c, ora)
-    assert_fit_parity(dev, ora, rtol=tol, inference=True, label=f"{kind}-{level}-{noise} kappa<={kap.max():.3g}")
+    assert_fit_parity(dev, ora, inference=True, label=f"{kind}-{level}-{noise} kappa<={kap.max():.3g}", **tol)
 
 
 WIDE = [("poly", 6, 12, "ols"), ("rho", 8, 16, "ridge"), ("rho", 6, 16, "wls"), ("nearcol", 4e-7, 16, "ols"),
@@ -64,7 +64,7 @@ def test_conditioned_wide_groups(lib, oracle, kind, level, p, method):
             dev = lib.fit_batch_host(c["offsets"], c["y"], c["x"], c["w"], **opt)
         finally:
             lib.force_path("auto")
-        assert_fit_parity(dev, ora, rtol=tol, inference=True, label=f"{kind}-{level} p={p} {method} [{path}] kappa<={kap.max():.3g}")
+        assert_fit_parity(dev, ora, inference=True, label=f"{kind}-{level} p={p} {method} [{path}] kappa<={kap.max():.3g}", **tol)
 
 
 def test_fallback_is_taken_where_needed_and_only_there(lib, oracle):
