@@ -482,43 +482,6 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		const int idf = (int)dfr;
 		tcrit = (Pm.tcrit && idf <= kTcritTable) ? Pm.tcrit[idf] : t_critical_dev(Pm.level, dfr);
 	}
-	if (!ROWS) {
-		// thread-per-group (solve_small_kernel): the P t tests and the F test share dfr, so their incomplete-beta
-		// tails are evaluated together (pvalues_same_df, specfun.cuh): P + 1 independent Horner chains per
-		// coefficient load instead of P + 1 dependent ones in sequence
-		double t2[P];
-#pragma unroll
-		for (int j = 0; j < P; ++j) {
-			const int64_t oj = g * P + j;
-			if ((live >> j) & 1u) {
-				const double se = sqrt(sigma2 * vdiag[j]);
-				const double t = b[j] / se;
-				o.coefficients[oj] = b[j];
-				o.std_errors[oj] = se;
-				o.t_values[oj] = t;
-				o.ci_lower[oj] = b[j] - tcrit * se;
-				o.ci_upper[oj] = b[j] + tcrit * se;
-				t2[j] = t * t;
-			} else {
-				o.coefficients[oj] = nanv;
-				o.std_errors[oj] = nanv;
-				o.t_values[oj] = nanv;
-				o.ci_lower[oj] = nanv;
-				o.ci_upper[oj] = nanv;
-				t2[j] = nanv;
-			}
-		}
-		double fs = nanv;
-		if (dfm > 0.0 && dfr > 0.0) fs = ((tss - rss) / dfm) / sigma2;
-		double pt[P], pf;
-		pvalues_same_df<P>(t2, live, fs, dfm, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co}, pt, pf);
-#pragma unroll
-		for (int j = 0; j < P; ++j) o.p_values[g * P + j] = ((live >> j) & 1u) ? pt[j] : nanv;
-		o.f_statistic[g] = fs;
-		o.f_pvalue[g] = pf;
-		if (o.has_inference) o.has_inference[g] = 1;
-		return;
-	}
 	// ... then lane q takes coefficients q, q+T, ...: the same instruction stream on different data.
 	// The p-values themselves (the expensive part) are evaluated after the round by all 32 lanes of the
 	// warp from the statistics deposited in v.pv: t^2 per coefficient and the F statistic.
@@ -541,14 +504,20 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 				o.t_values[oj] = t;
 				o.ci_lower[oj] = bj - tcrit * se;
 				o.ci_upper[oj] = bj + tcrit * se;
-				v.pv[j] = t * t;
+				if (ROWS)
+					v.pv[j] = t * t;
+				else
+					o.p_values[oj] = pvalue_f(t * t, 1.0, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
 			} else {
 				o.coefficients[oj] = nanv;
 				o.std_errors[oj] = nanv;
 				o.t_values[oj] = nanv;
 				o.ci_lower[oj] = nanv;
 				o.ci_upper[oj] = nanv;
-				v.pv[j] = nanv;
+				if (ROWS)
+					v.pv[j] = nanv;
+				else
+					o.p_values[oj] = nanv;
 			}
 		}
 	}
@@ -557,9 +526,13 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		if (dfm > 0.0 && dfr > 0.0) fs = ((tss - rss) / dfm) / sigma2;
 		o.f_statistic[g] = fs;
 		if (o.has_inference) o.has_inference[g] = 1;
-		v.pv[P] = fs;
-		v.pv[P + 1] = dfm; // > 0 marks "p-values wanted" for this slot
-		v.pv[P + 2] = dfr;
+		if (ROWS) {
+			v.pv[P] = fs;
+			v.pv[P + 1] = dfm; // > 0 marks "p-values wanted" for this slot
+			v.pv[P + 2] = dfr;
+		} else {
+			o.f_pvalue[g] = pvalue_f(fs, dfm, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
+		}
 	}
 }
 

@@ -338,168 +338,6 @@ static __device__ __noinline__ double pvalue_f(double f, double d1, double d2, c
 	return f_upper_p_fast(f, d1, d2, T);
 }
 
-// K two-sided t tests and one F test of ONE fit share their residual degrees of freedom nu. Evaluating the K + 1
-// incomplete-beta tails together turns K + 1 dependent Horner chains (one multiply-add latency per term, one
-// coefficient load per term and tail) into K + 1 independent chains per coefficient load: same arithmetic, same
-// results as pvalue_f element by element, ~K + 1 times fewer stall cycles in the thread-per-group solve kernel.
-//   f[i]  = t_i^2 (NaN = no coefficient: result unspecified, the caller stores NaN), want bit i set = wanted
-//   fstat = F statistic with (d1, nu) degrees of freedom; pf receives its upper tail (NaN when d1 <= 0)
-template <int K>
-__device__ __forceinline__ void pvalues_same_df(const double (&f)[K], unsigned want, double fstat, double d1, double d2,
-                                                const DfTables &T, double (&pt)[K], double &pf) {
-	const bool tables = T.ce != nullptr && d2 >= 1.0 && d2 <= (double)kTcritTable && d2 == floor(d2);
-	const bool f_ok = d1 > 0.0 && !isnan(fstat);
-	const bool f_batched = tables && f_ok && d1 == floor(d1) && d1 <= 1024.0 && (((int)d1) & 1) && fstat > 0.0 && !isinf(fstat);
-	if (!tables) {
-#pragma unroll
-		for (int i = 0; i < K; ++i) pt[i] = ((want >> i) & 1u) ? pvalue_f(f[i], 1.0, d2, T) : nan_f64();
-		pf = f_ok ? pvalue_f(fstat, d1, d2, T) : nan_f64();
-		return;
-	}
-	const int nu = (int)d2, m = nu >> 1;
-	const bool odd = nu & 1;
-	constexpr int E = K + 1;
-	double x[E], y[E], res[E];
-	unsigned need = want & ((1u << K) - 1u);
-#pragma unroll
-	for (int i = 0; i < K; ++i) {
-		const double den = d2 + f[i];
-		x[i] = d2 / den;
-		y[i] = f[i] / den;
-	}
-	{
-		const double den = d2 + d1 * fstat;
-		x[K] = f_batched ? d2 / den : 0.5;
-		y[K] = f_batched ? d1 * fstat / den : 0.5;
-		if (f_batched) need |= 1u << K;
-	}
-	// classes (betai_half_fast): remainder series for x <= 0.6, the finite sum for nu <= 400 otherwise
-	unsigned ser = 0u, fin = 0u;
-	int N = 0;
-#pragma unroll
-	for (int e = 0; e < E; ++e) {
-		if (!((need >> e) & 1u)) continue;
-		if (x[e] <= 0.6) {
-			ser |= 1u << e;
-			int Ne = (int)(-39.2f / __logf(fmaxf((float)x[e], 1e-30f))) + 3;
-			N = Ne > N ? Ne : N;
-		} else if (nu <= 400 && x[e] <= 1.0) {
-			fin |= 1u << e;
-		}
-	}
-	const double *tab = odd ? T.co : T.ce;
-	if (ser) {
-		if (N > kSeriesTerms) N = kSeriesTerms;
-		const int N8 = (N + 7) & ~7;
-		const double *t = tab + m + N8;
-		double acc[E];
-#pragma unroll
-		for (int e = 0; e < E; ++e) acc[e] = 0.0;
-		for (int n = N8; n > 0; n -= 8) {
-			t -= 8;
-			double c[8];
-#pragma unroll
-			for (int k = 0; k < 8; ++k) c[k] = __ldg(t + k);
-#pragma unroll
-			for (int k = 7; k >= 0; --k)
-#pragma unroll
-				for (int e = 0; e < E; ++e) acc[e] = fma(acc[e], x[e], c[k]);
-		}
-		// x^m for all elements: the same square-and-multiply schedule (m is common)
-		double r[E], b[E];
-#pragma unroll
-		for (int e = 0; e < E; ++e) {
-			r[e] = 1.0;
-			b[e] = x[e];
-		}
-		for (int mm = m; mm > 0; mm >>= 1) {
-			if (mm & 1) {
-#pragma unroll
-				for (int e = 0; e < E; ++e) r[e] *= b[e];
-			}
-#pragma unroll
-			for (int e = 0; e < E; ++e) b[e] *= b[e];
-		}
-#pragma unroll
-		for (int e = 0; e < E; ++e)
-			if ((ser >> e) & 1u)
-				res[e] = odd ? 0.63661977236758134308 * r[e] * sqrt(x[e]) * sqrt(y[e]) * acc[e] : r[e] * sqrt(y[e]) * acc[e];
-	}
-	if (fin) {
-		// sum_{n < m} tab[n] x^n, exactly m terms (horner_exact), for all elements at once
-		const double *t = tab + m;
-		double acc[E];
-#pragma unroll
-		for (int e = 0; e < E; ++e) acc[e] = 0.0;
-		const int rm = m & 7;
-		for (int i = 0; i < rm; ++i) {
-			--t;
-			const double c = __ldg(t);
-#pragma unroll
-			for (int e = 0; e < E; ++e) acc[e] = fma(acc[e], x[e], c);
-		}
-		for (int n = m - rm; n > 0; n -= 8) {
-			t -= 8;
-			double c[8];
-#pragma unroll
-			for (int k = 0; k < 8; ++k) c[k] = __ldg(t + k);
-#pragma unroll
-			for (int k = 7; k >= 0; --k)
-#pragma unroll
-				for (int e = 0; e < E; ++e) acc[e] = fma(acc[e], x[e], c[k]);
-		}
-#pragma unroll
-		for (int e = 0; e < E; ++e) {
-			if (!((fin >> e) & 1u)) continue;
-			const double sy = sqrt(y[e]), cx = sqrt(x[e]);
-			double pv;
-			if (odd)
-				pv = 0.63661977236758134308 * (atan2(cx, sy) - (m > 0 ? sy * cx * acc[e] : 0.0));
-			else
-				pv = 1.0 - sy * acc[e];
-			if (pv > 1e-4)
-				res[e] = pv; // 1 - A keeps >= 11 digits
-			else
-				fin &= ~(1u << e); // deep tail through the finite sum: the scalar routine's other branches
-		}
-	}
-	const unsigned done = ser | fin;
-#pragma unroll
-	for (int i = 0; i < K; ++i) {
-		if (!((want >> i) & 1u)) {
-			pt[i] = nan_f64();
-		} else if (isnan(f[i])) {
-			pt[i] = nan_f64();
-		} else if (isinf(f[i]) || !(x[i] > 0.0)) {
-			pt[i] = 0.0;
-		} else if (!(y[i] > 0.0)) {
-			pt[i] = 1.0;
-		} else if ((done >> i) & 1u) {
-			pt[i] = fmin(res[i], 1.0);
-		} else {
-			pt[i] = pvalue_f(f[i], 1.0, d2, T);
-		}
-	}
-	if (!f_ok) {
-		pf = nan_f64();
-	} else if (f_batched && ((done >> K) & 1u)) {
-		// odd d1: I_x(a, 1/2) from the batch, then the recurrence of f_upper_p_fast
-		double acc = res[K], term = 0.0;
-		const int mf = (int)d1;
-		if (mf > 1) {
-			const double xa = odd ? pow_int(x[K], m) * sqrt(x[K]) : pow_int(x[K], m);
-			term = xa * sqrt(y[K]) * T.gratio[nu] * 1.12837916709551257390; // 2/sqrt(pi)
-		}
-		for (int twob = 1; twob < mf; twob += 2) {
-			acc += term;
-			term *= y[K] * (double)(nu + twob) * T.rcp[twob + 2];
-		}
-		pf = fmin(acc, 1.0);
-	} else {
-		pf = pvalue_f(fstat, d1, d2, T);
-	}
-}
-
 // One thread per table entry.
 static __global__ void df_tables_kernel(double level, double *__restrict__ tcrit, double *__restrict__ gratio,
                                  double *__restrict__ rcp, double *__restrict__ ce, double *__restrict__ co) {
