@@ -655,10 +655,15 @@ __device__ __forceinline__ void accumulate_group(const SmemGroup &sg, const doub
 // ---------------------------------------------------------------------------------------------
 template <bool HASW, bool HAST, class Hdr>
 __device__ __forceinline__ void producer_loop(const AccArgs &a, unsigned char *smem, uint64_t *full_bar,
-                                              uint64_t *empty_bar, Hdr *hdr, int NS, int lane, int max_groups) {
+                                              uint64_t *empty_bar, Hdr *hdr, int NS, int lane, int max_groups,
+                                              int n_end = 1, int nb = 0) {
+	// nb > 0 (consumers that take stages by ticket and may be several fills ahead of the producer): the full
+	// barrier of fill number k is full_bar[k % nb], nb > stages + consumers, so that a waiter is never a whole
+	// barrier phase ahead (a parity wait cannot tell phase n from phase n - 2). The data stage stays k % NS.
 	const int p = a.p;
 	int s = 0;
 	uint32_t ph = 0;
+	int fb = 0; // index of the full barrier of the current fill
 	for (int64_t t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
 		int64_t g = a.tile_g0[t];
 		const int64_t gend = a.tile_g0[t + 1];
@@ -707,13 +712,13 @@ __device__ __forceinline__ void producer_loop(const AccArgs &a, unsigned char *s
 			unsigned char *base = smem + (size_t)s * a.stage_bytes;
 			int lx = 0, ly = 0, lw = 0, lt = 0;
 			uint32_t tx = 0;
-			tx += stage_fetch<8>(base, (const unsigned char *)(a.x + row0 * p), rows * p * 8, lane, &full_bar[s], &lx);
-			tx += stage_fetch<8>(base + a.xcap, (const unsigned char *)(a.y + row0), rows * 8, lane, &full_bar[s], &ly);
+			tx += stage_fetch<8>(base, (const unsigned char *)(a.x + row0 * p), rows * p * 8, lane, &full_bar[fb], &lx);
+			tx += stage_fetch<8>(base + a.xcap, (const unsigned char *)(a.y + row0), rows * 8, lane, &full_bar[fb], &ly);
 			if (HASW)
 				tx += stage_fetch<8>(base + a.xcap + a.ycap, (const unsigned char *)(a.w + row0), rows * 8, lane,
-				                     &full_bar[s], &lw);
+				                     &full_bar[fb], &lw);
 			if (HAST)
-				tx += stage_fetch<1>(base + a.xcap + a.ycap + a.wcap, a.train + row0, rows, lane, &full_bar[s], &lt);
+				tx += stage_fetch<1>(base + a.xcap + a.ycap + a.wcap, a.train + row0, rows, lane, &full_bar[fb], &lt);
 			if (lane == 0) {
 				hdr[s].rowstart[0] = 0;
 				hdr[s].g_first = g;
@@ -727,22 +732,179 @@ __device__ __forceinline__ void producer_loop(const AccArgs &a, unsigned char *s
 			__syncwarp();
 			if (lane == 0) {
 				if (tx)
-					mbar_arrive_expect_tx(&full_bar[s], tx);
+					mbar_arrive_expect_tx(&full_bar[fb], tx);
 				else
-					mbar_arrive(&full_bar[s]);
+					mbar_arrive(&full_bar[fb]);
 			}
 			g = g_next;
 			if (++s == NS) {
 				s = 0;
 				ph ^= 1u;
 			}
+			fb = nb > 0 ? (fb + 1 == nb ? 0 : fb + 1) : s;
 		}
 	}
-	// end marker
-	mbar_wait(&empty_bar[s], ph ^ 1u);
-	if (lane == 0) {
-		hdr[s].count = -1;
-		mbar_arrive(&full_bar[s]);
+	// end marker(s): one per consumer that takes stages by ticket (each leaves on its own marker), otherwise one
+	// that every consumer sees
+	for (int e = 0; e < n_end; ++e) {
+		mbar_wait(&empty_bar[s], ph ^ 1u);
+		if (lane == 0) {
+			hdr[s].count = -1;
+			mbar_arrive(&full_bar[fb]);
+		}
+		if (++s == NS) {
+			s = 0;
+			ph ^= 1u;
+		}
+		fb = nb > 0 ? (fb + 1 == nb ? 0 : fb + 1) : s;
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// The same producer with the group offsets of a whole tile prefetched into shared memory (cp.async, one tile
+// ahead) and the tile bounds read two tiles ahead. In producer_loop the offsets of the next stage are a global
+// load issued ~0.1 us before they are needed: its latency (~0.7 us) sits on the per-stage critical path of the
+// one warp that feeds the SM, next to two dependent loads per tile -- about 1.2 us per 39 KB stage, i.e. the
+// 4.7 TB/s at which the small-group kernels used to saturate whatever the consumers did.
+// obuf: shared memory, 2 * kOffsetTile int64 entries.
+// ---------------------------------------------------------------------------------------------
+constexpr int kOffsetTile = 1024; // offsets held per tile; groups of a tile beyond that read global memory
+__device__ __forceinline__ void cp_async8(void *dst_smem, const void *src) {
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <bool HASW, bool HAST, class Hdr>
+__device__ __forceinline__ void producer_loop_pf(const AccArgs &a, unsigned char *smem, uint64_t *full_bar,
+                                                 uint64_t *empty_bar, Hdr *hdr, int NS, int lane, int max_groups,
+                                                 int64_t *obuf, int n_end = 1, int nb = 0, uint32_t hint = 20000u) {
+	const int p = a.p;
+	int s = 0;
+	uint32_t ph = 0;
+	int fb = 0; // index of the full barrier of the current fill (see producer_loop)
+	const int64_t stride = gridDim.x;
+	// offsets[g0 .. g1] (at most kOffsetTile of them) -> obuf[b]; always commits a group
+	auto prefetch = [&](int b, int64_t g0, int64_t g1) {
+		int64_t n = g1 - g0 + 1;
+		if (n > kOffsetTile) n = kOffsetTile;
+		for (int64_t i = lane; i < n; i += 32) cp_async8(obuf + b * kOffsetTile + i, a.offsets + g0 + i);
+		cp_async_commit();
+	};
+	int64_t t = blockIdx.x;
+	int64_t g = 0, gend = 0, gn = 0, gendn = 0;
+	if (t < a.n_tiles) {
+		g = a.tile_g0[t];
+		gend = a.tile_g0[t + 1];
+		prefetch(0, g, gend);
+	}
+	if (t + stride < a.n_tiles) {
+		gn = a.tile_g0[t + stride];
+		gendn = a.tile_g0[t + stride + 1];
+	}
+	int b = 0;
+	for (; t < a.n_tiles; t += stride) {
+		// next tile: its offsets start streaming now, the bounds of the tile after it go to registers
+		const bool have_next = t + stride < a.n_tiles;
+		if (have_next)
+			prefetch(b ^ 1, gn, gendn);
+		else
+			cp_async_commit();
+		int64_t gnn = 0, gendnn = 0;
+		if (t + 2 * stride < a.n_tiles) {
+			gnn = a.tile_g0[t + 2 * stride];
+			gendnn = a.tile_g0[t + 2 * stride + 1];
+		}
+		cp_async_wait<1>(); // this tile's offsets have landed (everything but the group just committed)
+		__syncwarp();
+		const int64_t gt0 = g;
+		const int64_t *ob = obuf + b * kOffsetTile;
+		auto off_at = [&](int64_t gi) -> int64_t { // offsets[gi], gt0 <= gi <= gend
+			const int64_t i = gi - gt0;
+			return i < kOffsetTile ? ob[i] : a.offsets[gi];
+		};
+		while (g < gend) {
+			mbar_wait_hint(&empty_bar[s], ph ^ 1u, hint);
+			const int64_t row0 = off_at(g);
+			int cnt = 0;
+			int64_t row_end = row0;
+			bool closed = false;
+			while (!closed && g + cnt < gend && cnt < max_groups) {
+				const int64_t gi = g + cnt + lane;
+				const bool in = gi < gend && (cnt + lane) < max_groups;
+				int64_t oe = row0;
+				if (in) oe = off_at(gi + 1);
+				const bool fits = in && (oe - row0) <= (int64_t)a.cap_rows;
+				const unsigned m = __ballot_sync(0xffffffffu, fits);
+				const int nfit = (m == 0xffffffffu) ? 32 : (__ffs(~m) - 1);
+				if (lane < nfit) hdr[s].rowstart[cnt + lane + 1] = (uint32_t)(oe - row0);
+				if (nfit > 0) row_end = __shfl_sync(0xffffffffu, oe, nfit - 1);
+				cnt += nfit;
+				if (nfit < 32) closed = true;
+			}
+			if (cnt == 0) {
+				// group g alone exceeds a stage: hand it to the streaming kernel
+				if (lane == 0) {
+					const int slot = atomicAdd(a.big_count, 1);
+					a.big_list[slot] = g;
+				}
+				g += 1;
+				continue;
+			}
+			const int64_t rows = row_end - row0;
+			unsigned char *base = smem + (size_t)s * a.stage_bytes;
+			int lx = 0, ly = 0, lw = 0, lt = 0;
+			uint32_t tx = 0;
+			tx += stage_fetch<8>(base, (const unsigned char *)(a.x + row0 * p), rows * p * 8, lane, &full_bar[fb], &lx);
+			tx += stage_fetch<8>(base + a.xcap, (const unsigned char *)(a.y + row0), rows * 8, lane, &full_bar[fb], &ly);
+			if (HASW)
+				tx += stage_fetch<8>(base + a.xcap + a.ycap, (const unsigned char *)(a.w + row0), rows * 8, lane,
+				                     &full_bar[fb], &lw);
+			if (HAST)
+				tx += stage_fetch<1>(base + a.xcap + a.ycap + a.wcap, a.train + row0, rows, lane, &full_bar[fb], &lt);
+			if (lane == 0) {
+				hdr[s].rowstart[0] = 0;
+				hdr[s].g_first = g;
+				hdr[s].count = cnt;
+				hdr[s].next = 0;
+				hdr[s].lead_x = lx;
+				hdr[s].lead_y = ly;
+				hdr[s].lead_w = lw;
+				hdr[s].lead_t = lt;
+			}
+			__syncwarp();
+			if (lane == 0) {
+				if (tx)
+					mbar_arrive_expect_tx(&full_bar[fb], tx);
+				else
+					mbar_arrive(&full_bar[fb]);
+			}
+			g += cnt;
+			if (++s == NS) {
+				s = 0;
+				ph ^= 1u;
+			}
+			fb = nb > 0 ? (fb + 1 == nb ? 0 : fb + 1) : s;
+		}
+		__syncwarp(); // every lane is done with obuf[b] before the tile after next overwrites it
+		g = gn;
+		gend = gendn;
+		gn = gnn;
+		gendn = gendnn;
+		b ^= 1;
+	}
+	cp_async_wait<0>();
+	for (int e = 0; e < n_end; ++e) {
+		mbar_wait_hint(&empty_bar[s], ph ^ 1u, hint);
+		if (lane == 0) {
+			hdr[s].count = -1;
+			mbar_arrive(&full_bar[fb]);
+		}
+		if (++s == NS) {
+			s = 0;
+			ph ^= 1u;
+		}
+		fb = nb > 0 ? (fb + 1 == nb ? 0 : fb + 1) : s;
 	}
 }
 

@@ -106,6 +106,35 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 	    "r"(parity), "r"(20000u) // suspend-time hint (ns): sleep in hardware instead of spinning
 	    : "memory");
 }
+// Same with a run-time suspend hint; hint 0 = pure spin on test_wait (experiments: wake-up latency of a suspended warp)
+__device__ __forceinline__ void mbar_wait_hint(uint64_t *bar, uint32_t parity, uint32_t hint_ns) {
+	if (hint_ns == 0u) {
+		uint32_t ok;
+		do {
+			asm volatile(
+			    "{\n"
+			    " .reg .pred p;\n"
+			    " mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+			    " selp.u32 %0, 1, 0, p;\n"
+			    "}\n"
+			    : "=r"(ok)
+			    : "r"(smem_u32(bar)), "r"(parity)
+			    : "memory");
+		} while (ok == 0u);
+		return;
+	}
+	asm volatile(
+	    "{\n"
+	    " .reg .pred p;\n"
+	    "WAIT_%=:\n"
+	    " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+	    " @p bra DONE_%=;\n"
+	    " bra WAIT_%=;\n"
+	    "DONE_%=:\n"
+	    "}\n" ::"r"(smem_u32(bar)),
+	    "r"(parity), "r"(hint_ns)
+	    : "memory");
+}
 __device__ __forceinline__ void mbar_wait_addr(uint32_t bar_addr, uint32_t parity) {
 	asm volatile(
 	    "{\n"

@@ -189,6 +189,10 @@ struct SmallGroupView {
 	// pass are queued for refine_kernel instead
 	int *refine_count;
 	int64_t *refine_list;
+	// stash kernel: no record of the group exists in HBM -- a group queued for refine_kernel gets its standard
+	// record written here (array-of-records layout, rec_len(P) doubles per group) at the moment it is queued
+	double *rec_out;
+	double *stash; // stash kernel: this group's slot (field f at stash[f * 32])
 };
 
 // First row (in state order) that passes `pred(row)`, searched by the T lanes together; -1 if none.
@@ -249,6 +253,23 @@ __device__ __forceinline__ double small_exact_rss(const SmallGroupView &v, const
 	}
 	for (int off = 1; off < v.T; off <<= 1) rss += shfl_xor_f64(v.mask, rss, off);
 	return rss;
+}
+
+// The group's sums as a standard moment record (common.cuh layout, element stride 1): what refine_kernel and
+// solve_group read. Only the stash kernel needs it, and only for the rare groups it queues.
+template <int P>
+__device__ __noinline__ void small_write_std_record(const SmallMoments<P> &M, const double (&sh)[P + 1], unsigned nonconst,
+                                                    int n_state, double sw, double *__restrict__ rec) {
+	constexpr int K = P + 1;
+	rec[0] = (double)M.nv;
+	rec[1] = sw;
+	rec[2] = (double)n_state;
+	rec[3] = 0.0;
+	for (int c = 0; c < K; ++c) rec[rec_off_shift(P) + c] = sh[c];
+	for (int c = 0; c < P; ++c) rec[rec_off_cdev(P) + c] = ((nonconst >> c) & 1u) ? 1.0 : 0.0;
+	for (int c = rec_off_cdev(P) + P; c < rec_off_s1(P); ++c) rec[c] = 0.0;
+	for (int c = 0; c < K; ++c) rec[rec_off_s1(P) + c] = M.s1[c];
+	for (int i = 0; i < SmallMoments<P>::NS2; ++i) rec[rec_off_s2(P) + i] = M.s2[i];
 }
 
 // Solve + statistics of one group from its sums, executed by the T lanes of the group together.
@@ -428,6 +449,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		} else if (v.refine_count) {
 			const int slot = atomicAdd(v.refine_count, 1);
 			v.refine_list[slot] = g;
+			if (v.rec_out) small_write_std_record<P>(M, sh, nonconst, n_state, sw, v.rec_out + g * rec_len(P));
 		}
 	}
 	if (!(rss > 0.0)) rss = 0.0;
@@ -566,11 +588,67 @@ __device__ __forceinline__ void small_store_record(const double (&keep)[SmallSpl
 		if (4 * k + 3 < NSUM || 4 * k + q < NSUM) recq[(int64_t)(4 * k) * rs] = keep[k];
 }
 
-template <int P, bool HASW, bool HAST, bool FUSED>
+// ---- stash (fit_small_stash_kernel) -----------------------------------------------------------------------
+// A warp parks the sums of the groups it has accumulated in a private shared-memory table, field-major with
+// 32 slots per field (slot = the lane that will solve the group), until 32 groups are waiting; then every lane
+// solves one group with all arrays in registers (small_solve, thread per group). Fields of a slot:
+//   g | nv, n_state, nonconst packed | [sum w] | shift[K] | S1[K] | S2[K(K+1)/2]
+template <int P, bool HASW> struct SmallStash {
+	static constexpr int K = P + 1;
+	static constexpr int NS2 = K * (K + 1) / 2;
+	static constexpr int NF = 2 + (HASW ? 1 : 0) + 2 * K + NS2;
+	static constexpr int BYTES = NF * 32 * 8;
+};
+// Every lane of the group holds all the sums (full butterfly); lane q stores the fields f = q (mod T).
+template <int P, bool HASW>
+__device__ __forceinline__ void small_stash_store(const SmallMoments<P> &M, const double (&sh)[P + 1], unsigned nonconst,
+                                                  int n_state, int64_t g, double *__restrict__ st, int q, int T) {
+	constexpr int K = P + 1;
+	int f = 0;
+	auto put = [&](double val) {
+		if ((f & (T - 1)) == q) st[f * 32] = val;
+		++f;
+	};
+	put(__longlong_as_double((long long)g));
+	put(__longlong_as_double((long long)M.nv | ((long long)n_state << 21) | ((long long)nonconst << 42)));
+	if (HASW) put(M.sw);
+#pragma unroll
+	for (int c = 0; c < K; ++c) put(sh[c]);
+#pragma unroll
+	for (int c = 0; c < K; ++c) put(M.s1[c]);
+#pragma unroll
+	for (int i = 0; i < SmallMoments<P>::NS2; ++i) put(M.s2[i]);
+}
+// The sums parked in one slot (sl = table + slot) back into registers.
+template <int P, bool HASW>
+__device__ __forceinline__ void small_stash_load(const double *__restrict__ sl, SmallMoments<P> &M, double (&sh)[P + 1],
+                                                 unsigned &nonconst, int &n_state, int64_t &g) {
+	constexpr int K = P + 1;
+	int f = 0;
+	auto get = [&]() { return sl[(f++) * 32]; };
+	g = (int64_t)__double_as_longlong(get());
+	const long long pk = __double_as_longlong(get());
+	M.nv = (int)(pk & 0x1fffff);
+	n_state = (int)((pk >> 21) & 0x1fffff);
+	nonconst = (unsigned)(pk >> 42) & 0xffu;
+	M.ns = n_state;
+	M.sw = HASW ? get() : (double)M.nv;
+#pragma unroll
+	for (int c = 0; c < K; ++c) sh[c] = get();
+#pragma unroll
+	for (int c = 0; c < K; ++c) M.s1[c] = get();
+#pragma unroll
+	for (int i = 0; i < SmallMoments<P>::NS2; ++i) M.s2[i] = get();
+#pragma unroll
+	for (int c = 0; c < P; ++c) M.q2[c] = 0.0;
+}
+
+template <int P, bool HASW, bool HAST, int MODE>
 __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, const FitParams &Pm,
                                             const AnofoxB200FitOutputs &o, double *records, int64_t n_groups) {
 	constexpr int K = P + 1;
 	constexpr int NQ = SmallSplit<P>::NQ;
+	constexpr bool FUSED = MODE != 0; // 1 and 2: every lane of the group ends up with all the sums
 	SmallMoments<P> M;
 	double keep[NQ];
 	double sh[K];
@@ -677,7 +755,9 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 					nonconst |= !(small_exact_cdev<P, HASW, HAST>(v, c, sh[c]) < 1e-10) ? (1u << c) : 0u;
 		}
 	}
-	if (FUSED)
+	if (MODE == 2)
+		small_stash_store<P, HASW>(M, sh, nonconst, n_state, g, v.stash, v.q, v.T);
+	else if (MODE == 1)
 		small_solve<P, HASW, HAST, true>(M, sh, nonconst, n_state, g, Pm, o, v);
 	else
 		small_store_record<P>(keep, M.nv, HASW ? M.sw : (double)M.nv, sh, nonconst, n_state, records + g, n_groups, v.q);
@@ -689,7 +769,7 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 #define ANOFOX_SOLVE_SMALL_MINB 4
 #endif
 template <int P>
-__global__ void __launch_bounds__(128, ANOFOX_SOLVE_SMALL_MINB) solve_small_kernel(const double *__restrict__ records, int64_t n_groups, FitParams Pm,
+__global__ void __launch_bounds__(512, 1) solve_small_kernel(const double *__restrict__ records, int64_t n_groups, FitParams Pm,
                                                           AnofoxB200FitOutputs o, int *refine_count,
                                                           int64_t *refine_list) {
 	constexpr int K = P + 1;
@@ -724,6 +804,8 @@ __global__ void __launch_bounds__(128, ANOFOX_SOLVE_SMALL_MINB) solve_small_kern
 	v.pv = nullptr;
 	v.refine_count = refine_count;
 	v.refine_list = refine_list;
+	v.rec_out = nullptr;
+	v.stash = nullptr;
 	small_solve<P, false, false, false>(M, sh, nonconst, n_state, g, Pm, o, v);
 }
 
@@ -735,8 +817,12 @@ struct SmallArgs {
 	AccArgs acc;
 	FitParams params;
 	AnofoxB200FitOutputs out;
-	int lanes_per_group; // T: 4, 8, 16 or 32
+	int lanes_per_group; // T: 4, 8, 16 or 32 (stash kernel: 1 .. 32)
 	int max_stage_groups;
+	int *refine_count;     // stash kernel: queue of the groups that need the exact residual pass
+	int64_t *refine_list;
+	int debug;             // experiments only: 1 = solve warps drop the tables without solving
+	uint32_t wait_hint;    // suspend hint (ns) of the stage barriers' waits; 0 = spin
 };
 
 template <int P, int NCW, bool HASW, bool HAST, bool FUSED>
@@ -745,7 +831,8 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 	__shared__ uint64_t full_bar[kSmallMaxStages], empty_bar[kSmallMaxStages];
 	__shared__ SmallStageHeader hdr[kSmallMaxStages];
 	constexpr int PVW = P + 3;                   // per slot: f[P] (t^2), F, d1 (0 = nothing to do), d2
-	__shared__ double pv_scratch[NCW][8 * PVW];  // at most 8 groups per warp round (T >= 4)
+	__shared__ double pv_scratch[FUSED ? NCW : 1][8 * PVW]; // at most 8 groups per warp round (T >= 4)
+	__shared__ int64_t obuf[2 * kOffsetTile];               // the producer's prefetched group offsets
 	const AccArgs &a = args.acc;
 	const int NS = a.n_stages;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -758,7 +845,7 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 	}
 	__syncthreads();
 	if (warp == 0) {
-		producer_loop<HASW, HAST>(a, smem, full_bar, empty_bar, hdr, NS, lane, args.max_stage_groups);
+		producer_loop_pf<HASW, HAST>(a, smem, full_bar, empty_bar, hdr, NS, lane, args.max_stage_groups, obuf, 1, 0, args.wait_hint);
 		return;
 	}
 	const int T = args.lanes_per_group;
@@ -766,13 +853,13 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 	const int gpw = 32 >> lt, lg = 5 - lt; // groups per warp round and its log2
 	const int sub = lane >> lt, q = lane & (T - 1);
 	const unsigned gmask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << (sub * T);
-	double *pvw = pv_scratch[warp - 1];
+	double *pvw = pv_scratch[FUSED ? warp - 1 : 0];
 	const bool want_p = FUSED && args.params.compute_inference && args.out.std_errors;
 	const DfTables Tb{args.params.tcrit, args.params.gratio, args.params.rcp, args.params.ce, args.params.co};
 	int s = 0;
 	uint32_t ph = 0;
 	for (;;) {
-		mbar_wait(&full_bar[s], ph);
+		mbar_wait_hint(&full_bar[s], ph, args.wait_hint);
 		const int cnt = hdr[s].count;
 		if (cnt < 0) break;
 		unsigned char *base = smem + (size_t)s * a.stage_bytes;
@@ -801,12 +888,14 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 				v.pv = pvw + sub * PVW;
 				v.refine_count = nullptr;
 				v.refine_list = nullptr;
+				v.rec_out = nullptr;
+				v.stash = nullptr;
 				v.sg.x = ax + (uint32_t)rb * (uint32_t)(P * 8);
 				v.sg.y = ay + (uint32_t)rb * 8u;
 				v.sg.w = aw + (uint32_t)rb * 8u;
 				v.sg.t = at + (uint32_t)rb;
 				v.sg.kone = v.sg.kzero = 0u;
-				small_group<P, HASW, HAST, FUSED>(v, g0 + gi, args.params, args.out, a.records, a.n_groups);
+				small_group<P, HASW, HAST, FUSED ? 1 : 0>(v, g0 + gi, args.params, args.out, a.records, a.n_groups);
 			}
 			__syncwarp();
 			if (want_p) {
@@ -835,6 +924,181 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 			s = 0;
 			ph ^= 1u;
 		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Stash kernel: rows -> results in ONE launch, with no redundant solve and no record round trip through HBM.
+// Warp roles inside the persistent CTA (one per SM):
+//   warp 0                 producer: TMA bulk copies of whole groups into the ring of stages (producer_loop)
+//   warps 1 .. NACC        accumulate: take the next stage by ticket (a stage belongs to exactly one warp), fold
+//                          its groups T lanes per group (small_group<MODE 2>) and park each group's sums in one of
+//                          the warp's two private 32-slot tables in shared memory; a full table is posted
+//   warps NACC+1 ..        solve: take the next posted table by ticket, lane k loads the sums of slot k into
+//                          registers, the table is handed back at once, and every lane runs the thread-per-group
+//                          solve + inference (the instruction stream of solve_small_kernel) and writes the struct
+// The accumulate warps are bound by the TMA stream from HBM, the solve warps by FP64 latency (a dependent chain
+// per group: it takes ~16 of them per SM to keep the issue slots busy); inside one CTA the two overlap instead
+// of running back to back as two launches, and the 0.7 GB record round trip of the two-kernel path is gone.
+#ifndef ANOFOX_STASH_SEG
+#define ANOFOX_STASH_SEG 0
+#endif
+template <int P, int NACC, int NSOL, bool HASW, bool HAST>
+__global__ void __launch_bounds__(32 * (1 + NACC + NSOL), 1) fit_small_stash_kernel(const SmallArgs args) {
+	extern __shared__ __align__(128) unsigned char smem[];
+	constexpr int NB = 32; // full barriers of the ring / of the posted tables: more than the warps that can wait on them
+	constexpr int NTAB = 2 * NACC;
+	constexpr int TAB = SmallStash<P, HASW>::NF * 32; // doubles per table
+	static_assert(NB > kSmallMaxStages + NACC && NB > NSOL + NTAB, "a ticket holder must never be a whole barrier phase ahead");
+	static_assert(!ANOFOX_STASH_SEG || 1 + NACC + NSOL >= 4 * NACC + 1, "the accumulate warps are warps 4, 8, .. 4 NACC");
+	__shared__ uint64_t full_bar[NB], empty_bar[kSmallMaxStages];
+	__shared__ uint64_t tab_full[NB], tab_empty[NTAB];
+	__shared__ int tab_ent[NB]; // posted table number k: physical table | (groups + 1) << 8; groups + 1 == 0: no more work
+	__shared__ SmallStageHeader hdr[kSmallMaxStages];
+	__shared__ int ticket, tab_prod, tab_cons, acc_done;
+	__shared__ int64_t obuf[2 * kOffsetTile];
+	const AccArgs &a = args.acc;
+	const int NS = a.n_stages;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	if (threadIdx.x == 0) {
+		for (int s = 0; s < NB; ++s) {
+			mbar_init(&full_bar[s], 1);
+			mbar_init(&tab_full[s], 1);
+		}
+		for (int s = 0; s < NS; ++s) mbar_init(&empty_bar[s], 1); // the one warp that took the stage
+		for (int s = 0; s < NTAB; ++s) mbar_init(&tab_empty[s], 1);
+		mbar_fence_init();
+		ticket = tab_prod = tab_cons = acc_done = 0;
+	}
+	__syncthreads();
+	if (warp == 0) {
+		producer_loop_pf<HASW, HAST>(a, smem, full_bar, empty_bar, hdr, NS, lane, args.max_stage_groups, obuf, NACC, NB, args.wait_hint);
+		return;
+	}
+	double *pool = reinterpret_cast<double *>(smem + (size_t)NS * a.stage_bytes);
+	// Roles by scheduler: warp w issues from sub-partition w % 4. The producer and the accumulate warps (a small
+	// loop) all sit on sub-partition 0; the solve warps (40 KB of straight-line code per pass, which streams
+	// through the instruction cache of the sub-partition) take the other three and cannot evict that loop.
+#if ANOFOX_STASH_SEG
+	const bool is_acc = (warp & 3) == 0 && (warp >> 2) <= NACC;
+	const int aw_i = (warp >> 2) - 1;
+#else
+	const bool is_acc = warp <= NACC;
+	const int aw_i = warp - 1;
+#endif
+	if (is_acc) {
+		// ------------------------------------------------ accumulate warps ------------------------------------
+		const int T = args.lanes_per_group;
+		const int lt = 31 - __clz(T);
+		const int gpw = 32 >> lt, lg = 5 - lt;
+		const int sub = lane >> lt, q = lane & (T - 1);
+		const unsigned gmask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << (sub * T);
+		int filled = 0, use = 0; // groups parked in the current table; tables this warp has started so far
+		auto post = [&](int phys, int groups) {
+			__syncwarp();
+			if (lane == 0) {
+				const int k = atomicAdd(&tab_prod, 1);
+				tab_ent[k & (NB - 1)] = phys | ((groups + 1) << 8);
+				mbar_arrive(&tab_full[k & (NB - 1)]); // release: the table's stores are visible to the waiter
+			}
+		};
+		for (;;) {
+			int tk = 0;
+			if (lane == 0) tk = atomicAdd(&ticket, 1);
+			tk = __shfl_sync(0xffffffffu, tk, 0);
+			const int s = tk % NS;
+			mbar_wait_hint(&full_bar[tk & (NB - 1)], (uint32_t)((tk / NB) & 1), args.wait_hint);
+			const int cnt = hdr[s].count;
+			if (cnt < 0) {
+				if (lane == 0) mbar_arrive(&empty_bar[s]);
+				break;
+			}
+			const int phys = 2 * aw_i + (use & 1);
+			if (filled == 0) mbar_wait(&tab_empty[phys], (uint32_t)(((use >> 1) & 1) ^ 1)); // its previous use has been read
+			double *st = pool + (size_t)phys * TAB;
+			unsigned char *base = smem + (size_t)s * a.stage_bytes;
+			const uint32_t ax = smem_u32(base + hdr[s].lead_x);
+			const uint32_t ay = smem_u32(base + a.xcap + hdr[s].lead_y);
+			const uint32_t aw = HASW ? smem_u32(base + a.xcap + a.ycap + hdr[s].lead_w) : 0u;
+			const uint32_t at = HAST ? smem_u32(base + a.xcap + a.ycap + a.wcap + hdr[s].lead_t) : 0u;
+			const int64_t g0 = hdr[s].g_first;
+			const int nrounds = (args.debug & 2) ? 0 : (cnt + gpw - 1) >> lg;
+			for (int r = 0; r < nrounds; ++r) {
+				const int gi = (r << lg) + sub;
+				if (gi < cnt) {
+					const int rb = (int)hdr[s].rowstart[gi];
+					SmallGroupView v;
+					v.n = (int)hdr[s].rowstart[gi + 1] - rb;
+					v.q = q;
+					v.T = T;
+					v.mask = gmask;
+					v.pv = nullptr;
+					v.refine_count = nullptr;
+					v.refine_list = nullptr;
+					v.rec_out = nullptr;
+					v.stash = st + filled + gi;
+					v.sg.x = ax + (uint32_t)rb * (uint32_t)(P * 8);
+					v.sg.y = ay + (uint32_t)rb * 8u;
+					v.sg.w = aw + (uint32_t)rb * 8u;
+					v.sg.t = at + (uint32_t)rb;
+					v.sg.kone = v.sg.kzero = 0u;
+					small_group<P, HASW, HAST, 2>(v, g0 + gi, args.params, args.out, a.records, a.n_groups);
+				}
+			}
+			__syncwarp();
+			if (lane == 0) mbar_arrive(&empty_bar[s]); // the rows are no longer needed: only the sums are kept
+			filled += cnt;
+			if (filled + args.max_stage_groups > 32) {
+				post(phys, filled);
+				filled = 0;
+				++use;
+			}
+		}
+		if (filled > 0) post(2 * aw_i + (use & 1), filled);
+		// the last accumulate warp to finish tells every solve warp that no more tables will come
+		int last = 0;
+		if (lane == 0) last = atomicAdd(&acc_done, 1) == NACC - 1 ? 1 : 0;
+		last = __shfl_sync(0xffffffffu, last, 0);
+		if (last)
+			for (int i = 0; i < NSOL; ++i) post(255, -1);
+		return;
+	}
+	// ---------------------------------------------------- solve warps -----------------------------------------
+	for (;;) {
+		int c = 0;
+		if (lane == 0) c = atomicAdd(&tab_cons, 1);
+		c = __shfl_sync(0xffffffffu, c, 0);
+		mbar_wait(&tab_full[c & (NB - 1)], (uint32_t)((c / NB) & 1));
+		const int ent = tab_ent[c & (NB - 1)];
+		const int n = (ent >> 8) - 1;
+		if (n < 0) break;
+		const int phys = ent & 255;
+		SmallMoments<P> M;
+		double sh[P + 1];
+		unsigned nonconst = 0u;
+		int n_state = 0;
+		int64_t g = 0;
+		if (lane < n) small_stash_load<P, HASW>(pool + (size_t)phys * TAB + lane, M, sh, nonconst, n_state, g);
+		__syncwarp();
+		if (lane == 0) mbar_arrive(&tab_empty[phys]); // the sums are in registers: the table can be refilled
+		if (args.debug & 1) {
+			if (lane < n && !(args.debug & 2)) args.out.intercept[g] = M.s1[0] + sh[0];
+			continue;
+		}
+		if (lane < n) {
+			SmallGroupView v;
+			v.n = 0;
+			v.q = 0;
+			v.T = 1;
+			v.mask = 0u;
+			v.pv = nullptr;
+			v.refine_count = args.refine_count;
+			v.refine_list = args.refine_list;
+			v.rec_out = a.records;
+			v.stash = nullptr;
+			small_solve<P, false, false, false>(M, sh, nonconst, n_state, g, args.params, args.out, v);
+		}
+		__syncwarp();
 	}
 }
 

@@ -682,17 +682,17 @@ static cudaError_t launch_solve_list(const double *records, const int64_t *list,
 	return cudaGetLastError();
 }
 
-static cudaError_t launch_small(const SmallArgs &a, bool fused, bool has_w, bool has_t, int grid, cudaStream_t st) {
+static cudaError_t launch_small(const SmallArgs &a, int mode, bool has_w, bool has_t, int grid, cudaStream_t st) {
 	cudaError_t e = cudaErrorInvalidValue;
 	switch (a.acc.p) {
-	case 1: e = launch_small_p1(fused, has_w, has_t, a, grid, st); break;
-	case 2: e = launch_small_p2(fused, has_w, has_t, a, grid, st); break;
-	case 3: e = launch_small_p3(fused, has_w, has_t, a, grid, st); break;
-	case 4: e = launch_small_p4(fused, has_w, has_t, a, grid, st); break;
-	case 5: e = launch_small_p5(fused, has_w, has_t, a, grid, st); break;
-	case 6: e = launch_small_p6(fused, has_w, has_t, a, grid, st); break;
-	case 7: e = launch_small_p7(fused, has_w, has_t, a, grid, st); break;
-	case 8: e = launch_small_p8(fused, has_w, has_t, a, grid, st); break;
+	case 1: e = launch_small_p1(mode, has_w, has_t, a, grid, st); break;
+	case 2: e = launch_small_p2(mode, has_w, has_t, a, grid, st); break;
+	case 3: e = launch_small_p3(mode, has_w, has_t, a, grid, st); break;
+	case 4: e = launch_small_p4(mode, has_w, has_t, a, grid, st); break;
+	case 5: e = launch_small_p5(mode, has_w, has_t, a, grid, st); break;
+	case 6: e = launch_small_p6(mode, has_w, has_t, a, grid, st); break;
+	case 7: e = launch_small_p7(mode, has_w, has_t, a, grid, st); break;
+	case 8: e = launch_small_p8(mode, has_w, has_t, a, grid, st); break;
 	}
 	LAUNCHED();
 	return e;
@@ -902,10 +902,14 @@ static RingGeom ring_geometry(int p, bool has_w, bool has_t, int64_t n_rows, int
 // path, 2 = small groups through the single fused kernel (tests / A-B runs)
 static std::atomic<int> g_force_path{0};
 struct SmallGeom {
-	bool use;
+	bool use, stash;
 	int T, max_groups;
 	StageGeom sg;
 };
+// which small-group kernels: accumulate-to-record + thread-per-group solve kernel by default; 2 = the redundant-solve
+// fused kernel, 6 = the stash kernel (rows -> results in one launch, fused_small.cuh) -- both A/B paths: measured
+// slower than the two-kernel path on C2
+static bool small_use_stash() { return g_force_path.load() == 6; }
 static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, int64_t n_groups) {
 	SmallGeom r;
 	memset(&r, 0, sizeof r);
@@ -914,17 +918,41 @@ static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	const double mean_bytes = mean_rows * (double)row_bytes;
 	r.use = g_force_path.load() != 1 && g_force_path.load() != 3 && p <= kSmallMaxFeatures && n_groups > 0 && mean_bytes <= 24.0 * 1024.0;
 	if (!r.use) return r;
-	int T = 4;
-	while (T < 32 && mean_bytes > 700.0 * T) T *= 2;
-	r.T = T;
-	const int gpw = 32 / T;
+	// the stash kernel's ring is what the stashes leave of the shared memory (>= ~110 KB): it takes the batches
+	// whose typical group is at most a ninth of that, the accumulate-to-record kernel the rest (where the solve
+	// stage is a small share of the work anyway)
+	const int64_t stash_ring = (int64_t)206 * 1024 - (int64_t)stash_pool_bytes(p, has_w);
+	r.stash = small_use_stash() && mean_bytes * 9.0 <= (double)stash_ring;
 	// tuning hooks (tools/sweep_small.sh): rounds of 32 lanes per stage and the shared-memory budget of the ring
 	static const int env_rounds = getenv("ANOFOX_B200_SMALL_ROUNDS") ? atoi(getenv("ANOFOX_B200_SMALL_ROUNDS")) : 0;
 	static const int env_small_kb = getenv("ANOFOX_B200_SMALL_KB") ? atoi(getenv("ANOFOX_B200_SMALL_KB")) : 0;
-	r.max_groups = std::min(kSmallStageGroups, (env_rounds > 0 ? env_rounds : 2) * gpw); // two rounds per stage
-	const int64_t budget = (env_small_kb > 0 ? env_small_kb : 196) * 1024;
+	static const int env_stage_kb = getenv("ANOFOX_B200_STASH_STAGE_KB") ? atoi(getenv("ANOFOX_B200_STASH_STAGE_KB")) : 0;
+	static const int env_T = getenv("ANOFOX_B200_STASH_T") ? atoi(getenv("ANOFOX_B200_STASH_T")) : 0;
+	int64_t budget;
+	if (r.stash) {
+		// a stage is one warp's unit of work: 32 / T groups, T lanes per group, about 40 KB of rows (a power of two
+		// of groups, so that two, four, ... stages fill the 32 slots of a warp's stash exactly)
+		const double stage_target = (env_stage_kb > 0 ? env_stage_kb : 40) * 1024.0;
+		int mg = 32;
+		while (mg > 1 && (double)mg * mean_bytes > stage_target) mg >>= 1;
+		int T = 32 / mg;
+		if (env_T > 0 && env_T <= 32 && (env_T & (env_T - 1)) == 0 && env_T >= T) T = env_T; // more lanes per group, same stage
+		r.T = T;
+		r.max_groups = mg;
+		// the ring gets what the stashes of the worker warps leave of the CTA's shared memory
+		budget = stash_ring;
+		if (env_small_kb > 0) budget = std::min<int64_t>(budget, (int64_t)env_small_kb * 1024);
+	} else {
+		int T = 4;
+		while (T < 32 && mean_bytes > 700.0 * T) T *= 2;
+		r.T = T;
+		const int gpw = 32 / T;
+		r.max_groups = std::min(kSmallStageGroups, (env_rounds > 0 ? env_rounds : 2) * gpw); // two rounds per stage
+		budget = (env_small_kb > 0 ? env_small_kb : 196) * 1024;
+	}
 	int64_t cap = (int64_t)std::ceil(std::max((double)r.max_groups, 4.0) * std::max(mean_rows, 1.0)) + 8;
-	if (cap * row_bytes > 96 * 1024) cap = 96 * 1024 / row_bytes;
+	const int64_t cap_bytes = r.stash ? std::min<int64_t>(96 * 1024, budget / 3 - 256) : 96 * 1024;
+	if (cap * row_bytes > cap_bytes) cap = cap_bytes / row_bytes;
 	if (cap * row_bytes < 8 * 1024) cap = 8 * 1024 / row_bytes;
 	StageGeom &g = r.sg;
 	g.cap_rows = (int)cap;
@@ -934,7 +962,10 @@ static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	g.tcap = has_t ? align16((int64_t)g.cap_rows + 32) : 0;
 	g.stage_bytes = (g.xcap + g.ycap + g.wcap + g.tcap + 127) & ~127;
 	g.n_stages = (int)std::min<int64_t>(kSmallMaxStages, budget / g.stage_bytes);
-	if (g.n_stages < 2) g.n_stages = 2;
+	if (g.n_stages < 2) {
+		// (cannot happen with the 96 KB stage cap and >= 100 KB of ring; keep the kernel's minimum anyway)
+		g.n_stages = 2;
+	}
 	g.window_rows = (int64_t)g.cap_rows * 8;
 	return r;
 }
@@ -1270,7 +1301,10 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	const bool use_ring = !small.use && g_force_path.load() != 3;
 	const StageGeom sg = small.use ? small.sg : stage_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
 	CU(cudaMemsetAsync(ws.big_count, 0, 768, st), "memset"); // big_count | refine_count | redo_count
-	const bool fused = small.use && g_force_path.load() == 2;
+	// small-group kernels: 2 = stash kernel (rows -> results, one launch), 1 = the redundant-solve fused kernel
+	// (A/B), 0 = accumulate to transposed records + thread-per-group solve kernel
+	const int small_mode = !small.use ? 0 : (small.stash ? 2 : (g_force_path.load() == 2 ? 1 : 0));
+	const bool fused = small_mode != 0;
 	const bool transposed = small.use && !fused; // record element (g, i) at records[g + i * G]
 	const int64_t rec_gs = transposed ? 1 : rec_len(p), rec_es = transposed ? G : 1;
 	int64_t big_threshold = sg.cap_rows;
@@ -1346,7 +1380,13 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 			sa.out = fo;
 			sa.lanes_per_group = small.T;
 			sa.max_stage_groups = small.max_groups;
-			CU(launch_small(sa, fused, wuse != nullptr, train_use != nullptr, grid, st), "fit_small_kernel");
+			static const int env_dbg = getenv("ANOFOX_B200_STASH_DEBUG") ? atoi(getenv("ANOFOX_B200_STASH_DEBUG")) : 0;
+			sa.debug = env_dbg;
+			static const int env_hint = getenv("ANOFOX_B200_WAIT_HINT_NS") ? atoi(getenv("ANOFOX_B200_WAIT_HINT_NS")) : 20000;
+			sa.wait_hint = (uint32_t)env_hint;
+			sa.refine_count = ws.refine_count;
+			sa.refine_list = ws.refine_list;
+			CU(launch_small(sa, small_mode, wuse != nullptr, train_use != nullptr, grid, st), "fit_small_kernel");
 		} else {
 			CU(launch_resident(a, grid, st), "acc_resident_kernel");
 		}
@@ -1408,7 +1448,7 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	} else {
 		CU(launch_solve(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_kernel");
 	}
-	if (!fused || N > big_threshold) {
+	if (small_mode != 1 || N > big_threshold) {
 		RefineArgs ra;
 		ra.offsets = offsets;
 		ra.y = y;
@@ -2491,7 +2531,7 @@ int32_t anofox_b200_plan(int64_t n_groups, int64_t n_rows, int32_t n_features, i
                          int32_t *lanes_per_group) {
 	const SmallGeom sm = small_geometry(n_features, has_w != 0, has_train != 0, n_rows, n_groups);
 	if (lanes_per_group) *lanes_per_group = sm.use ? sm.T : 0;
-	return sm.use ? 1 : 0;
+	return sm.use ? (sm.stash ? 2 : 1) : 0;
 }
 
 // Test hook: evaluate the device special functions on arrays (host pointers).

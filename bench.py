@@ -35,6 +35,8 @@ WORKLOADS = {
     # name: (G, n, p, method, inference, options)
     "C1": (10_000, 100, 3, "ols", False, {}),
     "C2": (1_000_000, 50, 5, "ols", True, {}),
+    "C2n": (1_000_000, 50, 5, "ols", False, {}),  # experiments: C2 without inference
+    "C2a": (1_000_000, 48, 5, "ols", True, {}),   # experiments: 128-byte aligned groups
     "C3r": (1_000_000, 200, 16, "ridge", False, {"alpha": 1.0, "rank_deficient": True}),
     "C3w": (1_000_000, 200, 16, "wls", False, {"weights": True, "rank_deficient": True}),
     "C5": (100_000, 1_000, 8, "ols", False, {"holdout": 0.2, "predict": True}),
@@ -301,6 +303,8 @@ def load_traffic():
 
 NAMES = {"C1": "ols_fit_agg 10k groups x 100 rows x 3 features",
          "C2": "ols_fit_agg 1M groups x 50 rows x 5 features, full inference",
+         "C2n": "ols_fit_agg 1M groups x 50 rows x 5 features, no inference (experiment)",
+         "C2a": "ols_fit_agg 1M groups x 48 rows x 5 features (experiment: 128-byte aligned groups)",
          "C3r": "ridge_fit_agg(lambda=1) 1M groups x 200 rows x 16 features incl. rank-deficient groups",
          "C3w": "wls_fit_agg 1M groups x 200 rows x 16 features incl. rank-deficient groups",
          "C5": "ols_fit_predict_by 100k groups x 1k rows x 8 features, 20% held-out"}
@@ -439,9 +443,14 @@ def run_group_workload(args, wname, rank, world, local, steps, warmup, headline,
     inp, outb = algorithmic_bytes(G, N, p, method, inference, predict)
     acc_launch_ms = acc_ms / max(calls, 1)
     acc_bytes = N * (8 * (p + 1) + (8 if method == "wls" else 0)) + 8 * (G + 1)
-    achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
     path, lanes = pkg.plan(G, N, p, method == "wls", predict)
-    if path == "fused":
+    if path == "stash":
+        acc_bytes += outb  # the one-launch kernel also writes the result structs
+    achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
+    if path == "stash":
+        kname = "fit_small_stash_kernel<%d> (rows -> results in one launch: TMA-staged rows, %d lanes per group, " \
+                "sums parked in shared memory, thread-per-group solve in the same warps)" % (p, lanes)
+    elif path == "fused":
         kname = "fit_small_kernel<%d> (rows -> moment records, %d lanes per group, TMA-staged)" % (p, lanes)
     else:
         kname = "acc_ring_kernel (streaming ring of TMA windows, FP64 DMMA moment accumulation)"
@@ -477,6 +486,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the groups (smoke runs only)")
+    ap.add_argument("--path", default="auto", help="A/B runs: force a kernel path (anofox_b200_force_path names)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the other BASELINE configs after the headline")
@@ -543,6 +553,7 @@ def main():
     from __graft_entry__ import load_package
     pkg = load_package()
     pkg.device_check()
+    pkg.force_path(args.path)
     cache = {}
     r = run_group_workload(args, args.workload, rank, world, local, args.steps, args.warmup, True, cache)
     secondary = {}

@@ -43,3 +43,6 @@ ts = sum(v[1] for v in agg.values()) or 1
 print(f"\nwarp instructions {tot}, stall samples {ts}; top {top} source lines by instructions:")
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
     print(f"{v[0] / 1e6:9.2f}M {100 * v[0] / tot:5.1f}%  samples {100 * v[1] / ts:5.1f}%  {k[0]}:{k[1]}  {k[2]}")
+print(f"\ntop {top} source lines by stall samples:")
+for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1])[:top]:
+    print(f"{v[0] / 1e6:9.2f}M {100 * v[0] / tot:5.1f}%  samples {100 * v[1] / ts:5.1f}%  {k[0]}:{k[1]}  {k[2]}")
