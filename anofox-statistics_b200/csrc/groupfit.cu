@@ -28,6 +28,7 @@
 #include "solve.cuh"
 #include "specfun.cuh"
 #include "qr.cuh"
+#include "hc.cuh"
 
 namespace b200 {
 
@@ -1174,8 +1175,8 @@ static int validate_common(const int64_t *offsets, int64_t G, const double *y, c
 		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "weights is NULL");
 		return ANOFOX_ERROR_INVALID_INPUT;
 	}
-	if (opt->hc_type != ANOFOX_HC_NONE) {
-		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "hc_type: robust standard errors are outside the B200 path");
+	if (opt->hc_type < ANOFOX_HC_NONE || opt->hc_type > ANOFOX_HC_HC3) { // map_options_parser.cpp: "Invalid hc_type"
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "Invalid hc_type");
 		return ANOFOX_ERROR_INVALID_INPUT;
 	}
 	DeviceInfo &di = device_info();
@@ -1476,6 +1477,25 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		qa.list = all ? nullptr : ws.qr_list;
 		qa.n_all = G;
 		CU(launch_qr(qa, P, fo, (int)std::min<int64_t>(G, (int64_t)di.sms * 4), st), "qr_fit_kernel");
+	}
+	if (!pred && P.compute_inference && opt->hc_type != ANOFOX_HC_NONE && opt->method != ANOFOX_B200_RIDGE) {
+		// robust (sandwich) standard errors: a second pass over the rows with the coefficients just written
+		// (ols.rs:209-245, wls.rs:230-266; ridge has no hc_type, ridge.rs)
+		HcArgs ha;
+		ha.offsets = offsets;
+		ha.y = y;
+		ha.x = x;
+		ha.w = wuse;
+		ha.train = train_use;
+		ha.flags_from_y = y_only_flags ? 1 : 0;
+		ha.n_groups = G;
+		ha.hc_type = opt->hc_type;
+		const size_t dyn = hc_smem_bytes(p);
+		CU(cudaFuncSetAttribute(hc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn), "hc_kernel attr");
+		const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)200 * 1024 / (dyn + 1024)));
+		hc_kernel<<<(unsigned)std::min<int64_t>(G, (int64_t)di.sms * per_sm), kHcThreads, dyn, st>>>(ha, P, fo);
+		LAUNCHED();
+		CU(cudaGetLastError(), "hc_kernel");
 	}
 	timer_mark(st);
 

@@ -152,8 +152,9 @@ typedef struct {
  * outputs are malloc()ed here and released with the two free functions below.
  * out_inference may be NULL. When inference was requested but the model is the
  * intercept-only shortcut (all columns constant) the inference struct is zero-length with
- * NaN F statistics (lib.rs:251-253). hc_type != NONE is answered with INVALID_INPUT:
- * robust standard errors are outside this path (DESIGN.md "out of scope"). */
+ * NaN F statistics (lib.rs:251-253). hc_type HC0 .. HC3 (OLS / WLS, with compute_inference) replaces the
+ * standard errors, t, p and confidence bounds by their heteroscedasticity-consistent versions (ols.rs:209-245,
+ * wls.rs:230-266; csrc/hc.cuh); the F statistic stays classical, as in the reference. */
 bool anofox_ols_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxOlsOptions options,
                     AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference, AnofoxError *out_error);
 bool anofox_ridge_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxRidgeOptions options,
@@ -198,7 +199,8 @@ typedef struct {
 	int32_t solver;            /* AnofoxSolverType: accepted, all three must agree to 1e-10
 	                              (test_map_options.test); one device solver serves them */
 	int32_t lambda_scaling;    /* AnofoxLambdaScaling (ridge) */
-	int32_t hc_type;           /* must be ANOFOX_HC_NONE */
+	int32_t hc_type;           /* AnofoxHcType: robust standard errors for OLS / WLS (ignored by ridge, which
+	                              has no such option: ridge.rs); outside 0..4 -> INVALID_INPUT */
 	double confidence_level;
 	double alpha;              /* ridge penalty; < 0 -> INVALID_ALPHA for the whole call */
 } AnofoxB200FitOptions;

@@ -155,6 +155,7 @@ struct Opts {
 	double level;
 	double alpha;
 	int lambda_scaling;
+	int hc_type = 0; // AnofoxHcType: robust (sandwich) standard errors for OLS / WLS, ols.rs:209-245, wls.rs:230-266
 };
 
 struct GroupResult {
@@ -392,6 +393,10 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 	// the origin the factorisation used, so that a residual of 1e-6 next to features of 1e6 keeps its digits.
 	std::vector<R> cx(pe, 0);
 	R cy = 0, b0c = 0;
+	// kept for the sandwich estimator: R^-1 of the factorised (shifted) design, its column order and rank
+	std::vector<R> hc_rinv, hc_shift(pe, 0);
+	std::vector<size_t> hc_perm;
+	size_t hc_rank = 0;
 
 	if (lambda > 0.0) {
 		// Ridge (guides/02_technical_guide.md:129-138; validation/r_seesion_output.txt:668-671):
@@ -499,6 +504,10 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 			sol[0] = acc;
 		}
 		if (ic) b0 = sol[0]; // the intercept column is never negligible
+		hc_rinv = rinv;
+		hc_perm = perm;
+		hc_rank = rank;
+		hc_shift = shiftx;
 		for (size_t c = 0; c < pe; ++c) {
 			beta[c] = sol[c + ic];
 			vdiag[c] = vd[c + ic];
@@ -509,11 +518,13 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 
 	// Residuals from the raw rows (NaN coefficients contribute nothing)
 	R rss = 0;
+	std::vector<R> resid(nv);
 	for (size_t k = 0; k < nv; ++k) {
 		R fit = b0c;
 		for (size_t c = 0; c < pe; ++c)
 			if (!aliased[c]) fit += beta[c] * ((R)d.X(valid[k], keep[c]) - cx[c]);
 		R e = ((R)d.Y(valid[k]) - cy) - fit;
+		resid[k] = e;
 		rss += sqw[k] * sqw[k] * e * e;
 	}
 
@@ -540,9 +551,48 @@ template <class R> void fit_group(const Opts &o, const RowView &d, GroupResult &
 		R tcrit = std::numeric_limits<R>::quiet_NaN();
 		if (dfr > 0 && o.level > 0.0 && o.level < 1.0)
 			tcrit = memo ? memo->get(o.level, dfr) : t_quantile_upper<R>(((R)1 + (R)o.level) / 2, (R)dfr);
+		// Heteroscedasticity-consistent covariance (ols.rs:209-245 / wls.rs:230-266 -> upstream compute_hc_inference,
+		// source not vendored). Restated from the published estimators (MacKinnon & White 1985; R sandwich::vcovHC
+		// for weighted fits): V = (X'WX)^-1 [sum omega_i x~_i x~_i'] (X'WX)^-1 over the estimable columns incl. the
+		// intercept, x~ = sqrt(w) x, e~ = sqrt(w) e, h_i = x~_i'(X'WX)^-1 x~_i, omega_i = e~^2 (HC0), e~^2 n/(n-k)
+		// (HC1), e~^2/(1-h_i) (HC2), e~^2/(1-h_i)^2 (HC3). t, p and the interval use the same residual df; the F
+		// statistic stays the classical one (the reference passes result.f_statistic through). Ridge has no HC.
+		std::vector<R> vhc;
+		if (o.hc_type != 0 && lambda == 0.0 && hc_rank > 0) {
+			const size_t rk = hc_rank;
+			std::vector<R> S(rk * rk, 0), u(rk), z(rk);
+			for (size_t k = 0; k < nv; ++k) {
+				for (size_t r = 0; r < rk; ++r) {
+					const size_t j = hc_perm[r];
+					z[r] = (ic && j == 0) ? sqw[k] : sqw[k] * ((R)d.X(valid[k], keep[j - ic]) - hc_shift[j - ic]);
+				}
+				R h = 0;
+				for (size_t c = 0; c < rk; ++c) { // u = R^-T z
+					R t = 0;
+					for (size_t r = 0; r <= c; ++r) t += hc_rinv[c * rk + r] * z[r];
+					u[c] = t;
+					h += t * t;
+				}
+				R et = sqw[k] * resid[k], om = et * et;
+				if (o.hc_type == ANOFOX_HC_HC1) om *= (R)nv / (R)((double)nv - (double)rk);
+				else if (o.hc_type == ANOFOX_HC_HC2) om /= (1 - h);
+				else if (o.hc_type == ANOFOX_HC_HC3) om /= (1 - h) * (1 - h);
+				for (size_t a = 0; a < rk; ++a)
+					for (size_t b2 = 0; b2 < rk; ++b2) S[a * rk + b2] += om * u[a] * u[b2];
+			}
+			vhc.assign(pe, std::numeric_limits<R>::quiet_NaN());
+			for (size_t r = 0; r < rk; ++r) { // V_rr = sum_ab Rinv[r][a] S[a][b] Rinv[r][b], a, b >= r
+				const size_t j = hc_perm[r];
+				if (ic && j == 0) continue;
+				R v = 0;
+				for (size_t a = r; a < rk; ++a)
+					for (size_t b2 = r; b2 < rk; ++b2) v += hc_rinv[a * rk + r] * S[a * rk + b2] * hc_rinv[b2 * rk + r];
+				vhc[j - ic] = v;
+			}
+		}
 		for (size_t c = 0; c < pe; ++c) {
 			if (aliased[c]) continue;
-			R se = std::sqrt(sigma2 * vdiag[c]);
+			R se = vhc.empty() ? std::sqrt(sigma2 * vdiag[c]) : std::sqrt(vhc[c]);
 			R t = beta[c] / se;
 			size_t j = keep[c];
 			out.se[j] = (double)se;
@@ -689,7 +739,7 @@ void fit_batch(const int64_t *offsets, int64_t G, const double *y, const double 
                const AnofoxB200FitOptions *fo, const AnofoxB200FitOutputs *out, const uint8_t *train,
                const AnofoxB200PredictOutputs *pred, int threads) {
 	Opts o{fo->method, fo->fit_intercept != 0, fo->compute_inference != 0, fo->confidence_level, fo->alpha,
-	       fo->lambda_scaling};
+	       fo->lambda_scaling, fo->method == ANOFOX_B200_RIDGE ? 0 : fo->hc_type};
 	if (pred) o.compute_inference = false; // ols_predict_aggregate.cpp:354-364
 #ifdef _OPENMP
 	if (threads > 0) omp_set_num_threads(threads);
@@ -800,7 +850,8 @@ extern "C" {
 
 bool oracle_ols_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxOlsOptions options,
                     AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference, AnofoxError *out_error) {
-	Opts o{ANOFOX_B200_OLS, options.fit_intercept, options.compute_inference, options.confidence_level, 0.0, 0};
+	Opts o{ANOFOX_B200_OLS, options.fit_intercept, options.compute_inference, options.confidence_level, 0.0, 0,
+	       (int)options.hc_type};
 	return single_fit(o, y, x, x_count, nullptr, out_core, out_inference, out_error);
 }
 
@@ -814,7 +865,8 @@ bool oracle_ridge_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_coun
 bool oracle_wls_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxDataArray weights,
                     AnofoxWlsOptions options, AnofoxFitResultCore *out_core, AnofoxFitResultInference *out_inference,
                     AnofoxError *out_error) {
-	Opts o{ANOFOX_B200_WLS, options.fit_intercept, options.compute_inference, options.confidence_level, 0.0, 0};
+	Opts o{ANOFOX_B200_WLS, options.fit_intercept, options.compute_inference, options.confidence_level, 0.0, 0,
+	       (int)options.hc_type};
 	return single_fit(o, y, x, x_count, &weights, out_core, out_inference, out_error);
 }
 

@@ -103,9 +103,9 @@ def test_free_functions_null_the_pointers(lib):
     assert not core.coefficients and not inf.std_errors and not inf.ci_upper  # lib.rs:272-311
     l.anofox_free_result_core(None)  # NULL-safe
     l.anofox_free_result_inference(None)
-    # hc_type is outside the path
+    # an hc_type outside NONE .. HC3 is a call-level error ("Invalid hc_type", map_options_parser.cpp)
     ok = l.anofox_ols_fit(A.DataArray(y.ctypes.data_as(A.c_double_p), None, 5), xs, 1,
-                          A.OlsOptions(True, True, 0.95, 1, 2), C.byref(core), C.byref(inf), C.byref(err))
+                          A.OlsOptions(True, True, 0.95, 1, 7), C.byref(core), C.byref(inf), C.byref(err))
     assert not ok and err.code == A.INVALID_INPUT
 
 
