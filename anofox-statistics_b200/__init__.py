@@ -69,6 +69,17 @@ def load_library():
                                                                 C.POINTER(abi.B200FitOptions),
                                                                 C.POINTER(abi.B200PredictOutputs),
                                                                 C.POINTER(abi.B200FitOutputs), E]
+    lib.anofox_b200_window_workspace_bytes.restype = C.c_size_t
+    lib.anofox_b200_window_workspace_bytes.argtypes = [C.c_int64, C.c_int32]
+    lib.anofox_b200_window_fit_predict_host.restype = C.c_int32
+    lib.anofox_b200_window_fit_predict_host.argtypes = common + [C.c_int64, C.c_int32, C.POINTER(abi.B200FitOptions),
+                                                                 C.c_int64, C.c_int64,
+                                                                 C.POINTER(abi.B200PredictOutputs), E]
+    lib.anofox_b200_window_fit_predict_device.restype = C.c_int32
+    lib.anofox_b200_window_fit_predict_device.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                          C.c_int64, C.c_int32, C.POINTER(abi.B200FitOptions),
+                                                          C.c_int64, C.c_int64, C.POINTER(abi.B200PredictOutputs),
+                                                          C.c_void_p, C.c_size_t, C.c_void_p, E]
     lib.anofox_b200_moment_block_len.restype = C.c_size_t
     lib.anofox_b200_moment_block_len.argtypes = [C.c_int32]
     lib.anofox_b200_first_valid_row_device.restype = C.c_int32
@@ -200,6 +211,39 @@ def fit_predict_batch_host(offsets, y, x, w=None, train=None, **opt):
                                                            C.byref(o), C.byref(ps), C.byref(fs), C.byref(err))
     _check(rc, err)
     return pred, fit
+
+
+def window_fit_predict_host(offsets, y, x, w=None, preceding=-1, end_offset=1, **opt):
+    """{ols,ridge,wls}_fit_predict(...) OVER (PARTITION BY g ORDER BY t ROWS BETWEEN <preceding> AND <end>) for
+    every row of every partition (src/window_functions/ols_fit_predict.cpp). preceding < 0 = UNBOUNDED PRECEDING;
+    end_offset 0 = CURRENT ROW, 1 = 1 PRECEDING. Returns dict(yhat, yhat_lower, yhat_upper); NaN = NULL."""
+    offsets, y, x, w, N, p = _prep(offsets, y, x, w)
+    G = len(offsets) - 1
+    o = abi.make_fit_options(**opt)
+    pred, ps = abi.alloc_predict_outputs_numpy(N)
+    err = abi.AnofoxError()
+    rc = load_library().anofox_b200_window_fit_predict_host(abi.np_ptr(offsets, C.c_int64), G,
+                                                            abi.np_ptr(y, C.c_double), abi.np_ptr(x, C.c_double),
+                                                            abi.np_ptr(w, C.c_double), N, p, C.byref(o),
+                                                            int(preceding), int(end_offset), C.byref(ps), C.byref(err))
+    _check(rc, err)
+    pred.pop("is_training", None)
+    return pred
+
+
+def window_workspace_bytes(N, p):
+    return int(load_library().anofox_b200_window_workspace_bytes(N, p))
+
+
+def window_fit_predict_device(offsets, y, x, w, N, G, p, pred_struct, workspace, workspace_bytes, stream=0,
+                              preceding=-1, end_offset=1, **opt):
+    """Device-pointer form (raw addresses; torch owns the memory)."""
+    o = abi.make_fit_options(**opt)
+    err = abi.AnofoxError()
+    rc = load_library().anofox_b200_window_fit_predict_device(offsets, G, y, x, w, N, p, C.byref(o), int(preceding),
+                                                              int(end_offset), C.byref(pred_struct), workspace,
+                                                              workspace_bytes, stream, C.byref(err))
+    _check(rc, err)
 
 
 # ---------------------------------------------------------------------------------------------

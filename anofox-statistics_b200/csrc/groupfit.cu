@@ -29,6 +29,8 @@
 #include "specfun.cuh"
 #include "qr.cuh"
 #include "hc.cuh"
+#include "window.cuh"
+#include "window_launch.h"
 
 namespace b200 {
 
@@ -1955,6 +1957,147 @@ static bool single_fit(int method, AnofoxDataArray y, const AnofoxDataArray *x, 
 	return true;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Window form of the fit-predict aggregates (window.cuh)
+// ---------------------------------------------------------------------------------------------
+static size_t window_scratch(AnofoxB200FitOutputs &o, unsigned char *base, int64_t N, int p) {
+	size_t off = 0;
+	auto take = [&](size_t bytes) {
+		size_t at = off;
+		off += (bytes + 255) & ~(size_t)255;
+		return base ? base + at : (unsigned char *)nullptr;
+	};
+	const size_t n1 = (size_t)std::max<int64_t>(N, 1);
+	memset(&o, 0, sizeof o);
+	o.coefficients = (double *)take(n1 * p * 8);
+	o.intercept = (double *)take(n1 * 8);
+	o.r_squared = (double *)take(n1 * 8);
+	o.adj_r_squared = (double *)take(n1 * 8);
+	o.residual_std_error = (double *)take(n1 * 8);
+	o.n_observations = (int64_t *)take(n1 * 8);
+	o.status = (int32_t *)take(n1 * 4);
+	return off;
+}
+
+static int window_device(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w, int64_t N,
+                         int p, const AnofoxB200FitOptions *opt, int64_t preceding, int64_t end_offset,
+                         const AnofoxB200PredictOutputs *pred, void *workspace, size_t workspace_bytes, cudaStream_t st,
+                         AnofoxError *err) {
+	if (p > kWindowMaxFeatures) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "the window form supports up to 8 features");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (end_offset < 0) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "frame end must be CURRENT ROW (0) or k PRECEDING (k > 0)");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	// the scan serves expanding frames that end at the current or the previous row; an expanding frame that ends
+	// further back is summed directly like a bounded one
+	if (preceding < 0 && end_offset > 1) preceding = (int64_t)1 << 60;
+	if (!pred || !pred->yhat || !pred->yhat_lower || !pred->yhat_upper) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "prediction outputs are NULL");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	AnofoxB200FitOutputs scratch;
+	const size_t need = window_scratch(scratch, (unsigned char *)workspace, N, p);
+	if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 255)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "workspace too small or misaligned (anofox_b200_window_workspace_bytes)");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (G == 0 || N == 0) return 0;
+	DeviceInfo &di = device_info();
+	const bool wls = opt->method == ANOFOX_B200_WLS;
+	FitParams P;
+	P.p = p;
+	P.method = opt->method;
+	P.fit_intercept = opt->fit_intercept != 0;
+	P.compute_inference = 0; // ols_fit_predict.cpp:281
+	P.lambda_scaling = opt->lambda_scaling;
+	P.level = opt->confidence_level;
+	P.alpha = opt->alpha;
+	P.predict_mode = 1;
+	P.min_state_rows = 0; // the window form has its own "more than p + intercept training rows" rule
+	P.qr_count = nullptr;
+	P.qr_list = nullptr;
+	DfTables T;
+	const int trc = get_tables(P.level, st, T, err);
+	if (trc) return trc;
+	P.tcrit = T.tcrit;
+	P.gratio = T.gratio;
+	P.rcp = T.rcp;
+	P.ce = T.ce;
+	P.co = T.co;
+	WindowArgs a;
+	a.offsets = offsets;
+	a.y = y;
+	a.x = x;
+	a.w = wls ? w : nullptr;
+	a.n_groups = G;
+	a.preceding = preceding;
+	a.end_offset = end_offset;
+	a.yhat = pred->yhat;
+	a.lower = pred->yhat_lower;
+	a.upper = pred->yhat_upper;
+	const int64_t warps = std::min<int64_t>(G, (int64_t)di.sms * 16);
+	CU(launch_window(p, wls, a, P, scratch, (int)((warps + 3) / 4), st), "window_fit_predict_kernel");
+	LAUNCHED();
+	return 0;
+}
+
+static int window_host(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w, int64_t N, int p,
+                       const AnofoxB200FitOptions *opt, int64_t preceding, int64_t end_offset,
+                       const AnofoxB200PredictOutputs *pred, AnofoxError *err) {
+	if (G > 0) {
+		bool ok = offsets[0] == 0 && offsets[G] == N;
+		for (int64_t g = 0; ok && g < G; ++g) ok = offsets[g] <= offsets[g + 1];
+		if (!ok) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "offsets must start at 0, be non-decreasing and end at n_rows");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+	}
+	if (!pred || !pred->yhat || !pred->yhat_lower || !pred->yhat_upper) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "prediction outputs are NULL");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	HostLease lease;
+	HostContext &c = *lease.c;
+	DrainGuard drain{c};
+	AnofoxB200FitOutputs tmp;
+	const size_t ws_bytes = window_scratch(tmp, nullptr, N, p);
+	DevLayout L;
+	const int64_t N1 = std::max<int64_t>(N, 1);
+	const size_t o_off = L.take((size_t)(G + 1) * 8), o_y = L.take((size_t)N1 * 8), o_x = L.take((size_t)N1 * p * 8);
+	const size_t o_w = w ? L.take((size_t)N1 * 8) : 0;
+	const size_t o_pred = L.take((size_t)N1 * 8 * 3);
+	const size_t o_ws = L.take(ws_bytes);
+	int rc = c.ensure(L.off, err);
+	if (rc) return rc;
+	unsigned char *d = c.dev;
+	cudaStream_t st = c.stream;
+	CU(cudaMemcpyAsync(d + o_off, offsets, (size_t)(G + 1) * 8, cudaMemcpyHostToDevice, st), "H2D offsets");
+	if (N > 0) {
+		CU(cudaMemcpyAsync(d + o_y, y, (size_t)N * 8, cudaMemcpyHostToDevice, st), "H2D y");
+		CU(cudaMemcpyAsync(d + o_x, x, (size_t)N * p * 8, cudaMemcpyHostToDevice, st), "H2D x");
+		if (w) CU(cudaMemcpyAsync(d + o_w, w, (size_t)N * 8, cudaMemcpyHostToDevice, st), "H2D w");
+	}
+	AnofoxB200PredictOutputs dp;
+	memset(&dp, 0, sizeof dp);
+	dp.yhat = (double *)(d + o_pred);
+	dp.yhat_lower = dp.yhat + N1;
+	dp.yhat_upper = dp.yhat + 2 * N1;
+	rc = window_device((const int64_t *)(d + o_off), G, (const double *)(d + o_y), (const double *)(d + o_x),
+	                   w ? (const double *)(d + o_w) : nullptr, N, p, opt, preceding, end_offset, &dp, d + o_ws, ws_bytes, st,
+	                   err);
+	if (rc) return rc;
+	if (N > 0) {
+		CU(cudaMemcpyAsync(pred->yhat, dp.yhat, (size_t)N * 8, cudaMemcpyDeviceToHost, st), "D2H");
+		CU(cudaMemcpyAsync(pred->yhat_lower, dp.yhat_lower, (size_t)N * 8, cudaMemcpyDeviceToHost, st), "D2H");
+		CU(cudaMemcpyAsync(pred->yhat_upper, dp.yhat_upper, (size_t)N * 8, cudaMemcpyDeviceToHost, st), "D2H");
+	}
+	CU(cudaStreamSynchronize(st), "sync");
+	return 0;
+}
+
 static int eval_specfun_host(int mode, int n, const double *a, const double *b, const double *c, double *out,
                              AnofoxError *err) {
 	clear_error(err);
@@ -2192,6 +2335,41 @@ size_t anofox_b200_moment_block_len(int32_t n_features) {
 	if (n_features <= 0 || n_features > kMaxFeatures) return 0;
 	const int k = n_features + 1;
 	return (size_t)(4 + k + k * (k + 1) / 2);
+}
+
+size_t anofox_b200_window_workspace_bytes(int64_t n_rows, int32_t n_features) {
+	AnofoxB200FitOutputs tmp;
+	return window_scratch(tmp, nullptr, n_rows, n_features);
+}
+
+int32_t anofox_b200_window_fit_predict_device(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
+                                              const double *w, int64_t n_rows, int32_t n_features,
+                                              const AnofoxB200FitOptions *options, int64_t frame_preceding,
+                                              int64_t frame_end_offset, const AnofoxB200PredictOutputs *pred,
+                                              void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err) {
+	return guarded(err, "window_fit_predict_device", [&]() -> int32_t {
+		int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+		if (rc) return rc;
+		return window_device(offsets, n_groups, y, x, w, n_rows, n_features, options, frame_preceding, frame_end_offset, pred,
+		                     workspace, workspace_bytes, (cudaStream_t)stream, err);
+	});
+}
+
+int32_t anofox_b200_window_fit_predict_host(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
+                                            const double *w, int64_t n_rows, int32_t n_features,
+                                            const AnofoxB200FitOptions *options, int64_t frame_preceding,
+                                            int64_t frame_end_offset, const AnofoxB200PredictOutputs *pred,
+                                            AnofoxError *err) {
+	return guarded(err, "window_fit_predict_host", [&]() -> int32_t {
+		int rc = validate_common(offsets, n_groups, y, x, w, n_rows, n_features, options, err);
+		if (rc) return rc;
+		if (n_features > kWindowMaxFeatures) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "the window form supports up to 8 features");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		return window_host(offsets, n_groups, y, x, w, n_rows, n_features, options, frame_preceding, frame_end_offset, pred,
+		                   err);
+	});
 }
 
 int32_t anofox_b200_first_valid_row_device(const double *y, const double *x, const double *w, int64_t n_rows,

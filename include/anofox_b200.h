@@ -293,6 +293,32 @@ int32_t anofox_b200_fit_predict_batch_host(const int64_t *offsets, int64_t n_gro
                                            const AnofoxB200PredictOutputs *pred, const AnofoxB200FitOutputs *fit,
                                            AnofoxError *err);
 
+/* Window form of the fit-predict aggregates:
+ *   {ols,ridge,wls}_fit_predict(y, x [, w], opts) OVER (PARTITION BY g ORDER BY t ROWS BETWEEN <start> AND <end>)
+ * (src/window_functions/ols_fit_predict.cpp:111-326, ridge_fit_predict.cpp, wls_fit_predict.cpp). DuckDB runs
+ * the aggregate once per output row over that row's frame; here the partitions arrive as a group-sorted CSR in
+ * ORDER BY order (offsets[G+1]) and every row gets its answer in one call:
+ *   frame of row i = rows [i - frame_preceding, i - frame_end_offset] of its partition;
+ *   frame_preceding < 0 = UNBOUNDED PRECEDING (expanding frame, prefix scan of the moment sums);
+ *   frame_end_offset    = 0 (CURRENT ROW) or k (k PRECEDING; 1 PRECEDING is the frame of the reference's headline
+ *                         benchmark, examples/performance_1m_groups/benchmark_ols.sql:17-19).
+ * A row trains when y (and w for WLS) is non-NaN; the answer is the NaN triple (= NULL struct) when the frame is
+ * empty, holds at most n_features + intercept training rows (ols_fit_predict.cpp:258-262) or the fit fails
+ * (:289-292); otherwise the model is fitted without inference and evaluated, with the simplified interval of
+ * anofox_predict_with_interval, at the x of the frame's LAST row (:157-163). pred->is_training is not written.
+ * n_features <= 8. null_policy 'drop_y_zero_x' is the caller's business (set y of those rows to NaN). */
+size_t anofox_b200_window_workspace_bytes(int64_t n_rows, int32_t n_features);
+int32_t anofox_b200_window_fit_predict_device(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
+                                              const double *w, int64_t n_rows, int32_t n_features,
+                                              const AnofoxB200FitOptions *options, int64_t frame_preceding,
+                                              int64_t frame_end_offset, const AnofoxB200PredictOutputs *pred,
+                                              void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err);
+int32_t anofox_b200_window_fit_predict_host(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
+                                            const double *w, int64_t n_rows, int32_t n_features,
+                                            const AnofoxB200FitOptions *options, int64_t frame_preceding,
+                                            int64_t frame_end_offset, const AnofoxB200PredictOutputs *pred,
+                                            AnofoxError *err);
+
 /* Row-sharded single group (config "1 B rows x 64 features over 8 GPUs").
  * Step 0, per rank: anofox_b200_first_valid_row_device finds the first row of this rank's shard that
  *   passes the reference's row filter (ols.rs:59-66, wls.rs:76-86) and writes it to shift_out[p+1]

@@ -846,6 +846,63 @@ void fit_batch(const int64_t *offsets, int64_t G, const double *y, const double 
 
 } // namespace
 
+// ---------------------------------------------------------------------------------------------
+// Window form: {ols,ridge,wls}_fit_predict(y, x, ...) OVER (PARTITION BY g ORDER BY t ROWS BETWEEN ...)
+// (src/window_functions/ols_fit_predict.cpp:111-326; ridge / wls analogous). For every output row DuckDB runs the
+// aggregate over the row's frame: Update keeps the rows with a non-NULL y as training data (:165-190) and
+// remembers the x of the LAST frame row (:157-163); Finalize (:243-326) answers NULL when no frame row carried an
+// x list or when the training rows are <= p + intercept, fits WITHOUT inference, and predicts at the remembered
+// x with the simplified interval of anofox_predict_with_interval. Restated literally: one raw-row fit per output
+// row. frame: rows [i - preceding, i - end_offset] of the partition (preceding < 0: unbounded).
+// ---------------------------------------------------------------------------------------------
+template <class R>
+void window_fit_predict(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w, int32_t p,
+                        const AnofoxB200FitOptions *fo, int64_t preceding, int64_t end_offset,
+                        const AnofoxB200PredictOutputs *pred, int threads) {
+	Opts o{fo->method, fo->fit_intercept != 0, false, fo->confidence_level, fo->alpha, fo->lambda_scaling, 0};
+	const bool wls = fo->method == ANOFOX_B200_WLS;
+#ifdef _OPENMP
+	if (threads > 0) omp_set_num_threads(threads);
+#pragma omp parallel for schedule(dynamic, 4)
+#endif
+	for (int64_t g = 0; g < G; ++g) {
+		const int64_t r0 = offsets[g], r1 = offsets[g + 1];
+		for (int64_t r = r0; r < r1; ++r) {
+			pred->yhat[r] = pred->yhat_lower[r] = pred->yhat_upper[r] = kNaN;
+			const int64_t hi = r - end_offset;
+			int64_t lo = preceding < 0 ? r0 : r - preceding;
+			if (lo < r0) lo = r0;
+			if (hi < lo) continue; // empty frame: the state was never initialised
+			std::vector<double> ty, tx, tw;
+			for (int64_t q = lo; q <= hi; ++q) {
+				bool tr = !std::isnan(y[q]);               // y IS NOT NULL (:170-172)
+				if (wls && w) tr = tr && !std::isnan(w[q]); // wls_fit_predict.cpp: weight must be present
+				if (!tr) continue;
+				ty.push_back(y[q]);
+				for (int32_t j = 0; j < p; ++j) tx.push_back(x[q * p + j]);
+				if (w) tw.push_back(w[q]);
+			}
+			const size_t min_obs = (size_t)p + (o.fit_intercept ? 1 : 0);
+			if (ty.size() <= min_obs) continue; // :258-262
+			RowView d;
+			d.p = (size_t)p;
+			d.y = ty.data();
+			d.xrm = tx.data();
+			d.w = w ? tw.data() : nullptr;
+			d.n = ty.size();
+			GroupResult res;
+			fit_group<R>(o, d, res, nullptr);
+			if (res.code != 0) continue; // :289-292
+			AnofoxPredictionResult pr;
+			predict_row<R>(res.coef.data(), (size_t)p, res.intercept, x + hi * p, res.rse, res.n_obs, o.level, kNaN, &pr);
+			pred->yhat[r] = pr.yhat;
+			pred->yhat_lower[r] = pr.yhat_lower;
+			pred->yhat_upper[r] = pr.yhat_upper;
+		}
+	}
+}
+
+
 extern "C" {
 
 bool oracle_ols_fit(AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count, AnofoxOlsOptions options,
@@ -956,6 +1013,19 @@ int32_t oracle_fit_predict_batch(const int64_t *offsets, int64_t n_groups, const
 		fit_batch<long double>(offsets, n_groups, y, x, w, n_features, options, fit, train, pred, threads);
 	else
 		fit_batch<double>(offsets, n_groups, y, x, w, n_features, options, fit, train, pred, threads);
+	return 0;
+}
+
+int32_t oracle_window_fit_predict(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
+                                  const double *w, int64_t n_rows, int32_t n_features,
+                                  const AnofoxB200FitOptions *options, int64_t preceding, int64_t end_offset,
+                                  const AnofoxB200PredictOutputs *pred, int32_t precision, int32_t threads) {
+	(void)n_rows;
+	if (precision == 1)
+		window_fit_predict<double>(offsets, n_groups, y, x, w, n_features, options, preceding, end_offset, pred, threads);
+	else
+		window_fit_predict<long double>(offsets, n_groups, y, x, w, n_features, options, preceding, end_offset, pred,
+		                                threads);
 	return 0;
 }
 

@@ -48,6 +48,11 @@ def lib():
                                                   abi.c_double_p, abi.c_uint8_p, C.c_int64, C.c_int32,
                                                   C.POINTER(abi.B200FitOptions), C.POINTER(abi.B200PredictOutputs),
                                                   C.POINTER(abi.B200FitOutputs), C.c_int32, C.c_int32]
+        _LIB.oracle_window_fit_predict.restype = C.c_int32
+        _LIB.oracle_window_fit_predict.argtypes = [abi.c_int64_p, C.c_int64, abi.c_double_p, abi.c_double_p,
+                                                   abi.c_double_p, C.c_int64, C.c_int32,
+                                                   C.POINTER(abi.B200FitOptions), C.c_int64, C.c_int64,
+                                                   C.POINTER(abi.B200PredictOutputs), C.c_int32, C.c_int32]
         _LIB.oracle_max_threads.restype = C.c_int32
     return _LIB
 
@@ -114,6 +119,20 @@ def fit_predict_batch(offsets, y, x, w=None, train=None, precision=0, threads=0,
                                         precision, threads)
     pred["rc"] = rc
     return pred, fit
+
+
+def window_fit_predict(offsets, y, x, w=None, preceding=-1, end_offset=1, precision=0, threads=0, **opt):
+    """One raw-row fit per output row over its frame (src/window_functions/ols_fit_predict.cpp)."""
+    offsets, y, x, w, N, p = _prep(offsets, y, x, w)
+    G = len(offsets) - 1
+    o = abi.make_fit_options(**opt)
+    pred, ps = abi.alloc_predict_outputs_numpy(N)
+    rc = lib().oracle_window_fit_predict(abi.np_ptr(offsets, C.c_int64), G, abi.np_ptr(y, C.c_double),
+                                         abi.np_ptr(x, C.c_double), abi.np_ptr(w, C.c_double), N, p, C.byref(o),
+                                         int(preceding), int(end_offset), C.byref(ps), precision, threads)
+    pred["rc"] = rc
+    pred.pop("is_training", None)
+    return pred
 
 
 def max_threads():
