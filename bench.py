@@ -310,6 +310,66 @@ NAMES = {"C1": "ols_fit_agg 10k groups x 100 rows x 3 features",
          "C5": "ols_fit_predict_by 100k groups x 1k rows x 8 features, 20% held-out"}
 
 
+def run_window_workload(args, rank, world, local, steps, warmup, G=1_000_000, n=100, p=3):
+    """The reference's own headline benchmark (examples/performance_1m_groups/benchmark_ols.sql:6-22):
+    ols_fit_predict(y, [x1, x2, x3]) OVER (PARTITION BY g ORDER BY t ROWS BETWEEN UNBOUNDED PRECEDING AND 1 PRECEDING)
+    over 1 M partitions x 100 rows = 100 M predictions; published there: 178.6 s (other hardware, DuckDB CPU)."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from importlib import import_module
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    synth = import_module("anofox_statistics_b200.synth")
+    G = max(64, int(G * args.scale))
+    N = G * n
+    d = synth.make_torch(G, n, p, seed=11 + rank)
+    out = {k: torch.empty(N, dtype=torch.float64, device="cuda") for k in ("yhat", "yhat_lower", "yhat_upper")}
+    ps = pkg.abi.B200PredictOutputs()
+    for nm, ctype in pkg.abi.B200PredictOutputs._fields_:
+        setattr(ps, nm, C.cast(out[nm].data_ptr(), ctype) if nm in out else None)
+    wsb = pkg.window_workspace_bytes(N, p)
+    ws = torch.empty(wsb + 256, dtype=torch.uint8, device="cuda")
+    wp = (ws.data_ptr() + 255) & ~255
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        pkg.window_fit_predict_device(d["offsets"].data_ptr(), d["y"].data_ptr(), d["x"].data_ptr(), None, N, G, p, ps,
+                                      wp, wsb, stream, preceding=-1, end_offset=1, method="ols")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        step()
+    barrier()
+    l0 = pkg.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    n_pred = int(torch.isfinite(out["yhat"]).sum().item())
+    res = {"workload": "ols_fit_predict OVER (PARTITION BY g ORDER BY t ROWS BETWEEN UNBOUNDED PRECEDING AND 1 PRECEDING), "
+                       "%d partitions x %d rows x %d features" % (G, n, p),
+           "ms_per_step": ms, "predictions_per_sec": world * N / (ms * 1e-3), "rows": N, "non_null_predictions": n_pred,
+           "steps": steps, "gpu_launches": pkg.launch_count() - l0,
+           "algorithmic_bytes": N * (8 * (p + 1) + 24) + 8 * (G + 1),
+           "frac_of_hbm_peak": (N * (8 * (p + 1) + 24) + 8 * (G + 1)) / (ms * 1e-3) / 1e9 / measured_peak_gbs()[0],
+           "reference_published_s": 178.6,
+           "reference_published_note": "examples/performance_1m_groups/README.md (DuckDB CPU, other hardware)"}
+    del d, out, ws
+    torch.cuda.empty_cache()
+    return res if rank == 0 else None
+
+
 def run_group_workload(args, wname, rank, world, local, steps, warmup, headline, data_cache=None):
     """One group-sharded workload on this rank (weak scaling: every rank fits its own copy of the shape).
     Returns the result dict on rank 0 (None elsewhere)."""
@@ -484,7 +544,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS) + ["W1"])
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the groups (smoke runs only)")
     ap.add_argument("--path", default="auto", help="A/B runs: force a kernel path (anofox_b200_force_path names)")
     ap.add_argument("--no-e2e", action="store_true")
@@ -503,6 +563,18 @@ def main():
         if world > 1:
             dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         line = run_c4(args, rank, world, local)
+        if rank == 0:
+            emit(line)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    if args.workload == "W1" and args.impl == "ours":
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        if world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        line = run_window_workload(args, rank, world, local, args.steps, args.warmup)
         if rank == 0:
             emit(line)
         if world > 1:
@@ -572,6 +644,9 @@ def main():
                                  "groups_fitted_ok": s["groups_fitted_ok"], "clocks": s["clocks"]}
         cache.clear()
         torch.cuda.empty_cache()
+        wres = run_window_workload(args, rank, world, local, 3, 3)
+        if rank == 0:
+            secondary["W1"] = wres
         if world > 1:
             # C4: the single huge group, 125 M rows x 64 features per GPU, three NCCL collectives per fit
             a4 = argparse.Namespace(**vars(args))
