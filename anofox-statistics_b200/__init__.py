@@ -69,6 +69,21 @@ def load_library():
                                                                 C.POINTER(abi.B200FitOptions),
                                                                 C.POINTER(abi.B200PredictOutputs),
                                                                 C.POINTER(abi.B200FitOutputs), E]
+    lib.anofox_b200_ingest_workspace_bytes.restype = C.c_size_t
+    lib.anofox_b200_ingest_workspace_bytes.argtypes = [C.c_int64, C.c_int64]
+    lib.anofox_b200_ingest_device.restype = C.c_int32
+    lib.anofox_b200_ingest_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_size_t, C.c_void_p, E]
+    lib.anofox_b200_ingest_bad_ids.restype = C.c_int32
+    lib.anofox_b200_ingest_bad_ids.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+    lib.anofox_b200_fit_columns_workspace_bytes.restype = C.c_size_t
+    lib.anofox_b200_fit_columns_workspace_bytes.argtypes = [C.c_int64, C.c_int64, C.c_int32]
+    lib.anofox_b200_fit_columns_batch_device.restype = C.c_int32
+    lib.anofox_b200_fit_columns_batch_device.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                         C.c_int64, C.c_int32, C.POINTER(abi.B200FitOptions),
+                                                         C.POINTER(abi.B200FitOutputs), C.c_void_p, C.c_size_t,
+                                                         C.c_void_p, E]
     lib.anofox_b200_window_workspace_bytes.restype = C.c_size_t
     lib.anofox_b200_window_workspace_bytes.argtypes = [C.c_int64, C.c_int32]
     lib.anofox_b200_window_fit_predict_host.restype = C.c_int32
@@ -231,6 +246,39 @@ def window_fit_predict_host(offsets, y, x, w=None, preceding=-1, end_offset=1, *
     return pred
 
 
+class DeviceIngest:
+    """Unsorted (group_id, y, x[, w]) rows -> group-sorted CSR on the device (include/anofox_b200.h, csrc/ingest.cuh).
+    torch owns the buffers; the partition itself is the library's radix kernels."""
+
+    def __init__(self, N, p, G, weights=False, device="cuda"):
+        import torch
+        self.torch, self.N, self.p, self.G = torch, N, p, G
+        dev = torch.device(device)
+        self.offsets = torch.empty(G + 1, dtype=torch.int64, device=dev)
+        self.y = torch.empty(N, dtype=torch.float64, device=dev)
+        self.x = torch.empty((N, p), dtype=torch.float64, device=dev)
+        self.w = torch.empty(N, dtype=torch.float64, device=dev) if weights else None
+        self.row_index = torch.empty(N, dtype=torch.int64, device=dev)
+        self.ws_bytes = load_library().anofox_b200_ingest_workspace_bytes(N, G)
+        self.ws = torch.empty(self.ws_bytes + 256, dtype=torch.uint8, device=dev)
+        self.ws_ptr = (self.ws.data_ptr() + 255) & ~255
+
+    def run(self, group_ids, y, x, w=None, stream=None):
+        torch = self.torch
+        err = abi.AnofoxError()
+        st = torch.cuda.current_stream().cuda_stream if stream is None else stream
+        p = lambda t: None if t is None else C.c_void_p(t.data_ptr())  # noqa: E731
+        rc = load_library().anofox_b200_ingest_device(p(group_ids), p(y), p(x), p(w), self.N, self.p, self.G, p(self.offsets),
+                                                      p(self.y), p(self.x), p(self.w) if w is not None else None,
+                                                      p(self.row_index), C.c_void_p(self.ws_ptr), self.ws_bytes,
+                                                      C.c_void_p(st), C.byref(err))
+        _check(rc, err)
+        return self
+
+    def bad_ids(self):
+        return int(load_library().anofox_b200_ingest_bad_ids(C.c_void_p(self.ws_ptr), self.N, self.G))
+
+
 def window_workspace_bytes(N, p):
     return int(load_library().anofox_b200_window_workspace_bytes(N, p))
 
@@ -303,6 +351,26 @@ class DeviceFit:
                                                          self._ptr(w), self.N, self.p, C.byref(o),
                                                          C.byref(self.out_struct), C.c_void_p(self.ws_ptr),
                                                          self.ws_bytes, C.c_void_p(st), C.byref(err))
+        _check(rc, err)
+        return self.out
+
+    def fit_columns(self, offsets, y, x_columns, w=None, stream=None, **opt):
+        """Batched scalar array fits ({ols,ridge,wls}_fit(y LIST, x LIST(LIST))): x_columns holds, per fit, p columns
+        of n_i values back to back (include/anofox_b200.h). G = number of fits."""
+        torch = self.torch
+        lib = load_library()
+        need = lib.anofox_b200_fit_columns_workspace_bytes(self.G, self.N, self.p)
+        if getattr(self, "_cws_bytes", 0) < need:
+            self._cws = torch.empty(need + 256, dtype=torch.uint8, device=y.device)
+            self._cws_ptr = (self._cws.data_ptr() + 255) & ~255
+            self._cws_bytes = need
+        o = abi.make_fit_options(**opt)
+        err = abi.AnofoxError()
+        st = torch.cuda.current_stream().cuda_stream if stream is None else stream
+        rc = lib.anofox_b200_fit_columns_batch_device(self._ptr(offsets), self.G, self._ptr(y), self._ptr(x_columns),
+                                                      self._ptr(w), self.N, self.p, C.byref(o), C.byref(self.out_struct),
+                                                      C.c_void_p(self._cws_ptr), self._cws_bytes, C.c_void_p(st),
+                                                      C.byref(err))
         _check(rc, err)
         return self.out
 

@@ -31,6 +31,7 @@
 #include "hc.cuh"
 #include "window.cuh"
 #include "window_launch.h"
+#include "ingest.cuh"
 
 namespace b200 {
 
@@ -1642,6 +1643,24 @@ __global__ void rebase_offsets_kernel(const int64_t *__restrict__ in, int64_t n,
 	if (i < n) out[i] = in[i] - r0;
 }
 
+// Column-major-per-fit -> row-major rows (the scalar array fits: ols_fit(y LIST, x LIST(LIST)), one fit per SQL row,
+// src/table_functions/ols_fit.cpp:120-173). Fit i owns rows [offsets[i], offsets[i+1]); its block of the input holds
+// column 0, column 1, ... each of n_i values. One warp per fit, reads coalesced along the block.
+__global__ void columns_to_rows_kernel(const int64_t *__restrict__ offsets, int64_t n_fits, const double *__restrict__ xc, int p,
+                                       double *__restrict__ xr) {
+	const int lane = threadIdx.x & 31;
+	const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+	for (int64_t f = wid; f < n_fits; f += nw) {
+		const int64_t r0 = offsets[f], n = offsets[f + 1] - r0;
+		const double *src = xc + r0 * p;
+		double *dst = xr + r0 * p;
+		for (int64_t e = lane; e < n * p; e += 32) {
+			const int64_t j = e / n, k = e - j * n;
+			dst[k * p + j] = src[e];
+		}
+	}
+}
+
 static int fit_host(const int64_t *offsets, int64_t G, const double *y, const double *x, const double *w,
                     const uint8_t *train, int64_t N, int p, const AnofoxB200FitOptions *opt,
                     const AnofoxB200FitOutputs *out, const AnofoxB200PredictOutputs *pred, AnofoxError *err,
@@ -1955,6 +1974,132 @@ static bool single_fit(int method, AnofoxDataArray y, const AnofoxDataArray *x, 
 		}
 	}
 	return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Scalar array fits, batched over the SQL rows of a DataChunk: {ols,ridge,wls}_fit(y LIST, x LIST(LIST) [, w LIST])
+// (src/table_functions/{ols,ridge,wls}_fit.cpp:120-230: one anofox_*_fit call per row there)
+// ---------------------------------------------------------------------------------------------
+static int fit_columns_device(const int64_t *offsets, int64_t F, const double *y, const double *x_cm, const double *w,
+                              int64_t N, int p, const AnofoxB200FitOptions *opt, const AnofoxB200FitOutputs &out,
+                              void *workspace, size_t workspace_bytes, cudaStream_t st, AnofoxError *err) {
+	DeviceInfo &di = device_info();
+	const size_t xbytes = (((size_t)std::max<int64_t>(N, 1) * p * 8) + 255) & ~(size_t)255;
+	Workspace wsz;
+	const size_t need = xbytes + carve(wsz, nullptr, F, N, p, di.sms);
+	if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 255)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "workspace too small or misaligned (anofox_b200_fit_columns_workspace_bytes)");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (F == 0) return 0;
+	double *xr = (double *)workspace;
+	if (N > 0) {
+		const int64_t warps = std::min<int64_t>(F, (int64_t)di.sms * 32);
+		columns_to_rows_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(offsets, F, x_cm, p, xr);
+		LAUNCHED();
+		CU(cudaGetLastError(), "columns_to_rows_kernel");
+	}
+	// min_state_rows = 0: these are direct anofox_*_fit calls, the aggregate's "fewer than 2 rows" rule does not apply
+	return fit_device(offsets, F, y, xr, w, nullptr, N, p, opt, out, nullptr, (unsigned char *)workspace + xbytes,
+	                  workspace_bytes - xbytes, st, err, 0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Ingest: unsorted rows -> group-sorted CSR (ingest.cuh)
+// ---------------------------------------------------------------------------------------------
+struct IngestWs {
+	uint32_t *keys[2], *vals[2], *hist, *sums, *counts;
+	int *bad;
+	int64_t n_tiles;
+	size_t bytes;
+};
+static size_t ingest_carve(IngestWs &w, unsigned char *base, int64_t N, int64_t G) {
+	size_t off = 0;
+	auto take = [&](size_t bytes) {
+		size_t at = off;
+		off += (bytes + 255) & ~(size_t)255;
+		return base ? base + at : (unsigned char *)nullptr;
+	};
+	const size_t n1 = (size_t)std::max<int64_t>(N, 1), g1 = (size_t)std::max<int64_t>(G, 1);
+	w.n_tiles = (int64_t)((n1 + kRadixTile - 1) / kRadixTile);
+	for (int i = 0; i < 2; ++i) {
+		w.keys[i] = (uint32_t *)take(n1 * 4);
+		w.vals[i] = (uint32_t *)take(n1 * 4);
+	}
+	const size_t nh = (size_t)256 * w.n_tiles;
+	w.hist = (uint32_t *)take(nh * 4);
+	w.sums = (uint32_t *)take((std::max(nh, g1) / kScanBlock + 2) * 4);
+	w.counts = (uint32_t *)take((g1 + 1) * 4);
+	w.bad = (int *)take(256);
+	w.bytes = off;
+	return off;
+}
+static int scan_u32(uint32_t *a, int64_t n, uint32_t *sums, cudaStream_t st, AnofoxError *err) {
+	if (n <= 0) return 0;
+	const int64_t nb = (n + kScanBlock - 1) / kScanBlock;
+	scan_local_kernel<<<(unsigned)nb, 256, 0, st>>>(a, n, sums);
+	LAUNCHED();
+	if (nb > 1) {
+		scan_sums_kernel<<<1, 256, 0, st>>>(sums, nb);
+		LAUNCHED();
+		scan_add_kernel<<<(unsigned)nb, 256, 0, st>>>(a, n, sums);
+		LAUNCHED();
+	}
+	CU(cudaGetLastError(), "scan kernels");
+	return 0;
+}
+static int ingest_device(const int64_t *group_ids, const double *y, const double *x, const double *w, int64_t N, int p,
+                         int64_t G, int64_t *offsets_out, double *y_out, double *x_out, double *w_out, int64_t *row_index_out,
+                         void *workspace, size_t workspace_bytes, cudaStream_t st, AnofoxError *err) {
+	clear_error(err);
+	if (N < 0 || G <= 0 || p <= 0 || p > kMaxFeatures || !offsets_out || (N > 0 && (!group_ids || !y || !x || !y_out || !x_out)) ||
+	    (w && !w_out)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "ingest: bad arguments");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	if (N >= ((int64_t)1 << 32) || G >= ((int64_t)1 << 32)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "ingest: at most 2^32 - 1 rows and groups per call");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	IngestWs ws;
+	const size_t need = ingest_carve(ws, (unsigned char *)workspace, N, G);
+	if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 255)) {
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "workspace too small or misaligned (anofox_b200_ingest_workspace_bytes)");
+		return ANOFOX_ERROR_INVALID_INPUT;
+	}
+	CU(cudaMemsetAsync(ws.counts, 0, (size_t)(G + 1) * 4, st), "memset");
+	CU(cudaMemsetAsync(ws.bad, 0, 4, st), "memset");
+	if (N > 0) {
+		ingest_keys_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(group_ids, N, G, ws.keys[0], ws.counts, ws.bad);
+		LAUNCHED();
+		CU(cudaGetLastError(), "ingest_keys_kernel");
+	}
+	int rc = scan_u32(ws.counts, G, ws.sums, st, err);
+	if (rc) return rc;
+	ingest_offsets_kernel<<<(unsigned)((G + 1 + 255) / 256), 256, 0, st>>>(ws.counts, G, N, offsets_out);
+	LAUNCHED();
+	CU(cudaGetLastError(), "ingest_offsets_kernel");
+	if (N == 0) return 0;
+	int bits = 1;
+	while (bits < 32 && ((int64_t)1 << bits) < G) ++bits;
+	const int passes = (bits + 7) / 8;
+	int cur = 0;
+	for (int ps = 0; ps < passes; ++ps) {
+		radix_hist_kernel<<<(unsigned)ws.n_tiles, kRadixThreads, 0, st>>>(ws.keys[cur], N, 8 * ps, ws.n_tiles, ws.hist);
+		LAUNCHED();
+		rc = scan_u32(ws.hist, (int64_t)256 * ws.n_tiles, ws.sums, st, err);
+		if (rc) return rc;
+		radix_scatter_kernel<<<(unsigned)ws.n_tiles, kRadixThreads, 0, st>>>(ws.keys[cur], ws.vals[cur], N, 8 * ps, ws.n_tiles, ws.hist,
+		                                                                    ws.keys[cur ^ 1], ws.vals[cur ^ 1], ps == 0 ? 1 : 0);
+		LAUNCHED();
+		CU(cudaGetLastError(), "radix pass");
+		cur ^= 1;
+	}
+	const int64_t ne = N * p;
+	ingest_gather_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(ws.vals[cur], N, p, y, x, w, y_out, x_out, w_out, row_index_out);
+	LAUNCHED();
+	CU(cudaGetLastError(), "ingest_gather_kernel");
+	return 0;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -2335,6 +2480,60 @@ size_t anofox_b200_moment_block_len(int32_t n_features) {
 	if (n_features <= 0 || n_features > kMaxFeatures) return 0;
 	const int k = n_features + 1;
 	return (size_t)(4 + k + k * (k + 1) / 2);
+}
+
+size_t anofox_b200_ingest_workspace_bytes(int64_t n_rows, int64_t n_groups) {
+	IngestWs w;
+	return ingest_carve(w, nullptr, n_rows, n_groups);
+}
+
+int32_t anofox_b200_ingest_device(const int64_t *group_ids, const double *y, const double *x, const double *w, int64_t n_rows,
+                                  int32_t n_features, int64_t n_groups, int64_t *offsets_out, double *y_out, double *x_out,
+                                  double *w_out, int64_t *row_index_out, void *workspace, size_t workspace_bytes, void *stream,
+                                  AnofoxError *err) {
+	return guarded(err, "ingest_device", [&]() -> int32_t {
+		DeviceInfo &di = device_info();
+		if (!di.ok) {
+			set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+			return ANOFOX_ERROR_INTERNAL;
+		}
+		return ingest_device(group_ids, y, x, w, n_rows, n_features, n_groups, offsets_out, y_out, x_out, w_out, row_index_out,
+		                     workspace, workspace_bytes, (cudaStream_t)stream, err);
+	});
+}
+
+// 1 when the last ingest on this workspace met a group id outside [0, n_groups) (such rows were filed under group 0)
+int32_t anofox_b200_ingest_bad_ids(const void *workspace, int64_t n_rows, int64_t n_groups) {
+	IngestWs w;
+	ingest_carve(w, (unsigned char *)workspace, n_rows, n_groups);
+	int v = 0;
+	if (cudaMemcpy(&v, w.bad, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+	return v;
+}
+
+size_t anofox_b200_fit_columns_workspace_bytes(int64_t n_fits, int64_t n_rows, int32_t n_features) {
+	if (n_fits < 0 || n_rows < 0 || n_features <= 0 || n_features > kMaxFeatures) return 0;
+	DeviceInfo &di = device_info();
+	Workspace w;
+	return ((((size_t)std::max<int64_t>(n_rows, 1) * n_features * 8) + 255) & ~(size_t)255) +
+	       carve(w, nullptr, n_fits, n_rows, n_features, di.ok ? di.sms : 148);
+}
+
+int32_t anofox_b200_fit_columns_batch_device(const int64_t *offsets, int64_t n_fits, const double *y, const double *x_columns,
+                                             const double *w, int64_t n_rows, int32_t n_features,
+                                             const AnofoxB200FitOptions *options, const AnofoxB200FitOutputs *out,
+                                             void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err) {
+	return guarded(err, "fit_columns_batch_device", [&]() -> int32_t {
+		int rc = validate_common(offsets, n_fits, y, x_columns, w, n_rows, n_features, options, err);
+		if (rc) return rc;
+		if (!out) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "outputs is NULL");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		if ((rc = check_outputs(out, options->compute_inference != 0, err))) return rc;
+		return fit_columns_device(offsets, n_fits, y, x_columns, w, n_rows, n_features, options, *out, workspace,
+		                          workspace_bytes, (cudaStream_t)stream, err);
+	});
 }
 
 size_t anofox_b200_window_workspace_bytes(int64_t n_rows, int32_t n_features) {

@@ -293,6 +293,40 @@ int32_t anofox_b200_fit_predict_batch_host(const int64_t *offsets, int64_t n_gro
                                            const AnofoxB200PredictOutputs *pred, const AnofoxB200FitOutputs *fit,
                                            AnofoxError *err);
 
+/* Ingest: unsorted rows -> the group-sorted CSR the batch entry points take. Replaces what *AggUpdate / *AggCombine
+ * do per row on the host (src/aggregate_functions/ols_aggregate.cpp:120-234): the rows of a query stay in scan order,
+ *   group_ids [N] int64 in [0, n_groups)  (e.g. the dense ids of DuckDB's group hash table)
+ *   y [N], x [N*p] row-major, w [N] or NULL
+ * and a STABLE radix partition on the device writes offsets_out [G+1], y_out, x_out, w_out in group order; inside a
+ * group the rows keep their arrival order (the "state order" of the reference: first valid row of the constant-column
+ * rule, order of the fit_predict output list). row_index_out [N] (optional) = the source row of every sorted row, for
+ * scattering per-row outputs back. At most 2^32 - 1 rows and groups per call. Only enqueues work on `stream`. */
+size_t anofox_b200_ingest_workspace_bytes(int64_t n_rows, int64_t n_groups);
+int32_t anofox_b200_ingest_device(const int64_t *group_ids, const double *y, const double *x, const double *w, int64_t n_rows,
+                                  int32_t n_features, int64_t n_groups, int64_t *offsets_out, double *y_out, double *x_out,
+                                  double *w_out, int64_t *row_index_out, void *workspace, size_t workspace_bytes, void *stream,
+                                  AnofoxError *err);
+/* 1 when the last ingest on this workspace met an id outside [0, n_groups) (those rows were filed under group 0);
+ * synchronising read of one flag. */
+int32_t anofox_b200_ingest_bad_ids(const void *workspace, int64_t n_rows, int64_t n_groups);
+
+/* Scalar array fits, batched: {ols,ridge,wls}_fit(y LIST, x LIST(LIST) [, w LIST]) computes ONE fit per SQL row from
+ * column arrays (src/table_functions/ols_fit.cpp:120-173 makes one anofox_ols_fit call per row of the DataChunk).
+ * This entry point takes all rows of a chunk (or of a query) at once:
+ *   offsets   [F+1]  rows of fit i are [offsets[i], offsets[i+1])  (device int64)
+ *   y         [N]    the concatenated y lists (the LIST(DOUBLE) child vector)
+ *   x_columns [N*p]  per fit a block of p columns of n_i values each, blocks in fit order -- the layout of the
+ *                    LIST(LIST(DOUBLE)) child when each row's inner lists are stored back to back
+ *   w         [N]    concatenated weight lists (WLS) or NULL
+ * The columns are turned into rows on the device and fitted by the same kernels as the aggregates. These are direct
+ * anofox_*_fit calls: the aggregate's "fewer than 2 rows" rule does not apply, and where the reference throws
+ * ("OLS fit failed: ...", ols_fit.cpp:175-177) status[i] carries the error code instead. */
+size_t anofox_b200_fit_columns_workspace_bytes(int64_t n_fits, int64_t n_rows, int32_t n_features);
+int32_t anofox_b200_fit_columns_batch_device(const int64_t *offsets, int64_t n_fits, const double *y, const double *x_columns,
+                                             const double *w, int64_t n_rows, int32_t n_features,
+                                             const AnofoxB200FitOptions *options, const AnofoxB200FitOutputs *out,
+                                             void *workspace, size_t workspace_bytes, void *stream, AnofoxError *err);
+
 /* Window form of the fit-predict aggregates:
  *   {ols,ridge,wls}_fit_predict(y, x [, w], opts) OVER (PARTITION BY g ORDER BY t ROWS BETWEEN <start> AND <end>)
  * (src/window_functions/ols_fit_predict.cpp:111-326, ridge_fit_predict.cpp, wls_fit_predict.cpp). DuckDB runs
