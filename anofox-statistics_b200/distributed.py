@@ -147,3 +147,48 @@ class ShardedSingleGroupFit:
             dist.all_reduce(rss, op=dist.ReduceOp.SUM, group=self.group)
         self.backend.solve(m, cd, shift, o, self.fit_out.out_struct, flag=self.flag, rss=rss)
         return out
+
+
+class MixedShardedFit:
+    """GROUP BY over several GPUs where a few groups are too large for one rank (SURVEY.md section 8e "mixed
+    case"): sharding.mixed_plan decides, per rank, which whole groups it fits (no collective) and which row slice of
+    every giant group it accumulates (one SUM + one MAX all-reduce per giant, as ShardedSingleGroupFit).
+
+    fit() takes the CSR of the whole query (host offsets) and this rank's view of the rows as device tensors
+    indexed by GLOBAL row (test scale: the full arrays; in production only plan.rows a rank touches need to be
+    resident). Results land in full-size [G] arrays: the rank's own groups and every giant group are valid."""
+
+    def __init__(self, offsets, world, rank, p, giant_rows, inference=True, device="cuda", group=None):
+        import numpy as np
+        import torch
+        import torch.distributed as dist
+        from . import DeviceFit
+        from . import sharding
+        self.torch, self.dist, self.group, self.rank, self.p = torch, dist, group, rank, p
+        self.offsets = np.asarray(offsets, dtype=np.int64)
+        self.plan = sharding.mixed_plan(self.offsets, world, giant_rows)
+        G = len(self.offsets) - 1
+        self.full = DeviceFit(G, 1, p, inference=inference, device=device)  # output arrays only
+        self.inference, self.device = inference, device
+        self._DeviceFit = DeviceFit
+
+    def fit(self, y, x, w=None, **opt):
+        torch, off = self.torch, self.offsets
+        out = self.full.out
+        out["status"].fill_(-1)  # -1 = not this rank's group
+        off_dev = torch.from_numpy(off).to(self.device)
+        for g0, g1 in self.plan["segments"][self.rank]:
+            r0, r1 = int(off[g0]), int(off[g1])
+            seg = self._DeviceFit(g1 - g0, r1 - r0, self.p, inference=self.inference, device=self.device)
+            loc = (off_dev[g0:g1 + 1] - r0).contiguous()
+            res = seg.fit(loc, y[r0:r1], x[r0:r1], None if w is None else w[r0:r1], **opt)
+            for k, v in res.items():
+                out[k][g0:g1] = v
+        for g in self.plan["giants"]:
+            a, b = self.plan["giant_rows"][g][self.rank]
+            one = ShardedSingleGroupFit(max(b - a, 1), self.p, inference=self.inference, device=self.device,
+                                        group=self.group)
+            res = one.fit(y[a:b], x[a:b], None if w is None else w[a:b], **opt)
+            for k, v in res.items():
+                out[k][g:g + 1] = v
+        return out

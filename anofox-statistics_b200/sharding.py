@@ -46,3 +46,42 @@ def row_ranges(n_rows, world):
     per = -(-n_rows // world)
     per = (per + 3) & ~3
     return [(min(r * per, n_rows), min((r + 1) * per, n_rows)) for r in range(world)]
+
+
+def mixed_plan(offsets, world, giant_rows):
+    """GROUP BY with a few giant groups among many ("mixed case").
+
+    Groups of more than `giant_rows` rows are ROW-sharded over all ranks (every rank accumulates a slice of the
+    group's rows, the moment blocks meet in one all-reduce: distributed.py); the remaining groups are cut into
+    contiguous group-id ranges balanced by their row count WITHOUT the giants, and fitted whole by one rank each.
+
+    Returns dict(giants=[g...], giant_rows={g: [(r0, r1) per rank]} (absolute row ranges),
+                 cuts=[world + 1] group cut points, segments={rank: [(g0, g1), ...]} = the rank's range with the
+                 giants cut out (each segment is a contiguous run of whole small groups)).
+    """
+    offsets = np.asarray(offsets, dtype=np.int64)
+    G = len(offsets) - 1
+    sizes = np.diff(offsets)
+    giants = [int(g) for g in np.flatnonzero(sizes > giant_rows)]
+    small = sizes.copy()
+    small[giants] = 0
+    so = np.zeros(G + 1, dtype=np.int64)
+    np.cumsum(small, out=so[1:])
+    cuts = group_ranges(so, world)
+    segments = {}
+    for r in range(world):
+        g0, g1 = int(cuts[r]), int(cuts[r + 1])
+        segs, start = [], g0
+        for g in giants:
+            if g0 <= g < g1:
+                if g > start:
+                    segs.append((start, g))
+                start = g + 1
+        if g1 > start:
+            segs.append((start, g1))
+        segments[r] = segs
+    giant_ranges = {}
+    for g in giants:
+        base = int(offsets[g])
+        giant_ranges[g] = [(base + a, base + b) for a, b in row_ranges(int(sizes[g]), world)]
+    return dict(giants=giants, giant_rows=giant_ranges, cuts=cuts, segments=segments)

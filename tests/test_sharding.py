@@ -218,3 +218,32 @@ def test_group_sharded_results_over_gloo(oracle):
         assert np.array_equal(pv, full["p_values"][g0:g1], equal_nan=True)
         covered += g1 - g0
     assert covered == G
+
+
+def test_mixed_plan_splits_only_the_giants():
+    """SURVEY 8(e) "mixed case": groups above the threshold are row-sharded over all ranks, the others stay whole."""
+    pkg = load_package()
+    from importlib import import_module
+    sh = import_module(pkg.__name__ + ".sharding")
+    rng = np.random.default_rng(8)
+    for world in (1, 2, 4, 8):
+        G = 500
+        sizes = rng.integers(0, 100, size=G)
+        sizes[[17, 250, 499]] = [50_000, 200_001, 77_777]
+        offsets = np.zeros(G + 1, dtype=np.int64)
+        np.cumsum(sizes, out=offsets[1:])
+        plan = sh.mixed_plan(offsets, world, giant_rows=10_000)
+        assert plan["giants"] == [17, 250, 499]
+        owned = []
+        for r in range(world):
+            for g0, g1 in plan["segments"][r]:
+                assert g0 < g1 and not any(g0 <= g < g1 for g in plan["giants"])
+                owned.extend(range(g0, g1))
+        assert sorted(owned) == [g for g in range(G) if g not in plan["giants"]]  # every small group exactly once
+        small_rows = [sum(int(sizes[g]) for g0, g1 in plan["segments"][r] for g in range(g0, g1)) for r in range(world)]
+        assert max(small_rows) - min(small_rows) <= 2 * 100  # balanced without the giants
+        for g in plan["giants"]:
+            rr = plan["giant_rows"][g]
+            assert len(rr) == world and rr[0][0] == offsets[g] and rr[-1][1] == offsets[g + 1]
+            assert all(a[1] == b[0] for a, b in zip(rr, rr[1:]))
+    assert sh.mixed_plan(np.array([0, 5, 9]), 2, giant_rows=100)["giants"] == []
