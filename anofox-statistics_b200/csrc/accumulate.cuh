@@ -424,7 +424,10 @@ __device__ __forceinline__ void mma_step(WarpAcc<NT, SIDE> &A, double (&c0)[NT *
 #pragma unroll
 	for (int t = 0; t < NT; ++t) {
 		double dv = v[t] - sh[t];
-		if (MASK) dv = ok ? dv : 0.0;
+		// weighted fits: a masked row has weff = 0, so its a-operand (and w dy below) is zero whatever d holds; the
+		// B-operand only needs its own mask where nothing else zeroes the product (unweighted masks, tail rows that
+		// may read past the data, the constant-column flags)
+		if (MASK && (!HASW || TAIL || TRACKNC)) dv = ok ? dv : 0.0;
 		d[t] = dv;
 		if (TRACKNC) A.nc[t] = A.nc[t] || (fabs(dv) >= 1e-10);
 		a[t] = HASW ? weff * dv : dv;
@@ -439,7 +442,7 @@ __device__ __forceinline__ void mma_step(WarpAcc<NT, SIDE> &A, double (&c0)[NT *
 		}
 	if (SIDE) {
 		double dy = yv - shy;
-		if (MASK) dy = ok ? dy : 0.0;
+		if (MASK && (!HASW || TAIL)) dy = ok ? dy : 0.0;
 		const double wdy = HASW ? weff * dy : dy;
 #pragma unroll
 		for (int t = 0; t < NT; ++t) {
@@ -524,7 +527,7 @@ __device__ __forceinline__ void mma_step_pipe(WarpAcc<NT, SIDE> &A, double (&c0)
 #pragma unroll
 	for (int t = 0; t < NT; ++t) {
 		double dv = in.v[t] - sh[t];
-		if (MASK) dv = ok ? dv : 0.0;
+		if (MASK && (!HASW || TRACKNC)) dv = ok ? dv : 0.0; // see mma_step
 		d[t] = dv;
 		if (TRACKNC) A.nc[t] = A.nc[t] || (fabs(dv) >= 1e-10);
 		a[t] = HASW ? weff * dv : dv;
@@ -532,7 +535,7 @@ __device__ __forceinline__ void mma_step_pipe(WarpAcc<NT, SIDE> &A, double (&c0)
 	double dy = 0.0;
 	if (SIDE) {
 		dy = in.yv - shy;
-		if (MASK) dy = ok ? dy : 0.0;
+		if (MASK && !HASW) dy = ok ? dy : 0.0;
 	}
 	if (more) step_load<NT, SIDE, HASW, HAST>(in, p0, pl, st0, stl, py, pw, pt);
 	int pair = 0;

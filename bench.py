@@ -370,6 +370,64 @@ def run_window_workload(args, rank, world, local, steps, warmup, G=1_000_000, n=
     return res if rank == 0 else None
 
 
+def run_finalize_pattern(args, rank, threads_list=(1, 8, 16), groups_per_call=2048, calls_per_thread=24, n=50, p=5):
+    """DuckDB's own call pattern against the host-pointer entry point: Finalize hands over at most 2 048 group states
+    per call (ols_aggregate.cpp:249-257) and runs on many threads at once (radix_partitioned_hashtable.cpp:990).
+    T host threads each make `calls_per_thread` calls of 2 048 groups x 50 rows x 5 features (C2's shape, ~4.9 MB in,
+    0.6 MB out per call) from pinned buffers; ctypes releases the GIL for the duration of a call."""
+    import ctypes as C
+    import threading
+    import numpy as np
+    import torch
+    from importlib import import_module
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    abi = pkg.abi
+    synth = import_module("anofox_statistics_b200.synth")
+    G = groups_per_call
+    N = G * n
+    res = {}
+    for T in threads_list:
+        bufs = []
+        for t in range(T):
+            d = synth.make_numpy(G, n, p, seed=100 + t)
+            h = {k: torch.from_numpy(np.ascontiguousarray(d[k])).pin_memory() for k in ("offsets", "y", "x")}
+            fit = {"coefficients": torch.empty((G, p), dtype=torch.float64).pin_memory()}
+            for k in abi.FIT_F64_G + abi.INF_F64_G + abi.EXTRA_F64_G:
+                fit[k] = torch.empty(G, dtype=torch.float64).pin_memory()
+            for k in abi.INF_F64_GP:
+                fit[k] = torch.empty((G, p), dtype=torch.float64).pin_memory()
+            fit["n_observations"] = torch.empty(G, dtype=torch.int64).pin_memory()
+            fit["status"] = torch.empty(G, dtype=torch.int32).pin_memory()
+            fit["has_inference"] = torch.empty(G, dtype=torch.uint8).pin_memory()
+            hs = abi.B200FitOutputs()
+            for nm, ctype in abi.B200FitOutputs._fields_:
+                setattr(hs, nm, None if nm not in fit else C.cast(fit[nm].data_ptr(), ctype))
+            bufs.append((h, fit, hs))
+
+        def work(t, reps):
+            h, fit, hs = bufs[t]
+            torch.cuda.set_device(torch.cuda.current_device())
+            for _ in range(reps):
+                pkg.fit_batch_host_into(h["offsets"].data_ptr(), h["y"].data_ptr(), h["x"].data_ptr(), None, hs, G, N, p,
+                                        method="ols", compute_inference=True)
+
+        for phase, reps in (("warm", 2), ("timed", calls_per_thread)):
+            ths = [threading.Thread(target=work, args=(t, reps)) for t in range(T)]
+            t0 = time.perf_counter()
+            for th in ths:
+                th.start()
+            for th in ths:
+                th.join()
+            dt = time.perf_counter() - t0
+        ok = all(int((b[1]["status"] == 0).sum()) == G for b in bufs)
+        res["threads_%d" % T] = {"fits_per_sec": T * calls_per_thread * G / dt, "ms_per_call": dt / calls_per_thread * 1e3,
+                                 "calls": T * calls_per_thread, "all_groups_ok": ok}
+        del bufs
+    res["shape"] = "%d groups x %d rows x %d features per call, full inference, pinned host buffers" % (G, n, p)
+    return res if rank == 0 else None
+
+
 def run_group_workload(args, wname, rank, world, local, steps, warmup, headline, data_cache=None):
     """One group-sharded workload on this rank (weak scaling: every rank fits its own copy of the shape).
     Returns the result dict on rank 0 (None elsewhere)."""
@@ -647,6 +705,8 @@ def main():
         wres = run_window_workload(args, rank, world, local, 3, 3)
         if rank == 0:
             secondary["W1"] = wres
+        if world == 1:
+            secondary["finalize_pattern"] = run_finalize_pattern(args, rank)
         if world > 1:
             # C4: the single huge group, 125 M rows x 64 features per GPU, three NCCL collectives per fit
             a4 = argparse.Namespace(**vars(args))

@@ -155,7 +155,12 @@ int main() {
 		cudaEventElapsedTime(&ms, e0, e1);
 		printf("DMMA m8n8k4 dependent chain, 4 warps/SMSP-set: latency ~%.1f cycles @1.9GHz\n", ms * 1e-3 * 1.9e9 / iters);
 		for (int wps : {4, 8, 16}) { // warps per SM with 36 independent accumulator pairs each (the p = 64 Gram step)
-			cudaEventRecord(e0); dmma_kernel<36><<<sms, 32 * wps>>>(out, iters / 4); cudaEventRecord(e1); CK(cudaEventSynchronize(e1));
+			cudaEventRecord(e0); dmma_kernel<36><<<sms, 32 * wps>>>(out, iters / 4);
+			if (cudaGetLastError() != cudaSuccess) { // 36 accumulator pairs x 16 warps do not fit the register file
+				printf("DMMA m8n8k4 x36 acc, %d warps/SM: not launchable (registers)\n", wps);
+				continue;
+			}
+			cudaEventRecord(e1); CK(cudaEventSynchronize(e1));
 			cudaEventElapsedTime(&ms, e0, e1);
 			printf("DMMA m8n8k4 x36 acc, %d warps/SM: %.2f TFLOP/s (%.3f ms)\n", wps, 2.0 * 256 * 36 * (iters / 4) * sms * wps / ms / 1e9, ms);
 		}
@@ -178,10 +183,10 @@ int main() {
 		int cfgs[][4] = {{32768, 32768, 1, 288}, {32768, 4096, 1, 288}, {32768, 2048, 1, 288}, {65536, 65536, 1, 288}, {16384, 16384, 2, 160}, {32768, 2048, 2, 160}, {49152, 2048, 1, 544}};
 		for (auto &c : cfgs) {
 			int stage = c[0], chunk = c[1], cps = c[2], thr = c[3];
-			CK(cudaFuncSetAttribute(bulk_stream<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * stage));
-			CK(cudaFuncSetAttribute(bulk_stream<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * stage));
 			for (int ns : {2, 4}) {
 				if ((size_t)ns * stage * cps > 220 * 1024) continue;
+				if (ns == 4) CK(cudaFuncSetAttribute(bulk_stream<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * stage));
+				else CK(cudaFuncSetAttribute(bulk_stream<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * stage));
 				for (int rep = 0; rep < 2; ++rep) {
 					cudaEventRecord(e0);
 					if (ns == 4) bulk_stream<4><<<sms * cps, thr, 4 * stage>>>(buf, bytes, stage, chunk, out);

@@ -32,7 +32,7 @@ for vals in rows[2:]:
     if best is None or rec["capture_duration_us"] > best["capture_duration_us"]:
         best = rec
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-path = os.path.join(root, "profiles", "traffic.json")
+path = os.environ.get("TRAFFIC_JSON", os.path.join(root, "profiles", "traffic.json"))
 try:
     db = json.load(open(path))
 except (OSError, ValueError):
