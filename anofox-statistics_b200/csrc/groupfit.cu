@@ -17,6 +17,7 @@
 #include <condition_variable>
 #include <mutex>
 #include <new>
+#include <string>
 #include <vector>
 
 #include "acc_launch.h"
@@ -1834,6 +1835,28 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 // ---------------------------------------------------------------------------------------------
 // One fit through the reference's own signature (drop-in layer)
 // ---------------------------------------------------------------------------------------------
+// Error texts = the Display strings of the reference's StatsError (crates/anofox-stats-core/src/errors.rs:7-37), which
+// anofox_*_fit copies into AnofoxError.message (lib.rs:258-262) and the scalar SQL functions surface as
+// "OLS fit failed: <message>" (src/table_functions/ols_fit.cpp:175-177; test/sql/error_handling.test matches on them).
+static std::string rust_f64(double v) { // Rust's Display for f64: shortest digits that round-trip, no exponent
+	char buf[64];
+	for (int prec = 1; prec <= 17; ++prec) {
+		snprintf(buf, sizeof buf, "%.*g", prec, v);
+		if (strtod(buf, nullptr) == v) break;
+	}
+	std::string t(buf);
+	if (t.find('e') != std::string::npos) {
+		snprintf(buf, sizeof buf, "%.17f", v);
+		t = buf;
+		while (!t.empty() && t.back() == '0') t.pop_back();
+		if (!t.empty() && t.back() == '.') t.pop_back();
+	}
+	return t;
+}
+static std::string msg_dimension(size_t y_len, size_t x_rows) {
+	return "Dimension mismatch: y has " + std::to_string(y_len) + " elements, X has " + std::to_string(x_rows) + " rows";
+}
+
 static bool single_fit(int method, AnofoxDataArray y, const AnofoxDataArray *x, size_t x_count,
                        const AnofoxDataArray *weights, bool fit_intercept, bool compute_inference, double level,
                        double alpha, int lambda_scaling, int solver, int hc_type, AnofoxFitResultCore *out_core,
@@ -1848,24 +1871,24 @@ static bool single_fit(int method, AnofoxDataArray y, const AnofoxDataArray *x, 
 		return false;
 	}
 	if (method == ANOFOX_B200_RIDGE && alpha < 0.0) { // ridge.rs:38-40 comes first
-		set_error(err, ANOFOX_ERROR_INVALID_ALPHA, "Invalid alpha: must be >= 0");
+		set_error(err, ANOFOX_ERROR_INVALID_ALPHA, ("Invalid alpha parameter: " + rust_f64(alpha) + " (must be >= 0)").c_str());
 		return false;
 	}
 	if (y.len == 0 || !y.data) {
-		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "Empty input: y"); // ols.rs:38-40
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "Empty input: y cannot be empty"); // ols.rs:38-40
 		return false;
 	}
 	if (weights && weights->len == 0) {
-		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "Empty input: weights");
+		set_error(err, ANOFOX_ERROR_INVALID_INPUT, "Empty input: weights cannot be empty"); // wls.rs:50-52
 		return false;
 	}
-	if (weights && weights->len != y.len) {
-		set_error(err, ANOFOX_ERROR_DIMENSION_MISMATCH, "Dimension mismatch: weights");
+	if (weights && weights->len != y.len) { // wls.rs:58-63
+		set_error(err, ANOFOX_ERROR_DIMENSION_MISMATCH, msg_dimension(y.len, weights->len).c_str());
 		return false;
 	}
 	for (size_t j = 0; j < x_count; ++j)
 		if (x[j].len != y.len) { // ols.rs:49-56
-			set_error(err, ANOFOX_ERROR_DIMENSION_MISMATCH, "Dimension mismatch: x column length differs from y");
+			set_error(err, ANOFOX_ERROR_DIMENSION_MISMATCH, msg_dimension(y.len, x[j].len).c_str());
 			return false;
 		}
 	const size_t n = y.len, p = x_count;
@@ -1919,10 +1942,22 @@ static bool single_fit(int method, AnofoxDataArray y, const AnofoxDataArray *x, 
 	              nullptr, err, 0);
 	if (rc) return false;
 	if (status != 0) {
-		const char *msg = status == ANOFOX_ERROR_NO_VALID_DATA        ? "No valid data"
-		                  : status == ANOFOX_ERROR_INSUFFICIENT_DATA ? "Insufficient data"
-		                                                             : "fit failed";
-		set_error(err, status, msg);
+		std::string msg = "fit failed";
+		if (status == ANOFOX_ERROR_NO_VALID_DATA) {
+			msg = "All rows filtered due to NULL/NaN values"; // errors.rs:16
+		} else if (status == ANOFOX_ERROR_INSUFFICIENT_DATA) {
+			// errors.rs:13 names the rows that survived the filter: count them for the text (the decision itself
+			// was made on the device)
+			size_t rows = 0;
+			for (size_t i = 0; i < n; ++i) {
+				bool ok = std::isfinite(yv[i]);
+				if (ok && weights) ok = std::isfinite(wv[i]) && wv[i] > 0.0;
+				for (size_t j = 0; ok && j < p; ++j) ok = std::isfinite(xr[i * p + j]);
+				rows += ok ? 1 : 0;
+			}
+			msg = "Insufficient data: " + std::to_string(rows) + " rows, " + std::to_string(p) + " features (need rows > features)";
+		}
+		set_error(err, status, msg.c_str());
 		return false;
 	}
 	double *c = (double *)malloc(std::max<size_t>(p, 1) * sizeof(double));

@@ -707,6 +707,20 @@ def main():
             secondary["W1"] = wres
         if world == 1:
             secondary["finalize_pattern"] = run_finalize_pattern(args, rank)
+            # CPU-A: the reference's own DuckDB callers (oracle/_ref, built by oracle/build_ref.sh) + the CPU oracle behind
+            # the seven FFI symbols, C1's query on the host cores; absent when oracle/_ref was not built
+            if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "duckdb")) and not args.no_cpu:
+                try:
+                    out = subprocess.run([sys.executable, os.path.join(ROOT, "harness", "time_c1.py"), "--flavour", "cpu"],
+                                         capture_output=True, text=True, timeout=300).stdout
+                    a = json.loads(out)
+                    secondary["cpu_baseline_sql_c1"] = {
+                        "kind": "reference-callers+port", "value": a["fits_per_sec_best"], "unit": "fits/s", "cores": a["threads"],
+                        "seconds_no_inference": a["seconds_no_inference"], "seconds_with_inference": a["seconds_with_inference"],
+                        "what": "DuckDB (built from the reference tree) + the reference's unmodified ols_aggregate.cpp + CPU oracle "
+                                "behind anofox_ols_fit: " + a["query"]}
+                except Exception as e:  # noqa: BLE001
+                    secondary["cpu_baseline_sql_c1"] = {"unavailable": str(e)[:200]}
         if world > 1:
             # C4: the single huge group, 125 M rows x 64 features per GPU, three NCCL collectives per fit
             a4 = argparse.Namespace(**vars(args))

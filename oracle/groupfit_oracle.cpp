@@ -38,6 +38,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <string>
 #include <vector>
 
 #ifdef _OPENMP
@@ -616,16 +617,33 @@ void set_err(AnofoxError *e, int code, const char *msg) {
 	e->message[255] = 0;
 }
 
-const char *code_msg(int code) {
-	switch (code) {
-	case ANOFOX_ERROR_INVALID_INPUT: return "invalid input";
-	case ANOFOX_ERROR_INVALID_ALPHA: return "invalid alpha: must be >= 0";
-	case ANOFOX_ERROR_INSUFFICIENT_DATA: return "insufficient data";
-	case ANOFOX_ERROR_DIMENSION_MISMATCH: return "dimension mismatch";
-	case ANOFOX_ERROR_NO_VALID_DATA: return "no valid data";
-	default: return "error";
+// Error texts = the Display strings of the reference's StatsError (crates/anofox-stats-core/src/errors.rs:7-37), which
+// anofox_*_fit copies into AnofoxError.message (lib.rs:258-262) and the scalar SQL functions surface as
+// "OLS fit failed: <message>" (src/table_functions/ols_fit.cpp:175-177; test/sql/error_handling.test matches on them).
+std::string rust_f64(double v) { // Rust's Display for f64: shortest digits that round-trip, no exponent
+	char buf[64];
+	for (int prec = 1; prec <= 17; ++prec) {
+		std::snprintf(buf, sizeof buf, "%.*g", prec, v);
+		if (std::strtod(buf, nullptr) == v) break;
 	}
+	std::string t(buf);
+	if (t.find('e') != std::string::npos) {
+		std::snprintf(buf, sizeof buf, "%.17f", v);
+		t = buf;
+		while (!t.empty() && t.back() == '0') t.pop_back();
+		if (!t.empty() && t.back() == '.') t.pop_back();
+	}
+	return t;
 }
+std::string msg_insufficient(size_t rows, size_t cols) {
+	return "Insufficient data: " + std::to_string(rows) + " rows, " + std::to_string(cols) + " features (need rows > features)";
+}
+std::string msg_dimension(size_t y_len, size_t x_rows) {
+	return "Dimension mismatch: y has " + std::to_string(y_len) + " elements, X has " + std::to_string(x_rows) + " rows";
+}
+std::string msg_empty(const char *field) { return std::string("Empty input: ") + field + " cannot be empty"; }
+std::string msg_alpha(double a) { return "Invalid alpha parameter: " + rust_f64(a) + " (must be >= 0)"; }
+const char *kMsgNoValidData = "All rows filtered due to NULL/NaN values";
 
 double *dup_array(const std::vector<double> &v) {
 	double *p = (double *)std::malloc(std::max<size_t>(v.size(), 1) * sizeof(double));
@@ -648,24 +666,24 @@ bool single_fit(const Opts &o, AnofoxDataArray y, const AnofoxDataArray *x, size
 		return false;
 	}
 	if (o.method == ANOFOX_B200_RIDGE && o.alpha < 0.0) {
-		set_err(err, ANOFOX_ERROR_INVALID_ALPHA, code_msg(ANOFOX_ERROR_INVALID_ALPHA));
+		set_err(err, ANOFOX_ERROR_INVALID_ALPHA, msg_alpha(o.alpha).c_str());
 		return false;
 	}
 	if (y.len == 0) {
-		set_err(err, ANOFOX_ERROR_INVALID_INPUT, "y is empty");
+		set_err(err, ANOFOX_ERROR_INVALID_INPUT, msg_empty("y").c_str());
 		return false;
 	}
 	if (w && w->len == 0) {
-		set_err(err, ANOFOX_ERROR_INVALID_INPUT, "weights is empty");
+		set_err(err, ANOFOX_ERROR_INVALID_INPUT, msg_empty("weights").c_str());
 		return false;
 	}
 	if (w && w->len != y.len) {
-		set_err(err, ANOFOX_ERROR_DIMENSION_MISMATCH, code_msg(ANOFOX_ERROR_DIMENSION_MISMATCH));
+		set_err(err, ANOFOX_ERROR_DIMENSION_MISMATCH, msg_dimension(y.len, w->len).c_str());
 		return false;
 	}
 	for (size_t j = 0; j < x_count; ++j)
 		if (x[j].len != y.len) {
-			set_err(err, ANOFOX_ERROR_DIMENSION_MISMATCH, code_msg(ANOFOX_ERROR_DIMENSION_MISMATCH));
+			set_err(err, ANOFOX_ERROR_DIMENSION_MISMATCH, msg_dimension(y.len, x[j].len).c_str());
 			return false;
 		}
 	RowView d;
@@ -681,7 +699,10 @@ bool single_fit(const Opts &o, AnofoxDataArray y, const AnofoxDataArray *x, size
 	GroupResult r;
 	fit_group<long double>(o, d, r);
 	if (r.code != 0) {
-		set_err(err, r.code, code_msg(r.code));
+		std::string m = r.code == ANOFOX_ERROR_INSUFFICIENT_DATA ? msg_insufficient(r.n_obs, x_count)
+		                : r.code == ANOFOX_ERROR_NO_VALID_DATA   ? std::string(kMsgNoValidData)
+		                                                         : std::string("fit failed");
+		set_err(err, r.code, m.c_str());
 		return false;
 	}
 	core->coefficients = dup_array(r.coef);
