@@ -1542,6 +1542,17 @@ struct HostContext {
 	bool events = false;
 	unsigned char *dev = nullptr;
 	size_t dev_bytes = 0;
+	// Small calls (DuckDB's per-group anofox_*_fit, a few KB): inputs are packed into one pinned staging buffer and
+	// cross the bus as ONE copy each way instead of ~4 + ~19 driver calls.
+	static constexpr size_t kStageHalf = (size_t)256 << 10;
+	unsigned char *hstage = nullptr;
+	bool stage_ready() {
+		if (!hstage && cudaHostAlloc((void **)&hstage, 2 * kStageHalf, cudaHostAllocDefault) != cudaSuccess) {
+			hstage = nullptr;
+			cudaGetLastError();
+		}
+		return hstage != nullptr;
+	}
 	int ensure(size_t bytes, AnofoxError *err) {
 		if (!stream) CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "cudaStreamCreate");
 		if (!in_stream) CU(cudaStreamCreateWithFlags(&in_stream, cudaStreamNonBlocking), "cudaStreamCreate");
@@ -1716,9 +1727,31 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 	if (rc) return rc;
 	unsigned char *d = c.dev;
 	cudaStream_t st = c.stream, sin = nch > 1 ? c.in_stream : c.stream, sout = nch > 1 ? c.out_stream : c.stream;
-	// ---- host -> device: offsets first, then the chunks in order ----
-	CU(cudaMemcpyAsync(d + o_off, offsets, (size_t)(G + 1) * 8, cudaMemcpyHostToDevice, sin), "H2D offsets");
+	// ---- small call: one packed copy each way through the context's pinned staging buffer ----
+	const size_t in_span = o_gp - o_off, out_span = o_g + (size_t)G1 * 8 * 12 - o_gp;
+	const bool small = nch == 1 && !pred && in_span <= HostContext::kStageHalf && out_span <= HostContext::kStageHalf &&
+	                   c.stage_ready();
+	struct Pending {
+		void *dst;
+		size_t off, bytes;
+	};
+	std::vector<Pending> pending;
+	if (small) {
+		unsigned char *hs = c.hstage;
+		memcpy(hs, offsets, (size_t)(G + 1) * 8);
+		if (N > 0) {
+			memcpy(hs + (o_y - o_off), y, (size_t)N * 8);
+			memcpy(hs + (o_x - o_off), x, (size_t)N * p * 8);
+			if (w) memcpy(hs + (o_w - o_off), w, (size_t)N * 8);
+			if (train) memcpy(hs + (o_t - o_off), train, (size_t)N);
+		}
+		CU(cudaMemcpyAsync(d + o_off, hs, in_span, cudaMemcpyHostToDevice, sin), "H2D packed");
+	} else {
+		// ---- host -> device: offsets first, then the chunks in order ----
+		CU(cudaMemcpyAsync(d + o_off, offsets, (size_t)(G + 1) * 8, cudaMemcpyHostToDevice, sin), "H2D offsets");
+	}
 	auto push = [&](int i) -> int { // chunk i's rows to the device
+		if (small) return 0;
 		const int64_t r0 = offsets[gb[i]], nr = offsets[gb[i + 1]] - r0;
 		if (nr > 0) {
 			CU(cudaMemcpyAsync(d + o_y + (size_t)r0 * 8, y + r0, (size_t)nr * 8, cudaMemcpyHostToDevice, sin), "H2D y");
@@ -1735,6 +1768,10 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 		if ((rc = push(i))) return rc;
 	double *gp = (double *)(d + o_gp), *gs = (double *)(d + o_g);
 	auto back = [&](void *dst, const void *src, size_t bytes) {
+		if (small) { // scattered from the staging buffer after the one packed copy below
+			if (dst && bytes) pending.push_back({dst, (size_t)((const unsigned char *)src - (d + o_gp)), bytes});
+			return cudaSuccess;
+		}
 		return (dst && bytes) ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, sout) : cudaSuccess;
 	};
 	for (int i = 0; i < nch; ++i) {
@@ -1826,9 +1863,11 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 			CU(back(pred->is_training + r0, dpred.is_training, (size_t)Nc), "D2H");
 		}
 	}
+	if (small) CU(cudaMemcpyAsync(c.hstage + HostContext::kStageHalf, d + o_gp, out_span, cudaMemcpyDeviceToHost, sout), "D2H packed");
 	CU(cudaStreamSynchronize(sin), "sync");
 	CU(cudaStreamSynchronize(st), "sync");
 	if (sout != st) CU(cudaStreamSynchronize(sout), "sync");
+	for (const Pending &q : pending) memcpy(q.dst, c.hstage + HostContext::kStageHalf + q.off, q.bytes);
 	return 0;
 }
 
