@@ -30,6 +30,7 @@
 #include "specfun.cuh"
 #include "qr.cuh"
 #include "hc.cuh"
+#include "hc_launch.h"
 #include "window.cuh"
 #include "window_launch.h"
 #include "ingest.cuh"
@@ -1494,12 +1495,41 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		ha.flags_from_y = y_only_flags ? 1 : 0;
 		ha.n_groups = G;
 		ha.hc_type = opt->hc_type;
-		const size_t dyn = hc_smem_bytes(p);
-		CU(cudaFuncSetAttribute(hc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn), "hc_kernel attr");
-		const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)200 * 1024 / (dyn + 1024)));
-		hc_kernel<<<(unsigned)std::min<int64_t>(G, (int64_t)di.sms * per_sm), kHcThreads, dyn, st>>>(ha, P, fo);
-		LAUNCHED();
-		CU(cudaGetLastError(), "hc_kernel");
+		ha.list = nullptr;
+		ha.count = nullptr;
+		bool rest = true; // anything left for the CTA-per-group kernel?
+		if (p <= kHcSmallMaxFeatures) {
+			// p <= 8: four lanes per group, everything in registers (hc_small.cuh); groups above kHcSmallMaxRows
+			// rows are listed for hc_kernel. The QR queue's list is free by now (qr_fit_kernel is enqueued) and is
+			// reused; the counter is a slot of its own in the block the call cleared at its start.
+			int *hc_count = ws.big_count + 176;
+			HcSmallArgs hs;
+			hs.offsets = offsets;
+			hs.y = y;
+			hs.x = x;
+			hs.w = wuse;
+			hs.train = train_use;
+			hs.n_groups = G;
+			hs.hc_type = opt->hc_type;
+			hs.big_list = ws.qr_list;
+			hs.big_count = hc_count;
+			const int64_t per_cta = 128 / 4;
+			const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((G + per_cta - 1) / per_cta, (int64_t)di.sms * 16));
+			CU(launch_hc_small(p, hs, P, fo, grid, st), "hc_small_kernel");
+			LAUNCHED();
+			ha.list = ws.qr_list;
+			ha.count = hc_count;
+			rest = N > kHcSmallMaxRows;
+		}
+		if (rest) {
+			const size_t dyn = hc_smem_bytes(p);
+			CU(cudaFuncSetAttribute(hc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn), "hc_kernel attr");
+			const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)200 * 1024 / (dyn + 1024)));
+			const int64_t most = ha.list ? std::min<int64_t>(G, N / kHcSmallMaxRows) : G;
+			hc_kernel<<<(unsigned)std::max<int64_t>(1, std::min<int64_t>(most, (int64_t)di.sms * per_sm)), kHcThreads, dyn, st>>>(ha, P, fo);
+			LAUNCHED();
+			CU(cudaGetLastError(), "hc_kernel");
+		}
 	}
 	timer_mark(st);
 

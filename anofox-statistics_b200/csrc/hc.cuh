@@ -34,6 +34,9 @@ struct HcArgs {
 	int flags_from_y;
 	int64_t n_groups;
 	int hc_type; // AnofoxHcType 1 .. 4
+	// list mode (after hc_small_kernel): only the groups list[0 .. *count); null = every group
+	const int64_t *list;
+	const int *count;
 };
 
 // dynamic shared memory: L (k x k) | Linv (k x k) | S (k x k) | zbuf (chunk x k) | om (chunk) | shift (k) | beta (k) | idx
@@ -64,7 +67,9 @@ __global__ void __launch_bounds__(kHcThreads) hc_kernel(HcArgs a, FitParams P, A
 	__shared__ int s_first, s_k, s_bad;
 	const double nanv = nan_f64();
 	const DfTables Tb{P.tcrit, P.gratio, P.rcp, P.ce, P.co};
-	for (int64_t g = blockIdx.x; g < a.n_groups; g += gridDim.x) {
+	const int64_t n_todo = a.list ? (int64_t)*a.count : a.n_groups;
+	for (int64_t it = blockIdx.x; it < n_todo; it += gridDim.x) {
+		const int64_t g = a.list ? a.list[it] : it;
 		__syncthreads();
 		if (o.status[g] != 0 || (o.has_inference && o.has_inference[g] == 0)) continue;
 		const int64_t r0 = a.offsets[g], r1 = a.offsets[g + 1];

@@ -428,6 +428,58 @@ def run_finalize_pattern(args, rank, threads_list=(1, 8, 16), groups_per_call=20
     return res if rank == 0 else None
 
 
+def run_next_rows(args, rank, d, G, n, p):
+    """The rows SURVEY section 8(f) marks "next", timed on the headline's data (C2's shape), a few steps each:
+    device ingest of scan-order rows (f-3), HC1 robust standard errors (f-4), column-major array fits (f-2)."""
+    import torch
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    N = G * n
+    res = {}
+
+    def timed(fn, steps=3, warm=2):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    peak = measured_peak_gbs()[0]
+    # f-4: HC1 on top of the full-inference fit
+    fit = pkg.DeviceFit(G, N, p, inference=True)
+    base = timed(lambda: fit.fit(d["offsets"], d["y"], d["x"], None, method="ols", compute_inference=True))
+    l0 = pkg.launch_count()
+    hc = timed(lambda: fit.fit(d["offsets"], d["y"], d["x"], None, method="ols", compute_inference=True, hc_type="hc1"))
+    res["hc1_on_c2"] = {"ms_per_step": hc, "ms_without_hc": base, "hc_pass_ms": hc - base,
+                        "gpu_launches_per_step": (pkg.launch_count() - l0) // 5,
+                        "finite_std_errors": int(torch.isfinite(fit.out["std_errors"]).all(dim=1).sum().item())}
+    # f-2: the same rows as p columns per fit (the layout of ols_fit(y LIST, x LIST(LIST)))
+    xc = d["x"].view(G, n, p).transpose(1, 2).contiguous().view(-1)
+    col = timed(lambda: fit.fit_columns(d["offsets"], d["y"], xc, None, method="ols", compute_inference=True))
+    res["column_fits_on_c2"] = {"ms_per_step": col, "fits_per_sec": G / (col * 1e-3), "transpose_and_fit_vs_fit_ms": [col, base]}
+    del xc, fit
+    torch.cuda.empty_cache()
+    # f-3: scan-order rows -> group-sorted CSR
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(5)
+    gid = torch.randint(0, G, (N,), generator=gen, dtype=torch.int64, device="cuda")
+    ing = pkg.DeviceIngest(N, p, G)
+    ms = timed(lambda: ing.run(gid, d["y"], d["x"]))
+    byts = N * (8 + 2 * 8 * (p + 1) + 8)  # ids in, rows in + out, row index out
+    ok = bool((ing.offsets[1:] - ing.offsets[:-1]).sum().item() == N) and ing.bad_ids() == 0
+    res["ingest_50m_rows"] = {"ms_per_step": ms, "rows_per_sec": N / (ms * 1e-3), "algorithmic_bytes": byts,
+                              "frac_of_hbm_peak": byts / (ms * 1e-3) / 1e9 / peak, "offsets_consistent": ok,
+                              "what": "%d scan-order rows x %d features, %d groups: stable radix partition + gather" % (N, p, G)}
+    del ing, gid
+    torch.cuda.empty_cache()
+    return res if rank == 0 else None
+
+
 def run_group_workload(args, wname, rank, world, local, steps, warmup, headline, data_cache=None):
     """One group-sharded workload on this rank (weak scaling: every rank fits its own copy of the shape).
     Returns the result dict on rank 0 (None elsewhere)."""
@@ -687,6 +739,10 @@ def main():
     cache = {}
     r = run_group_workload(args, args.workload, rank, world, local, args.steps, args.warmup, True, cache)
     secondary = {}
+    if not args.no_secondary and args.workload == "C2" and world == 1 and "d" in cache:
+        nr = run_next_rows(args, rank, cache["d"], r["G"], r["n"], r["p"])
+        if rank == 0:
+            secondary["next_rows"] = nr
     if not args.no_secondary and args.workload == "C2" and args.scale == 1.0:
         # the other BASELINE configs, a few steps each, so that the driver's BENCH / SCALE records time them too
         for wn in ("C1", "C3r", "C3w", "C5"):

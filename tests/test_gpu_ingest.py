@@ -72,3 +72,45 @@ def test_unsorted_rows_to_fits_match_the_oracle(b200, oracle):
     off = np.concatenate([[0], np.cumsum(np.bincount(gid, minlength=G))]).astype(np.int64)
     ora = oracle.fit_batch(off, y[order], x[order], None, method="ols", compute_inference=True)
     assert_fit_parity(got, ora, rtol=1e-9, inference=True, label="ingest -> fit")
+
+
+def test_ingest_and_column_fits_degenerate_inputs(b200, oracle):
+    """Zero rows, every row in one group, and a column-fit batch that holds empty fits."""
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    # no rows: offsets all zero
+    ing = b200.DeviceIngest(0, 2, 5)
+    ing.run(dev(np.zeros(0, dtype=np.int64)), dev(np.zeros(0)), dev(np.zeros((0, 2))))
+    torch.cuda.synchronize()
+    assert np.array_equal(ing.offsets.cpu().numpy(), np.zeros(6, dtype=np.int64)) and ing.bad_ids() == 0
+    # every row in the last of many groups
+    N, G = 5000, 1 << 16
+    rng = np.random.default_rng(3)
+    y, x = rng.normal(size=N), rng.normal(size=(N, 2))
+    ing = b200.DeviceIngest(N, 2, G)
+    ing.run(dev(np.full(N, G - 1, dtype=np.int64)), dev(y), dev(x))
+    torch.cuda.synchronize()
+    off = ing.offsets.cpu().numpy()
+    assert off[-1] == N and (off[:-1] == 0).all()
+    assert np.array_equal(ing.y.cpu().numpy(), y) and np.array_equal(ing.x.cpu().numpy(), x)
+    # column fits: empty fits between ordinary ones give the reference's error code for them, the others fit
+    sizes = np.array([0, 12, 0, 0, 30, 1])
+    offc = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    p = 2
+    ys, blocks, cols = [], [], []
+    for n in sizes:
+        X = rng.normal(size=(int(n), p))
+        ys.append(1.0 + X @ np.array([0.5, -2.0]) + rng.normal(0, 0.1, size=int(n)))
+        blocks.append(X.T.reshape(-1))
+        cols.append([X[:, j].copy() for j in range(p)])
+    fit = b200.DeviceFit(len(sizes), int(offc[-1]), p, inference=False)
+    out = fit.fit_columns(dev(offc), dev(np.concatenate(ys)), dev(np.concatenate(blocks)), None, method="ols")
+    torch.cuda.synchronize()
+    st = out["status"].cpu().numpy()
+    for i, n in enumerate(sizes):
+        if n == 0:
+            assert st[i] != 0, i
+            continue
+        r = oracle.single_fit("ols", ys[i], cols[i], None)
+        assert st[i] == (0 if r.ok else r.error_code), (i, st[i])
+        if r.ok:
+            assert np.allclose(out["coefficients"][i].cpu().numpy(), np.asarray(r.coefficients), rtol=1e-9, atol=1e-12)

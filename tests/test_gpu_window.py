@@ -93,3 +93,29 @@ def test_window_rejects_wide_designs(lib, b200):
     off = np.array([0, 30], dtype=np.int64)
     with pytest.raises(b200.B200Error):
         lib.window_fit_predict_host(off, np.zeros(30), np.zeros((30, 9)), None, method="ols")
+
+
+def test_window_degenerate_inputs(lib, oracle):
+    """Empty input, empty partitions between full ones, one-row partitions, a frame that never holds enough rows,
+    and the argument checks of the entry point (frame end, feature limit)."""
+    # no rows at all
+    dev = lib.window_fit_predict_host(np.zeros(1, dtype=np.int64), np.zeros(0), np.zeros((0, 2)), None, preceding=-1, end_offset=1)
+    assert all(dev[k].size == 0 for k in ("yhat", "yhat_lower", "yhat_upper"))
+    # empty and one-row partitions next to ordinary ones
+    rng = np.random.default_rng(77)
+    sizes = np.array([0, 1, 0, 25, 1, 2, 0, 40, 3, 0])
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    N = int(off[-1])
+    x = rng.uniform(-3, 3, size=(N, 2))
+    y = 1.0 + x @ np.array([2.0, -1.0]) + rng.normal(0, 0.5, size=N)
+    for prec, end in ((-1, 1), (1, 0), (2, 1)):  # the last two frames never reach p + 2 rows: every prediction NULL
+        dev = lib.window_fit_predict_host(off, y, x, None, preceding=prec, end_offset=end)
+        ora = oracle.window_fit_predict(off, y, x, None, preceding=prec, end_offset=end)
+        check(dev, ora, f"degenerate prec={prec} end={end}")
+        if prec > 0:
+            assert np.isnan(dev["yhat"]).all()
+    # argument checks
+    with pytest.raises(lib.B200Error, match="frame end"):
+        lib.window_fit_predict_host(off, y, x, None, preceding=-1, end_offset=-1)
+    with pytest.raises(lib.B200Error, match="up to 8 features"):
+        lib.window_fit_predict_host(np.array([0, 20], dtype=np.int64), np.zeros(20), np.zeros((20, 9)), None, preceding=-1, end_offset=1)
