@@ -113,4 +113,5 @@ def test_ingest_and_column_fits_degenerate_inputs(b200, oracle):
         r = oracle.single_fit("ols", ys[i], cols[i], None)
         assert st[i] == (0 if r.ok else r.error_code), (i, st[i])
         if r.ok:
-            assert np.allclose(out["coefficients"][i].cpu().numpy(), np.asarray(r.coefficients), rtol=1e-9, atol=1e-12)
+            assert np.allclose(out["coefficients"][i].cpu().numpy(), np.asarray(r.coefficients), rtol=1e-9, atol=1e-12,
+                               equal_nan=True)
