@@ -75,6 +75,8 @@ def load_library():
     lib.anofox_b200_ingest_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.c_size_t, C.c_void_p, E]
+    lib.anofox_b200_ingest_device_static.restype = C.c_int32
+    lib.anofox_b200_ingest_device_static.argtypes = [C.c_void_p] * 4 + [C.c_int64, C.c_int32, C.c_int64] + [C.c_void_p] * 7 + [E]
     lib.anofox_b200_ingest_bad_ids.restype = C.c_int32
     lib.anofox_b200_ingest_bad_ids.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
     lib.anofox_b200_fit_columns_workspace_bytes.restype = C.c_size_t
@@ -277,6 +279,20 @@ class DeviceIngest:
 
     def bad_ids(self):
         return int(load_library().anofox_b200_ingest_bad_ids(C.c_void_p(self.ws_ptr), self.N, self.G))
+
+
+INGEST_STATIC_MAX_BYTES = 16 * 1024 * 1024  # ANOFOX_B200_INGEST_STATIC_MAX_BYTES (include/anofox_b200.h)
+
+
+def ingest_device_static(group_ids, y, x, w, N, p, G, offsets_out, y_out, x_out, w_out, row_index_out, bad_ids_out, stream=0):
+    """anofox_b200_ingest_device_static: the ingest with the library's built-in scratch array (no allocation).
+    Every argument is a raw device address (or None); raises B200Error beyond the array's size."""
+    err = abi.AnofoxError()
+    v = lambda a: None if a is None else C.c_void_p(a)  # noqa: E731
+    rc = load_library().anofox_b200_ingest_device_static(v(group_ids), v(y), v(x), v(w), N, p, G, v(offsets_out), v(y_out),
+                                                         v(x_out), v(w_out), v(row_index_out), v(bad_ids_out),
+                                                         C.c_void_p(stream), C.byref(err))
+    _check(rc, err)
 
 
 def window_workspace_bytes(N, p):

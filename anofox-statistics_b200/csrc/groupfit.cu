@@ -2615,6 +2615,81 @@ int32_t anofox_b200_ingest_bad_ids(const void *workspace, int64_t n_rows, int64_
 	return v;
 }
 
+// ---- ingest without any allocation: scratch in a file-scope device array ----------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it). No counterpart in the reference. The scratch of the radix
+// partition (keys, row indices, histograms, counters: ingest_carve) lives in g_ingest_static_scratch, which every
+// GPU that loads the library holds until the process exits. In HOST code the array's name is only a stand-in for
+// the symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device, with that device
+// current, and that pointer is what the kernels get.
+static __device__ __align__(256) unsigned char g_ingest_static_scratch[ANOFOX_B200_INGEST_STATIC_MAX_BYTES];
+
+static int ingest_static_scratch(unsigned char **out, AnofoxError *err) {
+	static std::mutex mu;
+	static unsigned char *addr[64];
+	int dev = -1;
+	cudaError_t e = cudaGetDevice(&dev);
+	if (e != cudaSuccess || dev < 0 || dev >= 64) {
+		set_error(err, ANOFOX_ERROR_INTERNAL, e != cudaSuccess ? cudaGetErrorString(e) : "device ordinal out of range");
+		return ANOFOX_ERROR_INTERNAL;
+	}
+	std::lock_guard<std::mutex> lock(mu);
+	if (!addr[dev]) {
+		void *ptr = nullptr;
+		e = cudaGetSymbolAddress(&ptr, g_ingest_static_scratch);
+		if (e != cudaSuccess || !ptr) {
+			char msg[200];
+			snprintf(msg, sizeof msg, "cudaGetSymbolAddress(g_ingest_static_scratch): %s", cudaGetErrorString(e));
+			set_error(err, ANOFOX_ERROR_INTERNAL, msg);
+			return ANOFOX_ERROR_INTERNAL;
+		}
+		addr[dev] = (unsigned char *)ptr;
+	}
+	*out = addr[dev];
+	return 0;
+}
+
+int32_t anofox_b200_ingest_device_static(const int64_t *group_ids, const double *y, const double *x, const double *w,
+                                         int64_t n_rows, int32_t n_features, int64_t n_groups, int64_t *offsets_out,
+                                         double *y_out, double *x_out, double *w_out, int64_t *row_index_out,
+                                         int32_t *bad_ids_out, void *stream, AnofoxError *err) {
+	return guarded(err, "ingest_device_static", [&]() -> int32_t {
+		clear_error(err);
+		DeviceInfo &di = device_info();
+		if (!di.ok) {
+			set_error(err, ANOFOX_ERROR_INTERNAL, di.why);
+			return ANOFOX_ERROR_INTERNAL;
+		}
+		if (n_rows < 0 || n_groups <= 0) {
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, "ingest: bad arguments");
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		IngestWs ws;
+		const size_t need = ingest_carve(ws, nullptr, n_rows, n_groups);
+		if (need > (size_t)ANOFOX_B200_INGEST_STATIC_MAX_BYTES) {
+			char msg[240];
+			snprintf(msg, sizeof msg,
+			         "ingest_device_static: %lld rows x %lld groups need %zu bytes of scratch, the built-in array holds %zu "
+			         "(ANOFOX_B200_INGEST_STATIC_MAX_BYTES); use anofox_b200_ingest_device with a workspace",
+			         (long long)n_rows, (long long)n_groups, need, (size_t)ANOFOX_B200_INGEST_STATIC_MAX_BYTES);
+			set_error(err, ANOFOX_ERROR_INVALID_INPUT, msg);
+			return ANOFOX_ERROR_INVALID_INPUT;
+		}
+		unsigned char *scratch = nullptr;
+		int rc = ingest_static_scratch(&scratch, err);
+		if (rc) return rc;
+		// ingest_device clears the counters and the flag it needs at zero itself; everything else is overwritten
+		rc = ingest_device(group_ids, y, x, w, n_rows, n_features, n_groups, offsets_out, y_out, x_out, w_out, row_index_out,
+		                   scratch, (size_t)ANOFOX_B200_INGEST_STATIC_MAX_BYTES, (cudaStream_t)stream, err);
+		if (rc) return rc;
+		if (bad_ids_out) {
+			ingest_carve(ws, scratch, n_rows, n_groups);
+			CU(cudaMemcpyAsync(bad_ids_out, ws.bad, sizeof(int32_t), cudaMemcpyDeviceToDevice, (cudaStream_t)stream), "bad flag copy");
+		}
+		return 0;
+	});
+}
+
 size_t anofox_b200_fit_columns_workspace_bytes(int64_t n_fits, int64_t n_rows, int32_t n_features) {
 	if (n_fits < 0 || n_rows < 0 || n_features <= 0 || n_features > kMaxFeatures) return 0;
 	DeviceInfo &di = device_info();

@@ -310,6 +310,25 @@ int32_t anofox_b200_ingest_device(const int64_t *group_ids, const double *y, con
  * synchronising read of one flag. */
 int32_t anofox_b200_ingest_bad_ids(const void *workspace, int64_t n_rows, int64_t n_groups);
 
+/* Ingest WITHOUT any allocation. No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and result (bit for bit) as anofox_b200_ingest_device, but the scratch of the radix partition is
+ * a file-scope device array inside the library (ANOFOX_B200_INGEST_STATIC_MAX_BYTES = 16 MiB, held by every GPU that
+ * loads the library until the process exits) instead of a caller workspace. The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine) and only enqueues work on `stream`.
+ *   limit   anofox_b200_ingest_workspace_bytes(n_rows, n_groups) <= ANOFOX_B200_INGEST_STATIC_MAX_BYTES -- about
+ *           16.5 bytes per row + 4 per group, e.g. 900 000 rows x 100 000 groups; beyond it the call returns
+ *           ANOFOX_ERROR_INVALID_INPUT with a message that names both sizes.
+ *   sharing every call on a device uses the SAME array: calls that overlap on the GPU (two streams, two threads) race;
+ *           serialise them. The array keeps the last call's contents; the call clears what it needs at zero itself.
+ *   bad_ids_out  optional DEVICE int32: set to 1 when an id was outside [0, n_groups) (what anofox_b200_ingest_bad_ids
+ *           reports for the workspace form), else 0; written on `stream`. */
+#define ANOFOX_B200_INGEST_STATIC_MAX_BYTES (16u * 1024u * 1024u)
+int32_t anofox_b200_ingest_device_static(const int64_t *group_ids, const double *y, const double *x, const double *w,
+                                         int64_t n_rows, int32_t n_features, int64_t n_groups, int64_t *offsets_out,
+                                         double *y_out, double *x_out, double *w_out, int64_t *row_index_out,
+                                         int32_t *bad_ids_out, void *stream, AnofoxError *err);
+
 /* Scalar array fits, batched: {ols,ridge,wls}_fit(y LIST, x LIST(LIST) [, w LIST]) computes ONE fit per SQL row from
  * column arrays (src/table_functions/ols_fit.cpp:120-173 makes one anofox_ols_fit call per row of the DataChunk).
  * This entry point takes all rows of a chunk (or of a query) at once:
