@@ -451,15 +451,15 @@ def fit_predict_batch_host_into(offsets, y, x, w, train, pred_struct, fit_struct
 def force_path(path):
     """Test / A-B hook: "auto", "record" (always the DMMA accumulation kernel + solve kernel) or "fused"
     (small groups through the single rows-to-results kernel instead of accumulate + register solve)."""
-    load_library().anofox_b200_force_path({"auto": 0, "record": 1, "fused": 2, "stages": 3, "ringslice": 4, "qr": 5, "stash": 6, "split": 7}[path])
+    load_library().anofox_b200_force_path({"auto": 0, "record": 1, "fused": 2, "stages": 3, "ringslice": 4, "qr": 5, "stash": 6, "split": 7, "resident": 8}[path])
 
 
 def plan(G, N, p, has_w=False, has_train=False):
     """("stash" | "fused", lanes_per_group) or ("record", 0): the kernel path a batch of this shape takes.
     "stash" = the one-launch rows-to-results kernel, "fused" = accumulate-to-record kernel + register solve kernel."""
     t = C.c_int32(0)
-    r = load_library().anofox_b200_plan(G, N, p, int(has_w), int(has_train), C.byref(t))
-    return {0: "record", 1: "fused", 2: "stash"}[r], int(t.value)
+    r = load_library().anofox_b200_plan(G, N, p, int(has_w), 2 if has_train == "predict" else int(bool(has_train)), C.byref(t))
+    return {0: "record", 1: "fused", 2: "stash", 3: "resident"}[r], int(t.value)
 
 
 def moment_block_len(p):

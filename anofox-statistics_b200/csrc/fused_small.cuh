@@ -58,19 +58,29 @@ __device__ __forceinline__ double shfl_xor_f64(unsigned mask, double v, int off)
 //   CHECK = false: fast path. Rows are masked only by w > 0 / the training flag; non-finite values
 //                  poison the sums and the caller re-runs with CHECK = true.
 //   CHECK = true : the full row filter of ols.rs:59-66 / wls.rs:76-86.
-template <int P, bool HASW, bool HAST, bool CHECK>
+//   ROT (P a power of two): slot c of the lane holds column (c + rot) mod P, rot = small_rot<P>(q). A row of
+//                  P = 8 doubles is 16 banks wide, so with every lane on column c the 16 lanes of a half-warp
+//                  meet in 2 bank pairs (8-way conflict); walking the columns in an order shifted by q / 2 spreads
+//                  them over all 32 banks. sh is in slot order too; the caller undoes the rotation of the sums
+//                  (small_unrotate) before anything combines the lanes.
+template <int P> __device__ __forceinline__ int small_rot(int q) { return ((q * 2 * P) >> 5) & (P - 1); }
+template <int P, bool HASW, bool HAST, bool CHECK, bool ROT = false>
 __device__ __forceinline__ void small_accumulate(SmallMoments<P> &M, const SmemGroup &sg, int n, int q, int T,
                                                  const double (&sh)[P + 1]) {
 	constexpr int K = P + 1;
+	static_assert(!ROT || (P & (P - 1)) == 0, "rotated column order: P must be a power of two");
 	uint32_t px = sg.x + (uint32_t)(q * P) * 8u, py = sg.y + (uint32_t)q * 8u;
 	uint32_t pw = sg.w + (uint32_t)q * 8u, pt = sg.t + (uint32_t)q;
 	const uint32_t stepx = (uint32_t)(T * P) * 8u, stepy = (uint32_t)T * 8u;
 	constexpr bool MASK = HASW || HAST || CHECK;
+	uint32_t co[P]; // byte offset of slot c's column inside the row
+#pragma unroll
+	for (int c = 0; c < P; ++c) co[c] = ROT ? (uint32_t)((c + small_rot<P>(q)) & (P - 1)) * 8u : (uint32_t)c * 8u;
 #pragma unroll 2
 	for (int i = q; i < n; i += T) {
 		double d[K];
 #pragma unroll
-		for (int c = 0; c < P; ++c) d[c] = lds_f64(px + (uint32_t)c * 8u);
+		for (int c = 0; c < P; ++c) d[c] = ROT ? lds_f64(px + co[c]) : lds_f64(px + (uint32_t)c * 8u);
 		d[P] = lds_f64(py);
 		px += stepx;
 		py += stepy;
@@ -112,6 +122,37 @@ __device__ __forceinline__ void small_accumulate(SmallMoments<P> &M, const SmemG
 			}
 		}
 	}
+}
+
+// Undo the slot order of a ROT accumulation: slot c held column (c + rot) mod P, so column t sits in slot (t - rot) mod P.
+// rot = sum of its bits s: one conditional, compile-time permutation per bit (new[t] = old[(t - s) mod P]).
+template <int P, int S, bool HASW> __device__ __forceinline__ void small_unrotate_step(SmallMoments<P> &M, bool on) {
+	constexpr int K = P + 1;
+	SmallMoments<P> R;
+#pragma unroll
+	for (int i = 0; i < P; ++i) {
+		const int si = (i - S) & (P - 1);
+#pragma unroll
+		for (int j = i; j < P; ++j) {
+			const int sj = (j - S) & (P - 1);
+			R.s2[utri(i, j, K)] = M.s2[utri(si < sj ? si : sj, si < sj ? sj : si, K)];
+		}
+		R.s2[utri(i, P, K)] = M.s2[utri(si, P, K)];
+		R.s1[i] = M.s1[si];
+		R.q2[i] = M.q2[si];
+	}
+#pragma unroll
+	for (int i = 0; i < P; ++i) {
+#pragma unroll
+		for (int j = i; j <= P; ++j) M.s2[utri(i, j, K)] = on ? R.s2[utri(i, j, K)] : M.s2[utri(i, j, K)];
+		M.s1[i] = on ? R.s1[i] : M.s1[i];
+		if (HASW) M.q2[i] = on ? R.q2[i] : M.q2[i];
+	}
+}
+template <int P, bool HASW> __device__ __forceinline__ void small_unrotate(SmallMoments<P> &M, int rot) {
+	if (P >= 2) small_unrotate_step<P, 1 % (P > 1 ? P : 2), HASW>(M, (rot & 1) != 0);
+	if (P >= 4) small_unrotate_step<P, 2 % (P > 2 ? P : 4), HASW>(M, (rot & 2) != 0);
+	if (P >= 8) small_unrotate_step<P, 4 % (P > 4 ? P : 8), HASW>(M, (rot & 4) != 0);
 }
 
 // Butterfly over the T lanes of a group: afterwards every lane holds the group's sums.
@@ -193,7 +234,16 @@ struct SmallGroupView {
 	// record written here (array-of-records layout, rec_len(P) doubles per group) at the moment it is queued
 	double *rec_out;
 	double *stash; // stash kernel: this group's slot (field f at stash[f * 32])
+	// resident kernel (small_group<..., TEAM = 2>): two warps share the accumulation of one group. Warp team_w = 1 folds
+	// rows 32 + lane, 96 + lane, ..., leaves its warp-reduced sums in team_x (shared memory, kSmallTeamDoubles) and
+	// returns; warp 0 adds them after the named barrier team_bar (64 threads) and carries on alone.
+	int team_w, team_bar;
+	double *team_x;
 };
+constexpr int kSmallTeamDoubles = 72; // >= NS2 + K + 1 + P + 2 for P = 8
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+	asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 
 // First row (in state order) that passes `pred(row)`, searched by the T lanes together; -1 if none.
 template <class Pred> __device__ __forceinline__ int small_first_row(const SmallGroupView &v, Pred pred) {
@@ -643,7 +693,7 @@ __device__ __forceinline__ void small_stash_load(const double *__restrict__ sl, 
 	for (int c = 0; c < P; ++c) M.q2[c] = 0.0;
 }
 
-template <int P, bool HASW, bool HAST, int MODE>
+template <int P, bool HASW, bool HAST, int MODE, bool ROT = false, int TEAM = 1>
 __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, const FitParams &Pm,
                                             const AnofoxB200FitOutputs &o, double *records, int64_t n_groups) {
 	constexpr int K = P + 1;
@@ -687,25 +737,70 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 	}
 	bool redo = false;
 	M.clear();
-	if (have && f >= 0) {
+	// ROT: the lane's accumulation runs in slot order (small_accumulate) with the shift in the same order
+	auto load_shift = [&](int frow, double (&dst)[K], bool slots) {
 #pragma unroll
-		for (int c = 0; c < P; ++c) sh[c] = lds_f64(v.sg.x + (uint32_t)(f * P + c) * 8u);
-		sh[P] = lds_f64(v.sg.y + (uint32_t)f * 8u);
-		small_accumulate<P, HASW, HAST, false>(M, v.sg, n, v.q, v.T, sh);
+		for (int c = 0; c < P; ++c) {
+			const int col = (ROT && slots) ? ((c + small_rot<P>(v.q)) & (P - 1)) : c;
+			dst[c] = lds_f64(v.sg.x + (uint32_t)(frow * P + col) * 8u);
+		}
+		dst[P] = lds_f64(v.sg.y + (uint32_t)frow * 8u);
+	};
+	if (have && f >= 0) {
+		load_shift(f, sh, true);
+		small_accumulate<P, HASW, HAST, false, ROT>(M, v.sg, n, TEAM > 1 ? v.q + v.T * v.team_w : v.q, TEAM * v.T, sh);
+		if (ROT) {
+			small_unrotate<P, HASW>(M, small_rot<P>(v.q));
+			load_shift(f, sh, false);
+		}
 		redo = reduce();
 		if (!(HASW || HAST)) M.nv = n;
 	} else if (have) {
 		redo = true; // no row passes the mask: the checked path settles n_state / NO_VALID_DATA
+	}
+	if (TEAM > 1) {
+		static_assert(TEAM <= 2 && (TEAM == 1 || (MODE == 1 && HAST)), "teams: fused mode with training flags, two warps");
+		double *tx = v.team_x;
+		if (v.team_w != 0) {
+			if (v.q == 0) {
+#pragma unroll
+				for (int i = 0; i < SmallMoments<P>::NS2; ++i) tx[i] = M.s2[i];
+#pragma unroll
+				for (int i = 0; i < K; ++i) tx[SmallMoments<P>::NS2 + i] = M.s1[i];
+				tx[SmallMoments<P>::NS2 + K] = M.sw;
+#pragma unroll
+				for (int i = 0; i < P; ++i) tx[SmallMoments<P>::NS2 + K + 1 + i] = M.q2[i];
+				tx[SmallMoments<P>::NS2 + K + 1 + P] = (double)M.nv;
+				tx[SmallMoments<P>::NS2 + K + 2 + P] = (double)M.ns;
+			}
+			named_bar_sync(v.team_bar, 64);
+			return;
+		}
+		named_bar_sync(v.team_bar, 64);
+#pragma unroll
+		for (int i = 0; i < SmallMoments<P>::NS2; ++i) M.s2[i] += tx[i];
+#pragma unroll
+		for (int i = 0; i < K; ++i) M.s1[i] += tx[SmallMoments<P>::NS2 + i];
+		M.sw += tx[SmallMoments<P>::NS2 + K];
+#pragma unroll
+		for (int i = 0; i < P; ++i) M.q2[i] += tx[SmallMoments<P>::NS2 + K + 1 + i];
+		M.nv += (int)tx[SmallMoments<P>::NS2 + K + 1 + P];
+		M.ns += (int)tx[SmallMoments<P>::NS2 + K + 2 + P];
+#pragma unroll
+		for (int c = 0; c < K; ++c) redo = redo || !finite_f64(M.s2[utri(c, c, K)]);
+		if (HASW) redo = redo || !finite_f64(M.sw);
 	}
 	if (redo) {
 		// a non-finite value somewhere: the full row filter of ols.rs:59-66
 		f = small_first_row(v, [&](int i) { return small_row_valid_full<P, HASW, HAST>(v, i); });
 		M.clear();
 		if (f >= 0) {
-#pragma unroll
-			for (int c = 0; c < P; ++c) sh[c] = lds_f64(v.sg.x + (uint32_t)(f * P + c) * 8u);
-			sh[P] = lds_f64(v.sg.y + (uint32_t)f * 8u);
-			small_accumulate<P, HASW, HAST, true>(M, v.sg, n, v.q, v.T, sh);
+			load_shift(f, sh, true);
+			small_accumulate<P, HASW, HAST, true, ROT>(M, v.sg, n, v.q, v.T, sh);
+			if (ROT) {
+				small_unrotate<P, HASW>(M, small_rot<P>(v.q));
+				load_shift(f, sh, false);
+			}
 		} else if (HAST) {
 			for (int i = v.q; i < n; i += v.T) M.ns += lds_u8(v.sg.t + (uint32_t)i) != 0u ? 1 : 0;
 		}

@@ -31,6 +31,8 @@
 #include "qr.cuh"
 #include "hc.cuh"
 #include "hc_launch.h"
+#include "resident.cuh"
+#include "resident_launch.h"
 #include "window.cuh"
 #include "window_launch.h"
 #include "ingest.cuh"
@@ -202,11 +204,18 @@ __global__ void default_train_y_kernel(const double *__restrict__ y, int64_t n_r
 // One warp per group: yhat and the simplified interval of anofox_predict_with_interval
 // (lib.rs:2292-2347) for every row of the group, in input order.
 // flags_y != null: also write is_training[r] = flags_y[r] && no NaN feature in row r.
+// list != null: only the groups list[0 .. *count) (after the resident kernel: the big groups and the groups the QR
+// fallback re-fitted).
 __global__ void predict_kernel(const int64_t *__restrict__ offsets, int64_t n_groups, const double *__restrict__ x,
                                int p, FitParams P, AnofoxB200FitOutputs fit, AnofoxB200PredictOutputs out,
-                               const uint8_t *__restrict__ flags_y) {
-	const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+                               const uint8_t *__restrict__ flags_y, const int64_t *__restrict__ list = nullptr,
+                               const int *__restrict__ count = nullptr) {
+	int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int lane = threadIdx.x & 31;
+	if (list) {
+		if (g >= (int64_t)*count) return;
+		g = list[g];
+	}
 	if (g >= n_groups) return;
 	const int64_t r0 = offsets[g], r1 = offsets[g + 1];
 	const double nanv = nan_f64();
@@ -976,6 +985,61 @@ static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 	return r;
 }
 
+// ---- resident fit-predict kernel (resident.cuh): groups between the small-group regime and one stage ----------
+static cudaError_t launch_resident_fp(const ResidentArgs &a, int p, bool has_w, int grid, cudaStream_t st) {
+	cudaError_t e = cudaErrorInvalidValue;
+	switch (p) {
+	case 1: e = launch_resident_fp_p1(has_w, a, grid, st); break;
+	case 2: e = launch_resident_fp_p2(has_w, a, grid, st); break;
+	case 3: e = launch_resident_fp_p3(has_w, a, grid, st); break;
+	case 4: e = launch_resident_fp_p4(has_w, a, grid, st); break;
+	case 5: e = launch_resident_fp_p5(has_w, a, grid, st); break;
+	case 6: e = launch_resident_fp_p6(has_w, a, grid, st); break;
+	case 7: e = launch_resident_fp_p7(has_w, a, grid, st); break;
+	case 8: e = launch_resident_fp_p8(has_w, a, grid, st); break;
+	}
+	LAUNCHED();
+	return e;
+}
+struct ResidentGeom {
+	bool use;
+	int max_groups;
+	StageGeom sg;
+};
+// Used by the fit-predict entry points when p <= 8 and the typical group is larger than the small-group kernels take
+// (24 KB) but three of them still fit the CTA's shared memory (C5: 1 000 rows x 8 features = 73 KB per group).
+// force_path 8 = also below 24 KB (tests), 1 / 3 = never.
+static ResidentGeom resident_geometry(int p, bool has_w, int64_t n_rows, int64_t n_groups, int fp_override = -1) {
+	ResidentGeom r;
+	memset(&r, 0, sizeof r);
+	const int fp = fp_override >= 0 ? fp_override : g_force_path.load();
+	if (!(fp == 0 || fp == 8) || p > kResidentMaxFeatures || n_groups <= 0 || n_rows <= 0) return r;
+	const int64_t row_bytes = 8 * (int64_t)(p + 1) + (has_w ? 8 : 0) + 1;
+	const double mean_rows = (double)n_rows / (double)n_groups;
+	const double mean_bytes = mean_rows * (double)row_bytes;
+	const int64_t budget = (int64_t)227 * 1024 - kResidentStaticBytes;
+	const int64_t slack = 4 * 32 + 4 * 16; // the regions' lead bytes and their 16-byte rounding
+	const int64_t cap_max = (budget / 3 - 128 - slack) / row_bytes;
+	if (mean_rows > (double)cap_max) return r;
+	if (fp != 8 && mean_bytes <= 24.0 * 1024.0) return r;
+	int64_t cap = (int64_t)std::ceil(mean_rows * 1.25) + 8;
+	cap = std::max<int64_t>(cap, 8 * 1024 / row_bytes);
+	cap = std::min(cap, cap_max);
+	StageGeom &g = r.sg;
+	g.cap_rows = (int)cap;
+	g.xcap = align16((int64_t)g.cap_rows * p * 8 + 32);
+	g.ycap = align16((int64_t)g.cap_rows * 8 + 32);
+	g.wcap = has_w ? align16((int64_t)g.cap_rows * 8 + 32) : 0;
+	g.tcap = align16((int64_t)g.cap_rows + 32);
+	g.stage_bytes = (g.xcap + g.ycap + g.wcap + g.tcap + 127) & ~127;
+	g.n_stages = (int)std::min<int64_t>(kResidentMaxStages, budget / g.stage_bytes);
+	if (g.n_stages < 3) return r;
+	g.window_rows = (int64_t)g.cap_rows * 8;
+	r.max_groups = (int)std::max<int64_t>(1, std::min<int64_t>(8, (int64_t)((double)cap / std::max(mean_rows, 1.0))));
+	r.use = true;
+	return r;
+}
+
 static void set_error(AnofoxError *err, int code, const char *msg) {
 	if (!err) return;
 	err->code = (AnofoxErrorCode)code;
@@ -1115,6 +1179,8 @@ static size_t carve(Workspace &w, unsigned char *base, int64_t G, int64_t N, int
 		min_cap = std::min(min_cap, stage_geometry(p, c & 1, c & 2, N, G).cap_rows);
 		const SmallGeom sm = small_geometry(p, c & 1, c & 2, N, G);
 		if (sm.use) min_cap = std::min(min_cap, sm.sg.cap_rows);
+		const ResidentGeom rg = resident_geometry(p, c & 1, N, G, 8); // whichever way the path is forced later
+		if (rg.use) min_cap = std::min(min_cap, rg.sg.cap_rows);
 	}
 	min_cap = std::max(min_cap, 1);
 	const int64_t n_tiles = (N + (int64_t)min_cap * 8 - 1) / ((int64_t)min_cap * 8) + 1;
@@ -1267,6 +1333,12 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 
 	const uint8_t *train_use = nullptr;
 	bool y_only_flags = false;
+	ResidentGeom resident;
+	memset(&resident, 0, sizeof resident);
+	if (pred) {
+		const ResidentGeom rg = resident_geometry(p, wuse != nullptr, N, G);
+		if (rg.use && (g_force_path.load() == 8 || !small_geometry(p, wuse != nullptr, true, N, G).use)) resident = rg;
+	}
 	if (pred) {
 		if (train) {
 			train_use = train;
@@ -1276,6 +1348,9 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 			// of the rule is applied by the checked path and by the predict kernels
 			const SmallGeom sm0 = small_geometry(p, wuse != nullptr, true, N, G);
 			y_only_flags = !wuse && !sm0.use && g_force_path.load() != 3 && pred->is_training != nullptr;
+			// the resident fit-predict kernel has every row in shared memory: it takes the y half of the rule as its
+			// flags, applies the feature half itself and writes is_training
+			if (resident.use) y_only_flags = true;
 			uint8_t *flags = (pred->is_training && !y_only_flags) ? pred->is_training : ws.train_tmp;
 			if (N > 0) {
 				if (y_only_flags)
@@ -1301,16 +1376,17 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		fo.status = ws.f_status;
 	}
 
-	const SmallGeom small = small_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
+	SmallGeom small = small_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
+	if (resident.use) small.use = false;
 	// 0 = auto, 1 = never the small-group kernels, 2 = fused small kernel, 3 = whole-group stages (the
 	// pre-ring DMMA kernel, kept for A/B runs)
-	const bool use_ring = !small.use && g_force_path.load() != 3;
-	const StageGeom sg = small.use ? small.sg : stage_geometry(p, wuse != nullptr, train_use != nullptr, N, G);
+	const bool use_ring = !small.use && !resident.use && g_force_path.load() != 3;
+	const StageGeom sg = small.use ? small.sg : (resident.use ? resident.sg : stage_geometry(p, wuse != nullptr, train_use != nullptr, N, G));
 	CU(cudaMemsetAsync(ws.big_count, 0, 768, st), "memset"); // big_count | refine_count | redo_count
 	// small-group kernels: 2 = stash kernel (rows -> results, one launch), 1 = the redundant-solve fused kernel
 	// (A/B), 0 = accumulate to transposed records + thread-per-group solve kernel
 	const int small_mode = !small.use ? 0 : (small.stash ? 2 : (g_force_path.load() == 2 ? 1 : 0));
-	const bool fused = small_mode != 0;
+	const bool fused = small_mode != 0 || resident.use; // the small groups leave the first kernel solved
 	const bool transposed = small.use && !fused; // record element (g, i) at records[g + i * G]
 	const int64_t rec_gs = transposed ? 1 : rec_len(p), rec_es = transposed ? G : 1;
 	int64_t big_threshold = sg.cap_rows;
@@ -1378,7 +1454,17 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 		a.n_stages = sg.n_stages;
 		const int grid = (int)std::min<int64_t>(di.sms, n_tiles);
 		timer_mark(st);
-		if (small.use) {
+		if (resident.use) {
+			// fit-predict, groups of up to one stage: rows -> fit results and predictions in one kernel
+			ResidentArgs ra;
+			ra.acc = a;
+			ra.params = P;
+			ra.out = fo;
+			ra.pred = *pred;
+			ra.write_is_training = (y_only_flags && pred->is_training) ? 1 : 0;
+			ra.max_stage_groups = resident.max_groups;
+			CU(launch_resident_fp(ra, p, wuse != nullptr, grid, st), "fit_predict_resident_kernel");
+		} else if (small.use) {
 			// fused: rows -> results in one kernel; otherwise rows -> transposed moment records
 			SmallArgs sa;
 			sa.acc = a;
@@ -1454,7 +1540,7 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	} else {
 		CU(launch_solve(ws.records, G, P, fo, ws.refine_count, ws.refine_list, st), "solve_kernel");
 	}
-	if (small_mode != 1 || N > big_threshold) {
+	if ((small_mode != 1 && !resident.use) || N > big_threshold) {
 		RefineArgs ra;
 		ra.offsets = offsets;
 		ra.y = y;
@@ -1533,11 +1619,26 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	}
 	timer_mark(st);
 
-	if (pred && N > 0) {
+	if (pred && N > 0 && resident.use && g_force_path.load() != 5) {
+		// the resident kernel has predicted every group it fitted; what is left: the big groups (fitted by the
+		// streaming path) and the groups the QR fallback re-fitted after their first prediction
+		const int threads = 256;
+		const uint8_t *fy = (y_only_flags && pred->is_training) ? train_use : nullptr;
+		if (N > big_threshold) {
+			const int64_t nbig_max = std::min<int64_t>(G, N / std::max<int64_t>(big_threshold, 1) + 1);
+			predict_kernel<<<(unsigned)((nbig_max * 32 + threads - 1) / threads), threads, 0, st>>>(offsets, G, x, p, P, fo, *pred, fy,
+			                                                                                      ws.big_list, ws.big_count);
+			LAUNCHED();
+		}
+		predict_kernel<<<(unsigned)((G * 32 + threads - 1) / threads), threads, 0, st>>>(offsets, G, x, p, P, fo, *pred, fy, ws.qr_list,
+		                                                                               ws.qr_count);
+		LAUNCHED();
+		CU(cudaGetLastError(), "predict_kernel (lists)");
+	} else if (pred && N > 0) {
 		const int threads = 256;
 		const unsigned blocks = (unsigned)((G * 32 + threads - 1) / threads);
 		const bool flat = (((uintptr_t)x) & 15) == 0;
-		const uint8_t *fy = y_only_flags ? train_use : nullptr;
+		const uint8_t *fy = (y_only_flags && pred->is_training) ? train_use : nullptr;
 		if (flat && p == 2)
 			predict_flat_kernel<2><<<blocks, threads, 0, st>>>(offsets, G, x, P, fo, *pred, fy);
 		else if (flat && p == 4)
@@ -3107,6 +3208,8 @@ int32_t anofox_b200_plan(int64_t n_groups, int64_t n_rows, int32_t n_features, i
                          int32_t *lanes_per_group) {
 	const SmallGeom sm = small_geometry(n_features, has_w != 0, has_train != 0, n_rows, n_groups);
 	if (lanes_per_group) *lanes_per_group = sm.use ? sm.T : 0;
+	// has_train == 2: a fit-predict call; 3 = the resident one-pass kernel takes it
+	if (has_train == 2 && !sm.use && resident_geometry(n_features, has_w != 0, n_rows, n_groups).use) return 3;
 	return sm.use ? (sm.stash ? 2 : 1) : 0;
 }
 

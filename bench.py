@@ -613,13 +613,18 @@ def run_group_workload(args, wname, rank, world, local, steps, warmup, headline,
     inp, outb = algorithmic_bytes(G, N, p, method, inference, predict)
     acc_launch_ms = acc_ms / max(calls, 1)
     acc_bytes = N * (8 * (p + 1) + (8 if method == "wls" else 0)) + 8 * (G + 1)
-    path, lanes = pkg.plan(G, N, p, method == "wls", predict)
+    path, lanes = pkg.plan(G, N, p, method == "wls", "predict" if predict else False)
+    if path == "resident":
+        acc_bytes += N + outb  # one flag byte per row in; fit structs and 25 bytes of predictions per row out
     if path == "stash":
         acc_bytes += outb  # the one-launch kernel also writes the result structs
     achieved = acc_bytes / (acc_launch_ms * 1e-3) / 1e9 if acc_launch_ms > 0 else None
     if path == "stash":
         kname = "fit_small_stash_kernel<%d> (rows -> results in one launch: TMA-staged rows, %d lanes per group, " \
                 "sums parked in shared memory, thread-per-group solve in the same warps)" % (p, lanes)
+    elif path == "resident":
+        kname = "fit_predict_resident_kernel<%d> (rows -> fit results and predictions in one launch: TMA-staged whole " \
+                "groups, FP64 DMMA moments, register solve, predictions from shared memory)" % p
     elif path == "fused":
         kname = "fit_small_kernel<%d> (rows -> moment records, %d lanes per group, TMA-staged)" % (p, lanes)
     else:

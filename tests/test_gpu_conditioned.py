@@ -21,7 +21,7 @@ def lib(b200):
     return b200
 
 
-@pytest.fixture(params=["auto", "stash", "record", "fused", "stages", "qr"])
+@pytest.fixture(params=["auto", "stash", "record", "fused", "stages", "qr", "resident"])
 def path(request, lib):
     lib.force_path(request.param)
     yield request.param

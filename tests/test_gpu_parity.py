@@ -23,7 +23,7 @@ def lib(b200):
     return b200
 
 
-@pytest.fixture(params=["auto", "stash", "record", "fused", "stages", "qr"])
+@pytest.fixture(params=["auto", "stash", "record", "fused", "stages", "qr", "resident"])
 def path(request, lib):
     """The kernel paths: "auto" takes the small-group kernels where they apply (p <= 8, small groups), "record"
     forces the DMMA accumulation kernel + solve kernel everywhere, "fused" / "stages" are the A/B variants, and
