@@ -1006,22 +1006,21 @@ struct ResidentGeom {
 	int max_groups;
 	StageGeom sg;
 };
-// Used by the fit-predict entry points when p <= 8 and the typical group is larger than the small-group kernels take
-// (24 KB) but three of them still fit the CTA's shared memory (C5: 1 000 rows x 8 features = 73 KB per group).
-// force_path 8 = also below 24 KB (tests), 1 / 3 = never.
+// For the fit-predict entry points when p <= 8 and three typical groups fit the CTA's shared memory (C5: 1 000 rows x
+// 8 features = 73 KB per group). Opt-in (force_path 8): measured on C5 the one-pass kernel moves 1.0x instead of 1.7x
+// the algorithmic bytes but is issue-bound (about 10 k warp instructions per group, 8 warps per SM at 255 registers)
+// and ends at 3.85 ms against 3.62 ms for accumulate -> solve -> predict.
 static ResidentGeom resident_geometry(int p, bool has_w, int64_t n_rows, int64_t n_groups, int fp_override = -1) {
 	ResidentGeom r;
 	memset(&r, 0, sizeof r);
 	const int fp = fp_override >= 0 ? fp_override : g_force_path.load();
-	if (!(fp == 0 || fp == 8) || p > kResidentMaxFeatures || n_groups <= 0 || n_rows <= 0) return r;
+	if (fp != 8 || p > kResidentMaxFeatures || n_groups <= 0 || n_rows <= 0) return r;
 	const int64_t row_bytes = 8 * (int64_t)(p + 1) + (has_w ? 8 : 0) + 1;
 	const double mean_rows = (double)n_rows / (double)n_groups;
-	const double mean_bytes = mean_rows * (double)row_bytes;
 	const int64_t budget = (int64_t)227 * 1024 - kResidentStaticBytes;
 	const int64_t slack = 4 * 32 + 4 * 16; // the regions' lead bytes and their 16-byte rounding
 	const int64_t cap_max = (budget / 3 - 128 - slack) / row_bytes;
 	if (mean_rows > (double)cap_max) return r;
-	if (fp != 8 && mean_bytes <= 24.0 * 1024.0) return r;
 	int64_t cap = (int64_t)std::ceil(mean_rows * 1.25) + 8;
 	cap = std::max<int64_t>(cap, 8 * 1024 / row_bytes);
 	cap = std::min(cap, cap_max);

@@ -18,6 +18,15 @@ def lib(b200):
     return b200
 
 
+@pytest.fixture
+def resident(lib):
+    """The one-pass kernel is opt-in (force_path "resident"): on C5 it is issue-bound and a little slower than the
+    three-kernel path it replaces."""
+    lib.force_path("resident")
+    yield lib
+    lib.force_path("auto")
+
+
 PK = ("yhat", "yhat_lower", "yhat_upper")
 
 
@@ -36,7 +45,8 @@ CASES = [("ols", 8, (600, 1100), 60), ("ols", 3, (1500, 2600), 40), ("ridge", 5,
 
 
 @pytest.mark.parametrize("method,p,nr,G", CASES, ids=[f"{c[0]}_p{c[1]}" for c in CASES])
-def test_resident_fit_predict_parity(lib, oracle, method, p, nr, G):
+def test_resident_fit_predict_parity(resident, oracle, method, p, nr, G):
+    lib = resident
     rng = np.random.default_rng(400 + 13 * p + len(method))
     c = make_case(rng, G, nr[0], nr[1], p, dirty=True, weights=(method == "wls"), collinear=True)
     off, y, x, w = c["offsets"], c["y"], c["x"], c["w"]
@@ -95,7 +105,7 @@ def test_resident_matches_the_three_kernel_path_bit_for_status(lib):
     try:
         lib.force_path("record")
         p0, f0 = lib.fit_predict_batch_host(c["offsets"], c["y"], c["x"], None, None, method="ols")
-        lib.force_path("auto")
+        lib.force_path("resident")
         p1, f1 = lib.fit_predict_batch_host(c["offsets"], c["y"], c["x"], None, None, method="ols")
     finally:
         lib.force_path("auto")

@@ -46,3 +46,29 @@ for k, v in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
 print(f"\ntop {top} source lines by stall samples:")
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1])[:top]:
     print(f"{v[0] / 1e6:9.2f}M {100 * v[0] / tot:5.1f}%  samples {100 * v[1] / ts:5.1f}%  {k[0]}:{k[1]}  {k[2]}")
+
+# SASS view: which instructions the warps wait at (top by stall samples, with the opcode)
+sass = subprocess.run(["ncu", "-i", rep] + ksel + ["--page", "source", "--print-source", "sass", "--csv"], capture_output=True, text=True).stdout
+rows = [r for r in csv.reader(io.StringIO(sass))]
+hdr_i = next((i for i, r in enumerate(rows) if "Source" in r and any("Samples" in c for c in r)), None)
+if hdr_i is not None:
+    h = rows[hdr_i]
+    ci = h.index("Source")
+    si = next(i for i, c in enumerate(h) if "Samples" in c)
+    body = []
+    for r in rows[hdr_i + 1:]:
+        try:
+            body.append((int(r[si]), r[ci].strip()[:110]))
+        except (ValueError, IndexError):
+            pass
+    tot_s = sum(b[0] for b in body) or 1
+    print(f"\ncolumns: {h[:12]}\ntop 40 SASS instructions by '{h[si]}' (total {tot_s}):")
+    for n, (smp, txt) in sorted(enumerate(body), key=lambda kv: -kv[1][0])[:40]:
+        print(f"  #{n:6d} {100 * smp / tot_s:5.1f}%  {txt}")
+    # by opcode
+    byop = {}
+    for smp, txt in body:
+        t = txt.split()
+        op = next((w for w in t if not w.startswith("@") and w[0].isalpha()), "?").split(".")[0]
+        byop[op] = byop.get(op, 0) + smp
+    print("stall samples by opcode:", ", ".join(f"{k} {100 * v / tot_s:.1f}%" for k, v in sorted(byop.items(), key=lambda kv: -kv[1])[:16]))
