@@ -399,6 +399,17 @@ class DeviceFit:
             raise B200Error(rc, "debug_counters")
         return dict(zip(("big", "refined", "redone", "huge", "qr"), [int(v) for v in out]))
 
+    def debug_raw(self):
+        """Experiments: the 192-int counter block of the last call as uint64 pairs (synchronises)."""
+        import numpy as np
+        out = (C.c_int32 * 192)()
+        fn = load_library().anofox_b200_debug_raw
+        fn.restype = C.c_int32
+        rc = fn(C.c_void_p(self.ws_ptr), C.c_int64(self.G), C.c_int64(self.N), C.c_int32(self.p), out)
+        if rc != 0:
+            raise B200Error(rc, "debug_raw")
+        return np.frombuffer(bytes(out), dtype=np.uint64)
+
     def fit_predict(self, offsets, y, x, w=None, train=None, stream=None, **opt):
         torch = self.torch
         o = abi.make_fit_options(**opt)

@@ -1462,6 +1462,9 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 			ra.pred = *pred;
 			ra.write_is_training = (y_only_flags && pred->is_training) ? 1 : 0;
 			ra.max_stage_groups = resident.max_groups;
+			// experiments: ANOFOX_B200_RESIDENT_DEBUG=1 -> per-phase clock totals in the spare slots of the counter block
+			static const int env_rdbg = getenv("ANOFOX_B200_RESIDENT_DEBUG") ? atoi(getenv("ANOFOX_B200_RESIDENT_DEBUG")) : 0;
+			ra.dbg = env_rdbg ? (unsigned long long *)(ws.big_count + 64 * 0 + 96 * 0) + 12 : nullptr; // ints 24 .. 55 of the block
 			CU(launch_resident_fp(ra, p, wuse != nullptr, grid, st), "fit_predict_resident_kernel");
 		} else if (small.use) {
 			// fused: rows -> results in one kernel; otherwise rows -> transposed moment records
@@ -3200,6 +3203,16 @@ int32_t anofox_b200_debug_counters(const void *workspace, int64_t n_groups, int6
 	out[2] = h[128];
 	out[3] = h[144];
 	out[4] = h[160];
+	return 0;
+}
+// Experiments: the whole counter block (192 ints) of the last call that used `workspace`.
+int32_t anofox_b200_debug_raw(const void *workspace, int64_t n_groups, int64_t n_rows, int32_t n_features, int32_t *out192) {
+	if (!workspace || !out192 || n_features <= 0 || n_features > kMaxFeatures) return ANOFOX_ERROR_INVALID_INPUT;
+	DeviceInfo &di = device_info();
+	Workspace ws;
+	carve(ws, (unsigned char *)const_cast<void *>(workspace), n_groups, n_rows, n_features, di.sms > 0 ? di.sms : 148);
+	if (cudaDeviceSynchronize() != cudaSuccess) return ANOFOX_ERROR_INTERNAL;
+	if (cudaMemcpy(out192, ws.big_count, 768, cudaMemcpyDeviceToHost) != cudaSuccess) return ANOFOX_ERROR_INTERNAL;
 	return 0;
 }
 // Which path a batch of this shape takes: 1 = fused small-group kernel (lanes_per_group set), 0 = record path.

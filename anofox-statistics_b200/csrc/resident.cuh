@@ -36,6 +36,7 @@ struct ResidentArgs {
 	AnofoxB200PredictOutputs pred;
 	int write_is_training; // the flags came from y alone: is_training = flag && no NaN feature is written here
 	int max_stage_groups;
+	unsigned long long *dbg; // experiments: per-phase clock totals of warp 1 / 2 of every CTA (null = off)
 };
 
 // what the first warp of a team leaves for the prediction pass of both
@@ -82,9 +83,13 @@ __global__ void __launch_bounds__(32 * (kResidentWarps + 1), 1) fit_predict_resi
 	const DfTables Tb{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co};
 	const double nanv = nan_f64();
 	const int rot = ROT ? small_rot<P>(lane) : 0;
+	long long t_wait = 0, t_fit = 0, t_prep = 0, t_bar = 0, t_pred = 0, t_groups = 0;
+	const bool dbg = args.dbg != nullptr && tm == 0;
 	for (int it = 0;; ++it) {
 		const int s = it % NS;
+		long long c0 = dbg ? clock64() : 0;
 		mbar_wait(&full_bar[s], (uint32_t)((it / NS) & 1));
+		if (dbg) t_wait += clock64() - c0;
 		const int cnt = hdr[s].count;
 		if (cnt < 0) break;
 		unsigned char *base = smem + (size_t)s * a.stage_bytes;
@@ -118,7 +123,14 @@ __global__ void __launch_bounds__(32 * (kResidentWarps + 1), 1) fit_predict_resi
 			// ---- 1 + 2. moments (both warps) and solve (first warp) ----
 			if (tw == 0 && want_p && lane == 0) pvw[P + 1] = 0.0;
 			__syncwarp();
+			c0 = dbg ? clock64() : 0;
 			small_group<P, HASW, true, 1, ROT, 2>(v, g, Pm, o, nullptr, a.n_groups);
+			if (dbg) {
+				const long long c1 = clock64();
+				t_fit += c1 - c0;
+				c0 = c1;
+				t_groups += 1;
+			}
 			if (tw == 0) {
 				__syncwarp();
 				if (want_p) {
@@ -164,7 +176,17 @@ __global__ void __launch_bounds__(32 * (kResidentWarps + 1), 1) fit_predict_resi
 					rp[tm].ok = ok ? 1 : 0;
 				}
 			}
+			if (dbg) {
+				const long long c1 = clock64();
+				t_prep += c1 - c0;
+				c0 = c1;
+			}
 			named_bar_sync(tbar, 64);
+			if (dbg) {
+				const long long c1 = clock64();
+				t_bar += c1 - c0;
+				c0 = c1;
+			}
 			// ---- 3. predict every row of the group from shared memory, both warps ----
 			{
 				const bool ok = rp[tm].ok != 0;
@@ -216,9 +238,19 @@ __global__ void __launch_bounds__(32 * (kResidentWarps + 1), 1) fit_predict_resi
 			}
 			// the team's scratch (team_x, rp) is rewritten for the next group only after both warps are here
 			named_bar_sync(tbar, 64);
+			if (dbg) t_pred += clock64() - c0;
 		}
 		__syncwarp();
 		if (lane == 0) mbar_arrive(&empty_bar[s]);
+	}
+	if (dbg && lane == 0) {
+		unsigned long long *d = args.dbg + 8 * tw;
+		atomicAdd(d + 0, (unsigned long long)t_wait);
+		atomicAdd(d + 1, (unsigned long long)t_fit);
+		atomicAdd(d + 2, (unsigned long long)t_prep);
+		atomicAdd(d + 3, (unsigned long long)t_bar);
+		atomicAdd(d + 4, (unsigned long long)t_pred);
+		atomicAdd(d + 5, (unsigned long long)t_groups);
 	}
 }
 
