@@ -239,6 +239,10 @@ struct SmallGroupView {
 	// returns; warp 0 adds them after the named barrier team_bar (64 threads) and carries on alone.
 	int team_w, team_bar;
 	double *team_x;
+	// resident kernel: where small_solve leaves what the prediction pass needs (shared memory; null = nowhere):
+	// [0] status, [1] intercept (NaN = none), [2] residual standard error, [3] n_observations, [4 .. 4+P) coefficients,
+	// [4+P] r_squared. With fit_x set and o.status null (window kernel) nothing is written to the output arrays.
+	double *fit_x = nullptr;
 };
 constexpr int kSmallTeamDoubles = 72; // >= NS2 + K + 1 + P + 2 for P = 8
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
@@ -347,8 +351,10 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		if (pe == 0 && !ic) status = ANOFOX_ERROR_INSUFFICIENT_DATA;                // ols.rs:102-107
 		else if (pe > 0 && M.nv < pe + ic) status = ANOFOX_ERROR_INSUFFICIENT_DATA; // ols.rs:134-139
 	}
+	const bool wr = o.status != nullptr; // false: results go to v.fit_x only
 	if (status != 0) {
-		if (q == 0) write_null_group(o, Pm, g, status);
+		if (q == 0 && wr) write_null_group(o, Pm, g, status);
+		if (q == 0 && v.fit_x) v.fit_x[0] = (double)status;
 		return;
 	}
 	const double inv_sw = 1.0 / sw;
@@ -360,7 +366,19 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 
 	if (pe == 0) {
 		// all columns constant: intercept-only shortcut (ols.rs:108-130, wls.rs:126-150)
-		if (q == 0) {
+		if (q == 0 && !wr) {
+			const double ss = fmax(syy_c, 0.0);
+			const double var = wls ? ss * inv_sw : ss / (n_valid - 1.0);
+			if (v.fit_x) {
+				v.fit_x[0] = 0.0;
+				v.fit_x[1] = ybar;
+				v.fit_x[2] = sqrt(var);
+				v.fit_x[3] = (double)M.nv;
+				for (int j = 0; j < P; ++j) v.fit_x[4 + j] = nanv;
+				v.fit_x[4 + P] = 0.0;
+			}
+		}
+		if (q == 0 && wr) {
 			const double ss = fmax(syy_c, 0.0);
 			const double var = wls ? ss * inv_sw : ss / (n_valid - 1.0);
 			o.status[g] = 0;
@@ -387,6 +405,14 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 			if (o.aic) o.aic[g] = aic;
 			if (o.bic) o.bic[g] = bic;
 			if (o.rss) o.rss[g] = ss;
+			if (v.fit_x) {
+				v.fit_x[0] = 0.0;
+				v.fit_x[1] = ybar;
+				v.fit_x[2] = sqrt(var);
+				v.fit_x[3] = (double)M.nv;
+				for (int j = 0; j < P; ++j) v.fit_x[4 + j] = nanv;
+				v.fit_x[4 + P] = 0.0;
+			}
 		}
 		return;
 	}
@@ -510,13 +536,24 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 	const double r2 = 1.0 - rss / tss;
 	const double sigma2 = dfr > 0.0 ? rss / dfr : nanv;
 	if (q == 0) {
-		o.status[g] = 0;
-		o.n_observations[g] = (int64_t)M.nv;
-		o.intercept[g] = ic ? b0 : nanv; // ols.rs:172-176
-		o.r_squared[g] = r2;
-		o.adj_r_squared[g] = dfr > 0.0 ? 1.0 - (1.0 - r2) * (n_valid - (double)ic) / dfr : nanv;
-		o.residual_std_error[g] = sqrt(sigma2);
-		if (o.rss) o.rss[g] = rss;
+		if (wr) {
+			o.status[g] = 0;
+			o.n_observations[g] = (int64_t)M.nv;
+			o.intercept[g] = ic ? b0 : nanv; // ols.rs:172-176
+			o.r_squared[g] = r2;
+			o.adj_r_squared[g] = dfr > 0.0 ? 1.0 - (1.0 - r2) * (n_valid - (double)ic) / dfr : nanv;
+			o.residual_std_error[g] = sqrt(sigma2);
+			if (o.rss) o.rss[g] = rss;
+		}
+		if (v.fit_x) {
+			v.fit_x[4 + P] = r2;
+			v.fit_x[0] = 0.0;
+			v.fit_x[1] = ic ? b0 : nanv;
+			v.fit_x[2] = sqrt(sigma2);
+			v.fit_x[3] = (double)M.nv;
+#pragma unroll
+			for (int j = 0; j < P; ++j) v.fit_x[4 + j] = ((live >> j) & 1u) ? b[j] : nanv;
+		}
 	}
 	if (q == (1 & (T - 1)) && (o.aic || o.bic)) {
 		double aic, bic;
@@ -525,9 +562,11 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 		if (o.bic) o.bic[g] = bic;
 	}
 	if (!inf_arrays) {
+		if (wr) {
 #pragma unroll
-		for (int j = 0; j < P; ++j)
-			if ((j & (T - 1)) == q) o.coefficients[g * P + j] = ((live >> j) & 1u) ? b[j] : nanv;
+			for (int j = 0; j < P; ++j)
+				if ((j & (T - 1)) == q) o.coefficients[g * P + j] = ((live >> j) & 1u) ? b[j] : nanv;
+		}
 		return;
 	}
 

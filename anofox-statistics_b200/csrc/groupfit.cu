@@ -2319,15 +2319,12 @@ static size_t window_scratch(AnofoxB200FitOutputs &o, unsigned char *base, int64
 		off += (bytes + 255) & ~(size_t)255;
 		return base ? base + at : (unsigned char *)nullptr;
 	};
-	const size_t n1 = (size_t)std::max<int64_t>(N, 1);
+	// The per-frame fits stay on chip (SmallGroupView::fit_x): no per-row scratch arrays any more. The workspace
+	// argument of the entry points stays (ABI), a token 256 bytes.
+	(void)N;
+	(void)p;
 	memset(&o, 0, sizeof o);
-	o.coefficients = (double *)take(n1 * p * 8);
-	o.intercept = (double *)take(n1 * 8);
-	o.r_squared = (double *)take(n1 * 8);
-	o.adj_r_squared = (double *)take(n1 * 8);
-	o.residual_std_error = (double *)take(n1 * 8);
-	o.n_observations = (int64_t *)take(n1 * 8);
-	o.status = (int32_t *)take(n1 * 4);
+	take(256);
 	return off;
 }
 

@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(32 * (kResidentWarps + 1), 1) fit_predict_resi
 	__shared__ double pv_scratch[NTEAM][PVW];
 	__shared__ double team_x[NTEAM][kSmallTeamDoubles];
 	__shared__ ResidentPredict rp[NTEAM];
+	__shared__ double fit_x[NTEAM][4 + 8 + 1];
 	const AccArgs &a = args.acc;
 	const FitParams &Pm = args.params;
 	const AnofoxB200FitOutputs &o = args.out;
@@ -120,6 +121,7 @@ __global__ void __launch_bounds__(32 * (kResidentWarps + 1), 1) fit_predict_resi
 			v.team_w = tw;
 			v.team_bar = tbar;
 			v.team_x = team_x[tm];
+			v.fit_x = fit_x[tm];
 			// ---- 1 + 2. moments (both warps) and solve (first warp) ----
 			if (tw == 0 && want_p && lane == 0) pvw[P + 1] = 0.0;
 			__syncwarp();
@@ -144,16 +146,17 @@ __global__ void __launch_bounds__(32 * (kResidentWarps + 1), 1) fit_predict_resi
 					}
 					__syncwarp();
 				}
-				// what the prediction pass needs, from the results just written (visible to the warp after __syncwarp)
-				const bool ok = o.status[g] == 0;
+				// what the prediction pass needs: small_solve left it in fit_x (no round trip through the outputs)
+				const double *fx = fit_x[tm];
+				const bool ok = fx[0] == 0.0;
 				double b0 = 0.0, margin = 0.0;
 				unsigned live = 0u;
 				if (ok) {
-					const double icpt = o.intercept[g];
+					const double icpt = fx[1];
 					const bool has_i = !isnan(icpt);
 					b0 = has_i ? icpt : 0.0;
-					const double rse = o.residual_std_error[g];
-					const int64_t nobs = o.n_observations[g];
+					const double rse = fx[2];
+					const int64_t nobs = (int64_t)fx[3];
 					if (!(isnan(rse) || rse <= 0.0 || nobs <= (int64_t)P + 1)) {
 						const int64_t kk = (int64_t)P + (has_i ? 1 : 0);
 						const int64_t df = nobs > kk ? nobs - kk : 0;
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(32 * (kResidentWarps + 1), 1) fit_predict_resi
 						}
 					}
 					if (lane < P) {
-						const double c = o.coefficients[g * P + lane];
+						const double c = fx[4 + lane];
 						rp[tm].coef[lane] = isnan(c) ? 0.0 : c; // aliased / constant columns contribute nothing (lib.rs:2292-2300)
 						live = isnan(c) ? 0u : (1u << lane);
 					}

@@ -139,7 +139,7 @@ template <int P, bool HASW> __device__ __forceinline__ bool win_row_fits(const W
 template <int P, bool HASW>
 __device__ __forceinline__ void win_fit_predict(const WindowArgs &a, WinSums<P> &F, const double (&sh)[P + 1],
                                                 const double (&xc)[P], int64_t slot, int64_t f_lo, int64_t f_hi,
-                                                const FitParams &Pm, const AnofoxB200FitOutputs &o) {
+                                                const FitParams &Pm, const AnofoxB200FitOutputs &o, double *fx) {
 	const double nanv = nan_f64();
 	double yh = nanv, lo = nanv, hi = nanv;
 	const int ic = Pm.fit_intercept ? 1 : 0;
@@ -159,15 +159,16 @@ __device__ __forceinline__ void win_fit_predict(const WindowArgs &a, WinSums<P> 
 		v.refine_list = nullptr;
 		v.rec_out = nullptr;
 		v.stash = nullptr;
+		v.fit_x = fx; // the fit's results stay on chip: no per-row scratch in HBM
 		small_solve<P, false, false, false>(F.M, sh, nonconst, F.n_train, slot, Pm, o, v);
-		if (o.status[slot] == 0) {
+		if (fx[0] == 0.0) {
 			double b[P];
 #pragma unroll
-			for (int c = 0; c < P; ++c) b[c] = o.coefficients[slot * P + c];
-			const double icpt = o.intercept[slot];
-			double rse = o.residual_std_error[slot];
-			const int64_t n = o.n_observations[slot];
-			const double r2 = o.r_squared[slot];
+			for (int c = 0; c < P; ++c) b[c] = fx[4 + c];
+			const double icpt = fx[1];
+			double rse = fx[2];
+			const int64_t n = (int64_t)fx[3];
+			const double r2 = fx[4 + P];
 			if (!(1.0 - r2 > 1e-5)) {
 				// (nearly) exact fit: tss - ess has cancelled; take the residuals from the frame's rows themselves
 				int rank = ic;
@@ -221,6 +222,10 @@ __device__ __forceinline__ void win_fit_predict(const WindowArgs &a, WinSums<P> 
 template <int P, bool HASW>
 __global__ void __launch_bounds__(128) window_fit_predict_kernel(const WindowArgs a, FitParams Pm, AnofoxB200FitOutputs o) {
 	constexpr int K = P + 1;
+	// per-thread hand-over of a frame's fit (status, intercept, rse, n, coefficients, r2: SmallGroupView::fit_x);
+	// 13 doubles apart: odd multiple of two banks
+	__shared__ double fit_slots[128][13];
+	double *fx = fit_slots[threadIdx.x];
 	const int lane = threadIdx.x & 31;
 	const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
 	const double nanv = nan_f64();
@@ -258,7 +263,7 @@ __global__ void __launch_bounds__(128) window_fit_predict_kernel(const WindowArg
 				}
 #pragma unroll
 				for (int c = 0; c < P; ++c) xc[c] = a.x[hi * P + c];
-				win_fit_predict<P, HASW>(a, F, sh, xc, r, lo, hi, Pm, o);
+				win_fit_predict<P, HASW>(a, F, sh, xc, r, lo, hi, Pm, o, fx);
 			}
 			continue;
 		}
@@ -326,7 +331,7 @@ __global__ void __launch_bounds__(128) window_fit_predict_kernel(const WindowArg
 				if (hi < r0)
 					a.yhat[r] = a.lower[r] = a.upper[r] = nanv; // empty frame
 				else
-					win_fit_predict<P, HASW>(a, F, sh, xc, r, r0, hi, Pm, o);
+					win_fit_predict<P, HASW>(a, F, sh, xc, r, r0, hi, Pm, o, fx);
 			}
 			__syncwarp();
 			carry = win_bcast<P, HASW>(S, 31);
