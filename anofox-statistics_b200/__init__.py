@@ -12,7 +12,7 @@ import numpy as np
 from . import _abi as abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libanofox_stats_b200.so")
+LIB_PATH = os.environ.get("ANOFOX_B200_LIB") or os.path.join(_HERE, "libanofox_stats_b200.so")  # env: A/B builds
 _LIB = None
 
 # every symbol include/anofox_b200.h declares

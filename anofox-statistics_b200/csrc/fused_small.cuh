@@ -899,11 +899,15 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 
 // One thread per group: moments from the transposed record (coalesced: consecutive lanes read consecutive
 // groups of the same field), then the same solve as the fused kernel with every array in registers.
+// register budget of the thread-per-group solve: (512, 1) = 128 registers; A/B builds override the pair
+#ifndef ANOFOX_SOLVE_SMALL_T
+#define ANOFOX_SOLVE_SMALL_T 512
+#endif
 #ifndef ANOFOX_SOLVE_SMALL_MINB
-#define ANOFOX_SOLVE_SMALL_MINB 4
+#define ANOFOX_SOLVE_SMALL_MINB 1
 #endif
 template <int P>
-__global__ void __launch_bounds__(512, 1) solve_small_kernel(const double *__restrict__ records, int64_t n_groups, FitParams Pm,
+__global__ void __launch_bounds__(ANOFOX_SOLVE_SMALL_T, ANOFOX_SOLVE_SMALL_MINB) solve_small_kernel(const double *__restrict__ records, int64_t n_groups, FitParams Pm,
                                                           AnofoxB200FitOutputs o, int *refine_count,
                                                           int64_t *refine_list) {
 	constexpr int K = P + 1;
