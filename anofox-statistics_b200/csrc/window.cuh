@@ -7,7 +7,7 @@
 //
 // Here the moment record is additive, so an expanding frame is an inclusive SCAN: one warp walks a partition 32
 // rows at a time, every lane takes one row, the shifted sums (n, sum w, S1, S2 about the partition's first training
-// row, and the running max |x - first| of the constant-column rule, ols.rs:76-87, which for a frame that starts
+// row, and the per-column "differs from the first row by >= 1e-10" flags of the constant-column rule, ols.rs:76-87, which for a frame that starts
 // at the partition's first row is exact) are prefix-summed across the lanes with shuffles and carried from chunk
 // to chunk; lane i then holds the sums of its own frame in registers and runs the thread-per-group solve of the
 // small-group kernels (small_solve, no inference: ols_fit_predict.cpp:281) followed by the prediction rule of
@@ -34,26 +34,24 @@ struct WindowArgs {
 
 template <int P> struct WinSums {
 	SmallMoments<P> M;  // nv = rows that enter the fit (finite y, x; w > 0 finite)
-	double dev[P];      // max |x - first| over those rows
+	unsigned nc;        // bit c: some fitting row has |x_c - first_c| >= 1e-10 (the column is not constant, ols.rs:76-87)
 	int n_train;        // rows with y (and w) present: the aggregate's y_values.size()
 };
 
 template <int P, bool HASW> __device__ __forceinline__ void win_clear(WinSums<P> &s) {
 	s.M.clear();
-#pragma unroll
-	for (int c = 0; c < P; ++c) s.dev[c] = 0.0;
+	s.nc = 0u;
 	s.n_train = 0;
 }
 
-// a += b (dev combines with max)
+// a += b (the constant-column flags combine with OR)
 template <int P, bool HASW> __device__ __forceinline__ void win_add(WinSums<P> &a, const WinSums<P> &b) {
 #pragma unroll
 	for (int i = 0; i < SmallMoments<P>::NS2; ++i) a.M.s2[i] += b.M.s2[i];
 #pragma unroll
 	for (int i = 0; i < P + 1; ++i) a.M.s1[i] += b.M.s1[i];
 	if (HASW) a.M.sw += b.M.sw;
-#pragma unroll
-	for (int c = 0; c < P; ++c) a.dev[c] = fmax(a.dev[c], b.dev[c]);
+	a.nc |= b.nc;
 	a.M.nv += b.M.nv;
 	a.n_train += b.n_train;
 }
@@ -66,10 +64,8 @@ template <int P, bool HASW> __device__ __forceinline__ WinSums<P> win_shfl_up(co
 	for (int i = 0; i < P + 1; ++i) r.M.s1[i] = __shfl_up_sync(0xffffffffu, s.M.s1[i], delta);
 	r.M.sw = HASW ? __shfl_up_sync(0xffffffffu, s.M.sw, delta) : 0.0;
 #pragma unroll
-	for (int c = 0; c < P; ++c) {
-		r.dev[c] = __shfl_up_sync(0xffffffffu, s.dev[c], delta);
-		r.M.q2[c] = 0.0;
-	}
+	for (int c = 0; c < P; ++c) r.M.q2[c] = 0.0;
+	r.nc = __shfl_up_sync(0xffffffffu, s.nc, delta);
 	r.M.nv = __shfl_up_sync(0xffffffffu, s.M.nv, delta);
 	r.M.ns = 0;
 	r.n_train = __shfl_up_sync(0xffffffffu, s.n_train, delta);
@@ -83,10 +79,8 @@ template <int P, bool HASW> __device__ __forceinline__ WinSums<P> win_bcast(cons
 	for (int i = 0; i < P + 1; ++i) r.M.s1[i] = __shfl_sync(0xffffffffu, s.M.s1[i], src);
 	r.M.sw = HASW ? __shfl_sync(0xffffffffu, s.M.sw, src) : 0.0;
 #pragma unroll
-	for (int c = 0; c < P; ++c) {
-		r.dev[c] = __shfl_sync(0xffffffffu, s.dev[c], src);
-		r.M.q2[c] = 0.0;
-	}
+	for (int c = 0; c < P; ++c) r.M.q2[c] = 0.0;
+	r.nc = __shfl_sync(0xffffffffu, s.nc, src);
 	r.M.nv = __shfl_sync(0xffffffffu, s.M.nv, src);
 	r.M.ns = 0;
 	r.n_train = __shfl_sync(0xffffffffu, s.n_train, src);
@@ -119,7 +113,7 @@ __device__ __forceinline__ void win_row(WinSums<P> &s, const double (&xr)[P], do
 	for (int c = 0; c < K; ++c) s.M.s1[c] += a[c];
 	if (HASW) s.M.sw += wv;
 #pragma unroll
-	for (int c = 0; c < P; ++c) s.dev[c] = fmax(s.dev[c], fabs(d[c]));
+	for (int c = 0; c < P; ++c) s.nc |= !(fabs(d[c]) < 1e-10) ? (1u << c) : 0u;
 	s.M.nv += 1;
 }
 
@@ -144,9 +138,7 @@ __device__ __forceinline__ void win_fit_predict(const WindowArgs &a, WinSums<P> 
 	double yh = nanv, lo = nanv, hi = nanv;
 	const int ic = Pm.fit_intercept ? 1 : 0;
 	if (F.n_train > P + ic) { // ols_fit_predict.cpp:258-262: y_values.size() <= min_obs -> NULL
-		unsigned nonconst = 0u;
-#pragma unroll
-		for (int c = 0; c < P; ++c) nonconst |= !(F.dev[c] < 1e-10) ? (1u << c) : 0u; // ols.rs:76-87
+		const unsigned nonconst = F.nc; // ols.rs:76-87
 		if (!HASW) F.M.sw = (double)F.M.nv;
 		F.M.ns = F.n_train;
 		SmallGroupView v;
