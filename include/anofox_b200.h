@@ -359,7 +359,8 @@ int32_t anofox_b200_fit_columns_batch_device(const int64_t *offsets, int64_t n_f
  * empty, holds at most n_features + intercept training rows (ols_fit_predict.cpp:258-262) or the fit fails
  * (:289-292); otherwise the model is fitted without inference and evaluated, with the simplified interval of
  * anofox_predict_with_interval, at the x of the frame's LAST row (:157-163). pred->is_training is not written.
- * n_features <= 8. null_policy 'drop_y_zero_x' is the caller's business (set y of those rows to NaN). */
+ * n_features <= 8. null_policy 'drop_y_zero_x' is the caller's business (set y of those rows to NaN).
+ * The per-frame fits stay on chip: the workspace is a token 256 bytes (the argument is kept for ABI stability). */
 size_t anofox_b200_window_workspace_bytes(int64_t n_rows, int32_t n_features);
 int32_t anofox_b200_window_fit_predict_device(const int64_t *offsets, int64_t n_groups, const double *y, const double *x,
                                               const double *w, int64_t n_rows, int32_t n_features,
