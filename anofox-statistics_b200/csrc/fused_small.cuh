@@ -453,6 +453,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 
 	// ---- Cholesky, left to right, limited pivoting (solve.cuh) --------------------------------
 	unsigned live = 0u;  // columns with a coefficient
+	const bool want_qr = Pm.qr_count != nullptr; // no queue (window form, moment-only entry points): skip the probe
 	double rinv[P];      // 1 / L_ii
 	int rank = 0;
 	bool suspicious = false;
@@ -470,7 +471,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 #pragma unroll
 		for (int c = 0; c < i; ++c) d -= A[ltri(i, c)] * A[ltri(i, c)];
 		bool alias = ridge ? !(d > 0.0) : (!(d >= 1e-14 * orig[i]) || !(d > 0.0));
-		if ((nonconst >> i) & 1u) suspicious = suspicious || chol_pivot_suspicious(d, a0, orig[i], ridge);
+		if (want_qr && ((nonconst >> i) & 1u)) suspicious = suspicious || chol_pivot_suspicious(d, a0, orig[i], ridge);
 		alias = alias || !((nonconst >> i) & 1u);
 		if (alias) {
 #pragma unroll
