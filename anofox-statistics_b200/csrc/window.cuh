@@ -213,8 +213,11 @@ __device__ __forceinline__ void win_fit_predict(const WindowArgs &a, WinSums<P> 
 
 // p <= 3: four CTAs per SM (128 registers, some spills) measured 4 % faster on W1 than two CTAs at 218 registers;
 // three CTAs (168 registers) measured slower than either
+#ifndef ANOFOX_WINDOW_MINB
+#define ANOFOX_WINDOW_MINB 4
+#endif
 template <int P, bool HASW>
-__global__ void __launch_bounds__(128, (P <= 3 ? 4 : 1)) window_fit_predict_kernel(const WindowArgs a, FitParams Pm, AnofoxB200FitOutputs o) {
+__global__ void __launch_bounds__(128, (P <= 3 ? ANOFOX_WINDOW_MINB : 1)) window_fit_predict_kernel(const WindowArgs a, FitParams Pm, AnofoxB200FitOutputs o) {
 	constexpr int K = P + 1;
 	// per-thread hand-over of a frame's fit (status, intercept, rse, n, coefficients, r2: SmallGroupView::fit_x);
 	// 13 doubles apart: odd multiple of two banks
