@@ -2302,8 +2302,8 @@ static int ingest_device(const int64_t *group_ids, const double *y, const double
 		CU(cudaGetLastError(), "radix pass");
 		cur ^= 1;
 	}
-	const int64_t ne = N * p;
-	ingest_gather_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(ws.vals[cur], N, p, y, x, w, y_out, x_out, w_out, row_index_out);
+	ingest_gather_kernel<<<(unsigned)((N + kGatherRows - 1) / kGatherRows), 256, 0, st>>>(ws.vals[cur], N, p, y, x, w, y_out, x_out, w_out,
+	                                                                                       row_index_out);
 	LAUNCHED();
 	CU(cudaGetLastError(), "ingest_gather_kernel");
 	return 0;

@@ -159,20 +159,34 @@ __global__ void ingest_offsets_kernel(const uint32_t *__restrict__ excl, int64_t
 	if (g < n_groups) offsets[g] = (int64_t)excl[g];
 	if (g == n_groups) offsets[g] = n;
 }
-// rows by sorted row index: one thread per (row, column) of X; y / w / perm by the column-0 threads
-__global__ void ingest_gather_kernel(const uint32_t *__restrict__ perm, int64_t n, int p, const double *__restrict__ y,
-                                     const double *__restrict__ x, const double *__restrict__ w, double *__restrict__ yo,
-                                     double *__restrict__ xo, double *__restrict__ wo, int64_t *__restrict__ row_index) {
-	const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (e >= n * p) return;
-	const int64_t i = e / p;
-	const int j = (int)(e - i * p);
-	const int64_t src = perm[i];
-	xo[e] = x[src * p + j];
-	if (j == 0) {
-		yo[i] = y[src];
-		if (w) wo[i] = w[src];
-		if (row_index) row_index[i] = src;
+// rows by sorted row index. A CTA takes kGatherRows consecutive OUTPUT rows: their source indices go to shared
+// memory once, then thread t walks the CTA's output elements t, t + 256, ... (coalesced stores; the p loads of a
+// source row sit side by side in a warp) with 32-bit index arithmetic on the CTA-local element number -- the first
+// version spent a 64-bit division per element and was compute-bound (2.9 of the 5.5 ms of a 50 M-row ingest).
+constexpr int kGatherRows = 256;
+__global__ void __launch_bounds__(256) ingest_gather_kernel(const uint32_t *__restrict__ perm, int64_t n, int p,
+                                                            const double *__restrict__ y, const double *__restrict__ x,
+                                                            const double *__restrict__ w, double *__restrict__ yo,
+                                                            double *__restrict__ xo, double *__restrict__ wo,
+                                                            int64_t *__restrict__ row_index) {
+	__shared__ uint32_t sperm[kGatherRows];
+	const int64_t r0 = (int64_t)blockIdx.x * kGatherRows;
+	const int nr = (int)(n - r0 < kGatherRows ? n - r0 : kGatherRows);
+	const int t = threadIdx.x;
+	uint32_t src = 0;
+	if (t < nr) {
+		src = perm[r0 + t];
+		sperm[t] = src;
+		yo[r0 + t] = y[src];
+		if (w) wo[r0 + t] = w[src];
+		if (row_index) row_index[r0 + t] = (int64_t)src;
+	}
+	__syncthreads();
+	const uint32_t ne = (uint32_t)nr * (uint32_t)p, up = (uint32_t)p;
+	double *__restrict__ dst = xo + r0 * p;
+	for (uint32_t le = (uint32_t)t; le < ne; le += 256u) {
+		const uint32_t row = le / up, col = le - row * up;
+		dst[le] = x[(int64_t)sperm[row] * p + col];
 	}
 }
 
