@@ -1790,18 +1790,29 @@ __global__ void rebase_offsets_kernel(const int64_t *__restrict__ in, int64_t n,
 
 // Column-major-per-fit -> row-major rows (the scalar array fits: ols_fit(y LIST, x LIST(LIST)), one fit per SQL row,
 // src/table_functions/ols_fit.cpp:120-173). Fit i owns rows [offsets[i], offsets[i+1]); its block of the input holds
-// column 0, column 1, ... each of n_i values. One warp per fit, reads coalesced along the block.
+// column 0, column 1, ... each of n_i values. One warp per fit; the lanes walk the OUTPUT elements (coalesced
+// stores, the loads fall on p short runs of the fit's own block, which the L1 holds), index arithmetic in 32 bits
+// whenever the fit has fewer than 2^31 elements.
 __global__ void columns_to_rows_kernel(const int64_t *__restrict__ offsets, int64_t n_fits, const double *__restrict__ xc, int p,
                                        double *__restrict__ xr) {
 	const int lane = threadIdx.x & 31;
 	const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
 	for (int64_t f = wid; f < n_fits; f += nw) {
 		const int64_t r0 = offsets[f], n = offsets[f + 1] - r0;
-		const double *src = xc + r0 * p;
-		double *dst = xr + r0 * p;
-		for (int64_t e = lane; e < n * p; e += 32) {
-			const int64_t j = e / n, k = e - j * n;
-			dst[k * p + j] = src[e];
+		const double *__restrict__ src = xc + r0 * p;
+		double *__restrict__ dst = xr + r0 * p;
+		const int64_t ne = n * p;
+		if (ne < ((int64_t)1 << 31)) {
+			const uint32_t un = (uint32_t)n, up = (uint32_t)p, une = (uint32_t)ne;
+			for (uint32_t o = (uint32_t)lane; o < une; o += 32u) {
+				const uint32_t k = o / up, j = o - k * up;
+				dst[o] = src[j * un + k];
+			}
+		} else {
+			for (int64_t o = lane; o < ne; o += 32) {
+				const int64_t k = o / p, j = o - k * p;
+				dst[o] = src[j * n + k];
+			}
 		}
 	}
 }
