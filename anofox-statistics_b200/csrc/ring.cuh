@@ -401,7 +401,9 @@ __global__ void __maxnreg__(ring_maxreg(NCW)) acc_ring_kernel(const RingArgs a) 
 			const int nq = (slice ? span / rstep : span >> (ltw + (NSET == 4 ? 4 : (NSET == 2 ? 3 : 2)))) + 1;
 			uint32_t py = ys + (uint32_t)(rp + rl) * 8u, pw = ws + (uint32_t)(rp + rl) * 8u, pt = ts + (uint32_t)(rp + rl);
 			// quads of this batch: as many as have landed, up to the ring end
-			const int to_end = (ring_rows - rp + rstep - 1) / rstep;
+			// (group mode: rstep = TW * QR is a power of two -- a shift, like nq above, not a division per batch)
+			const int to_end = slice ? (ring_rows - rp + rstep - 1) / rstep
+			                         : (ring_rows - rp + rstep - 1) >> (ltw + (NSET == 4 ? 4 : (NSET == 2 ? 3 : 2)));
 			const int nqe = nq < to_end ? nq : to_end;
 			int q = 0;
 			if constexpr (kRingPipelined<NT>) {
