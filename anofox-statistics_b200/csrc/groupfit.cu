@@ -1686,6 +1686,17 @@ struct HostContext {
 		}
 		return hstage != nullptr;
 	}
+	// Medium calls (DuckDB's Finalize hands over up to 2 048 groups: ~0.7 MB of results in 19 arrays): the results
+	// come back as ONE copy into this pinned buffer and are scattered by the host, instead of 19 small copies.
+	static constexpr size_t kOutStage = (size_t)2 << 20;
+	unsigned char *hstage_out = nullptr;
+	bool out_stage_ready() {
+		if (!hstage_out && cudaHostAlloc((void **)&hstage_out, kOutStage, cudaHostAllocDefault) != cudaSuccess) {
+			hstage_out = nullptr;
+			cudaGetLastError();
+		}
+		return hstage_out != nullptr;
+	}
 	int ensure(size_t bytes, AnofoxError *err) {
 		if (!stream) CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "cudaStreamCreate");
 		if (!in_stream) CU(cudaStreamCreateWithFlags(&in_stream, cudaStreamNonBlocking), "cudaStreamCreate");
@@ -1875,6 +1886,7 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 	const size_t in_span = o_gp - o_off, out_span = o_g + (size_t)G1 * 8 * 12 - o_gp;
 	const bool small = nch == 1 && !pred && in_span <= HostContext::kStageHalf && out_span <= HostContext::kStageHalf &&
 	                   c.stage_ready();
+	const bool pack_out = !small && nch == 1 && !pred && out && out_span <= HostContext::kOutStage && c.out_stage_ready();
 	struct Pending {
 		void *dst;
 		size_t off, bytes;
@@ -1912,7 +1924,7 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 		if ((rc = push(i))) return rc;
 	double *gp = (double *)(d + o_gp), *gs = (double *)(d + o_g);
 	auto back = [&](void *dst, const void *src, size_t bytes) {
-		if (small) { // scattered from the staging buffer after the one packed copy below
+		if (small || pack_out) { // scattered from the staging buffer after the one packed copy below
 			if (dst && bytes) pending.push_back({dst, (size_t)((const unsigned char *)src - (d + o_gp)), bytes});
 			return cudaSuccess;
 		}
@@ -2007,11 +2019,12 @@ static int fit_host(const int64_t *offsets, int64_t G, const double *y, const do
 			CU(back(pred->is_training + r0, dpred.is_training, (size_t)Nc), "D2H");
 		}
 	}
-	if (small) CU(cudaMemcpyAsync(c.hstage + HostContext::kStageHalf, d + o_gp, out_span, cudaMemcpyDeviceToHost, sout), "D2H packed");
+	unsigned char *hback = small ? c.hstage + HostContext::kStageHalf : c.hstage_out;
+	if (small || pack_out) CU(cudaMemcpyAsync(hback, d + o_gp, out_span, cudaMemcpyDeviceToHost, sout), "D2H packed");
 	CU(cudaStreamSynchronize(sin), "sync");
 	CU(cudaStreamSynchronize(st), "sync");
 	if (sout != st) CU(cudaStreamSynchronize(sout), "sync");
-	for (const Pending &q : pending) memcpy(q.dst, c.hstage + HostContext::kStageHalf + q.off, q.bytes);
+	for (const Pending &q : pending) memcpy(q.dst, hback + q.off, q.bytes);
 	return 0;
 }
 
