@@ -65,3 +65,22 @@ def test_ridge_ignores_hc_and_bad_value_is_an_error(lib, b200):
     a = lib.fit_batch_host(off, y, x, None, method="ridge", alpha=1.0, compute_inference=True, hc_type="hc3")
     b = lib.fit_batch_host(off, y, x, None, method="ridge", alpha=1.0, compute_inference=True)
     assert np.array_equal(a["std_errors"], b["std_errors"])  # ridge.rs has no hc_type
+
+
+@pytest.mark.parametrize("hc,method", [("hc1", "ols"), ("hc3", "wls")])
+def test_hc_small_features_with_long_groups_mixed_in(lib, oracle, hc, method):
+    """p <= 8: groups of up to 2 048 rows take the four-lanes-per-group kernel, longer ones are listed by it and
+    handled by the CTA-per-group kernel (list mode) -- both kinds in one batch, and the boundary sizes themselves."""
+    rng = np.random.default_rng(31)
+    sizes = np.array([100, 3000, 50, 2500, 2048, 2049, 7, 2047])
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    N, p = int(off[-1]), 4
+    x = rng.normal(size=(N, p)) * 2 + 1
+    y = 0.5 + x @ np.array([1.0, -2.0, 0.25, 3.0]) + rng.normal(size=N) * (0.2 + np.abs(x[:, 1]))
+    x[int(off[3]):int(off[4]), 2] = 1.75  # a constant column inside one of the long groups
+    y[::53] = np.nan
+    w = rng.uniform(0.5, 2.0, size=N) if method == "wls" else None
+    opt = dict(method=method, compute_inference=True, hc_type=hc)
+    dev = lib.fit_batch_host(off, y, x, w, **opt)
+    ora = oracle.fit_batch(off, y, x, w, **opt)
+    assert_fit_parity(dev, ora, rtol=1e-9, inference=True, label=f"{hc}/{method}/long groups")
