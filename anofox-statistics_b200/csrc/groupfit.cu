@@ -1384,7 +1384,11 @@ static int fit_device(const int64_t *offsets, int64_t G, const double *y, const 
 	CU(cudaMemsetAsync(ws.big_count, 0, 768, st), "memset"); // big_count | refine_count | redo_count
 	// small-group kernels: 2 = stash kernel (rows -> results, one launch), 1 = the redundant-solve fused kernel
 	// (A/B), 0 = accumulate to transposed records + thread-per-group solve kernel
-	const int small_mode = !small.use ? 0 : (small.stash ? 2 : (g_force_path.load() == 2 ? 1 : 0));
+	// a handful of groups (the per-group anofox_*_fit calls of DuckDB's Finalize: G = 1): the single-launch fused
+	// kernel -- its redundant solve costs nothing at this size and two launches (solve, refine) drop out of a call
+	// whose cost is launch latency
+	const bool tiny_batch = g_force_path.load() == 0 && G <= 32;
+	const int small_mode = !small.use ? 0 : (small.stash ? 2 : ((g_force_path.load() == 2 || tiny_batch) ? 1 : 0));
 	const bool fused = small_mode != 0 || resident.use; // the small groups leave the first kernel solved
 	const bool transposed = small.use && !fused; // record element (g, i) at records[g + i * G]
 	const int64_t rec_gs = transposed ? 1 : rec_len(p), rec_es = transposed ? G : 1;
