@@ -26,7 +26,7 @@ constexpr int stash_pool_bytes(int p, bool has_w) { return 2 * stash_acc_warps(p
 	cudaError_t launch_small_p##P_(int mode, bool has_w, bool has_t, const SmallArgs &a, int grid, cudaStream_t st);   \
 	cudaError_t launch_solve_small_p##P_(const double *records, int64_t n_groups, const FitParams &P,                \
 	                                     const AnofoxB200FitOutputs &o, int *refine_count, int64_t *refine_list,     \
-	                                     cudaStream_t st);
+	                                     int defer_p, cudaStream_t st);
 B200_DECLARE_SMALL(1)
 B200_DECLARE_SMALL(2)
 B200_DECLARE_SMALL(3)
@@ -85,14 +85,14 @@ template <int P, bool HASW, bool HAST> cudaError_t launch_stash_t(const SmallArg
 	}                                                                                                                \
 	cudaError_t launch_solve_small_p##P_(const double *records, int64_t n_groups, const FitParams &P,                \
 	                                     const AnofoxB200FitOutputs &o, int *refine_count, int64_t *refine_list,     \
-	                                     cudaStream_t st) {                                                          \
+	                                     int defer_p, cudaStream_t st) {                                             \
 		static const int thr = getenv("ANOFOX_B200_SOLVE_THREADS") ? atoi(getenv("ANOFOX_B200_SOLVE_THREADS")) : 128; \
 		const unsigned blocks = (unsigned)((n_groups + thr - 1) / thr);                                              \
 		static const int dyn_kb = getenv("ANOFOX_B200_SOLVE_DYN_KB") ? atoi(getenv("ANOFOX_B200_SOLVE_DYN_KB")) : 0; \
 		if (dyn_kb > 0)                                                                                              \
 			cudaFuncSetAttribute(solve_small_kernel<P_>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_kb * 1024); \
 		solve_small_kernel<P_><<<blocks, thr, (size_t)dyn_kb * 1024, st>>>(records, n_groups, P, o, refine_count,    \
-		                                                                   refine_list);                             \
+		                                                                   refine_list, defer_p);                    \
 		return cudaGetLastError();                                                                                   \
 	}
 

@@ -243,6 +243,9 @@ struct SmallGroupView {
 	// [0] status, [1] intercept (NaN = none), [2] residual standard error, [3] n_observations, [4 .. 4+P) coefficients,
 	// [4+P] r_squared. With fit_x set and o.status null (window kernel) nothing is written to the output arrays.
 	double *fit_x = nullptr;
+	// thread-per-group solve: leave the p-values to pvalues_deferred_kernel (groupfit.cu). The slots then carry what it
+	// needs: p_values[g*P+j] = residual degrees of freedom (NaN for a dead column), f_pvalue[g] = model degrees of freedom.
+	bool defer_p = false;
 };
 constexpr int kSmallTeamDoubles = 72; // >= NS2 + K + 1 + P + 2 for P = 8
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
@@ -619,7 +622,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 				if (ROWS)
 					v.pv[j] = t * t;
 				else
-					o.p_values[oj] = pvalue_f(t * t, 1.0, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
+					o.p_values[oj] = v.defer_p ? dfr : pvalue_f(t * t, 1.0, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
 			} else {
 				o.coefficients[oj] = nanv;
 				o.std_errors[oj] = nanv;
@@ -643,7 +646,7 @@ __device__ __forceinline__ void small_solve(const SmallMoments<P> &M, const doub
 			v.pv[P + 1] = dfm; // > 0 marks "p-values wanted" for this slot
 			v.pv[P + 2] = dfr;
 		} else {
-			o.f_pvalue[g] = pvalue_f(fs, dfm, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
+			o.f_pvalue[g] = v.defer_p ? dfm : pvalue_f(fs, dfm, dfr, DfTables{Pm.tcrit, Pm.gratio, Pm.rcp, Pm.ce, Pm.co});
 		}
 	}
 }
@@ -910,7 +913,7 @@ __device__ __forceinline__ void small_group(const SmallGroupView &v, int64_t g, 
 template <int P>
 __global__ void __launch_bounds__(ANOFOX_SOLVE_SMALL_T, ANOFOX_SOLVE_SMALL_MINB) solve_small_kernel(const double *__restrict__ records, int64_t n_groups, FitParams Pm,
                                                           AnofoxB200FitOutputs o, int *refine_count,
-                                                          int64_t *refine_list) {
+                                                          int64_t *refine_list, int defer_p) {
 	constexpr int K = P + 1;
 	const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (g >= n_groups) return;
@@ -945,6 +948,7 @@ __global__ void __launch_bounds__(ANOFOX_SOLVE_SMALL_T, ANOFOX_SOLVE_SMALL_MINB)
 	v.refine_list = refine_list;
 	v.rec_out = nullptr;
 	v.stash = nullptr;
+	v.defer_p = defer_p != 0;
 	small_solve<P, false, false, false>(M, sh, nonconst, n_state, g, Pm, o, v);
 }
 

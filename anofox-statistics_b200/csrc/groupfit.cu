@@ -712,21 +712,61 @@ static cudaError_t launch_small(const SmallArgs &a, int mode, bool has_w, bool h
 	LAUNCHED();
 	return e;
 }
+// The p-values the thread-per-group solve left out (SmallGroupView::defer_p): one thread per (group, statistic), the P
+// t-tests and the F test of a group side by side. The same pvalue_f on the same arguments as the in-line form, so the
+// results are bit-identical; the point is the instruction stream: the distribution code is more than half of the
+// solve kernel's instructions and most of its code size, and it diverges per statistic -- here it runs at full
+// occupancy (few registers) instead of inside a 128-register thread that holds a whole fit.
+__global__ void __launch_bounds__(256) pvalues_deferred_kernel(int64_t n_groups, int p, int ic, FitParams P, AnofoxB200FitOutputs o) {
+	// threads [0, G p): the t-tests in output order; threads [G p, G p + G): the F tests -- a warp never mixes the two
+	const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const int64_t nt = n_groups * p;
+	if (e >= nt + n_groups) return;
+	const DfTables T{P.tcrit, P.gratio, P.rcp, P.ce, P.co};
+	if (e < nt) {
+		const double dfr = o.p_values[e];
+		if (isnan(dfr)) return; // dead column or NULL struct: stays NaN
+		const int64_t g = e / p;
+		if (o.status[g] != 0) return;
+		const double t = o.t_values[e];
+		o.p_values[e] = pvalue_f(t * t, 1.0, dfr, T);
+	} else {
+		const int64_t g = e - nt;
+		if (o.status[g] != 0) return;                           // NULL struct: every statistic is NaN already
+		if (o.has_inference && o.has_inference[g] == 0) return; // intercept-only fit: no inference (lib.rs:251-253)
+		const double dfm = o.f_pvalue[g];
+		if (isnan(dfm)) return;
+		const double dfr = (double)o.n_observations[g] - dfm - (double)ic;
+		o.f_pvalue[g] = pvalue_f(o.f_statistic[g], dfm, dfr, T);
+	}
+}
+
 static cudaError_t launch_solve_small(const double *records, int64_t G, const FitParams &P, const AnofoxB200FitOutputs &o,
                                       int *refine_count, int64_t *refine_list, cudaStream_t st) {
 	if (G <= 0) return cudaSuccess;
 	cudaError_t e = cudaErrorInvalidValue;
+	// A/B (ANOFOX_B200_DEFER_PVALUES=1): p-values in a kernel of their own. Measured on C2: solve stage 0.433 ms against
+	// 0.387 ms with the p-values in line (bit-identical results) -- the distribution code costs its ~0.2 ms either way
+	// and overlaps better with the rest of the solve inside one thread. Off by default.
+	static const int env_defer = getenv("ANOFOX_B200_DEFER_PVALUES") ? atoi(getenv("ANOFOX_B200_DEFER_PVALUES")) : 0;
+	const int defer_p = (P.compute_inference && o.std_errors && o.p_values && o.f_pvalue && o.t_values && env_defer) ? 1 : 0;
 	switch (P.p) {
-	case 1: e = launch_solve_small_p1(records, G, P, o, refine_count, refine_list, st); break;
-	case 2: e = launch_solve_small_p2(records, G, P, o, refine_count, refine_list, st); break;
-	case 3: e = launch_solve_small_p3(records, G, P, o, refine_count, refine_list, st); break;
-	case 4: e = launch_solve_small_p4(records, G, P, o, refine_count, refine_list, st); break;
-	case 5: e = launch_solve_small_p5(records, G, P, o, refine_count, refine_list, st); break;
-	case 6: e = launch_solve_small_p6(records, G, P, o, refine_count, refine_list, st); break;
-	case 7: e = launch_solve_small_p7(records, G, P, o, refine_count, refine_list, st); break;
-	case 8: e = launch_solve_small_p8(records, G, P, o, refine_count, refine_list, st); break;
+	case 1: e = launch_solve_small_p1(records, G, P, o, refine_count, refine_list, defer_p, st); break;
+	case 2: e = launch_solve_small_p2(records, G, P, o, refine_count, refine_list, defer_p, st); break;
+	case 3: e = launch_solve_small_p3(records, G, P, o, refine_count, refine_list, defer_p, st); break;
+	case 4: e = launch_solve_small_p4(records, G, P, o, refine_count, refine_list, defer_p, st); break;
+	case 5: e = launch_solve_small_p5(records, G, P, o, refine_count, refine_list, defer_p, st); break;
+	case 6: e = launch_solve_small_p6(records, G, P, o, refine_count, refine_list, defer_p, st); break;
+	case 7: e = launch_solve_small_p7(records, G, P, o, refine_count, refine_list, defer_p, st); break;
+	case 8: e = launch_solve_small_p8(records, G, P, o, refine_count, refine_list, defer_p, st); break;
 	}
 	LAUNCHED();
+	if (e == cudaSuccess && defer_p) {
+		const int64_t n = G * (P.p + 1);
+		pvalues_deferred_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(G, P.p, P.fit_intercept ? 1 : 0, P, o);
+		LAUNCHED();
+		e = cudaGetLastError();
+	}
 	return e;
 }
 
