@@ -952,6 +952,14 @@ __global__ void __launch_bounds__(ANOFOX_SOLVE_SMALL_T, ANOFOX_SOLVE_SMALL_MINB)
 	small_solve<P, false, false, false>(M, sh, nonconst, n_state, g, Pm, o, v);
 }
 
+// rows of 64 bytes (p = 8): the lanes of a group walk the columns in rotated order (small_accumulate ROT), which takes
+// the 8-way shared-memory bank conflict out of the row loads: 1 M groups x 50 rows x 8 features, accumulate kernel
+// 1.69 -> 1.51 ms (x 200 rows: 2.38 -> 2.27 ms). p = 4 (32-byte rows, 4-way conflict) measured 2 % slower with the
+// rotation and its un-rotation than without, so it stays plain. A/B: -DANOFOX_SMALL_ROT=0.
+#ifndef ANOFOX_SMALL_ROT
+#define ANOFOX_SMALL_ROT 1
+#endif
+template <int P> constexpr bool kSmallRot = ANOFOX_SMALL_ROT != 0 && P == 8;
 constexpr int kSmallStageGroups = 64; // groups per stage of the fused kernel at most (two rounds of 32)
 constexpr int kSmallMaxStages = 8;
 using SmallStageHeader = StageHeaderT<kSmallStageGroups>;
@@ -1038,7 +1046,7 @@ __global__ void __launch_bounds__(32 * (NCW + 1), 1) fit_small_kernel(const Smal
 				v.sg.w = aw + (uint32_t)rb * 8u;
 				v.sg.t = at + (uint32_t)rb;
 				v.sg.kone = v.sg.kzero = 0u;
-				small_group<P, HASW, HAST, FUSED ? 1 : 0>(v, g0 + gi, args.params, args.out, a.records, a.n_groups);
+				small_group<P, HASW, HAST, FUSED ? 1 : 0, kSmallRot<P>>(v, g0 + gi, args.params, args.out, a.records, a.n_groups);
 			}
 			__syncwarp();
 			if (want_p) {
