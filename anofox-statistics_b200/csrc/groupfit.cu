@@ -998,14 +998,15 @@ static SmallGeom small_geometry(int p, bool has_w, bool has_t, int64_t n_rows, i
 		budget = stash_ring;
 		if (env_small_kb > 0) budget = std::min<int64_t>(budget, (int64_t)env_small_kb * 1024);
 	} else {
-		// lanes per group: about 700 bytes of rows per lane up to p = 5 (C1, C2: 12.5 rows per lane); from p = 6 on the
+		// lanes per group: up to 900 bytes of rows per lane up to p = 5 (C2: 600 B = 12.5 rows per lane; C1: 800 B = 25
+		// rows, T = 4 measured 10 % faster in the accumulate kernel than T = 8, which a 700-byte rule chose); from p = 6 on the
 		// per-group butterfly over the 28 .. 54 sums weighs more than the rows, so a lane takes up to 16 rows
 		// (measured at p = 8: 1 M x 50 rows T = 8 -> 4: 1.51 -> 1.23 ms; 250 k x 200 rows T = 32 -> 16: 2.27 -> 1.22 ms)
 		int T = 4;
 		if (p >= 6)
 			while (T < 32 && mean_rows > 16.0 * T) T *= 2;
 		else
-			while (T < 32 && mean_bytes > 700.0 * T) T *= 2;
+			while (T < 32 && mean_bytes > 900.0 * T) T *= 2;
 		static const int env_small_T = getenv("ANOFOX_B200_SMALL_T") ? atoi(getenv("ANOFOX_B200_SMALL_T")) : 0; // tuning hook
 		if (env_small_T >= 4 && env_small_T <= 32 && (env_small_T & (env_small_T - 1)) == 0) T = env_small_T;
 		r.T = T;
