@@ -9,7 +9,8 @@ from __graft_entry__ import load_package  # noqa: E402
 
 pkg = load_package()
 synth = import_module("anofox_statistics_b200.synth")
-for p, n in ((8, 50), (4, 50), (8, 200)):
+shapes = [tuple(int(v) for v in a.split("x")) for a in sys.argv[1:]] or [(8, 50), (4, 50), (8, 200)]
+for p, n in shapes:
     G = 1_000_000 if n == 50 else 250_000
     d = synth.make_torch(G, n, p, seed=2)
     fit = pkg.DeviceFit(G, G * n, p, inference=True)
