@@ -895,8 +895,10 @@ static RingGeom ring_geometry(int p, bool has_w, bool has_t, int64_t n_rows, int
 	static const int env_win_kb = getenv("ANOFOX_B200_RING_WIN_KB") ? atoi(getenv("ANOFOX_B200_RING_WIN_KB")) : 0;
 	static const int env_team = getenv("ANOFOX_B200_RING_TEAM") ? atoi(getenv("ANOFOX_B200_RING_TEAM")) : 0;
 	// measured (tools/sweep.sh): 8 KB windows lose a third of the bandwidth to per-copy overhead; one-tile shapes
-	// (small p: y and the flags are tiny copies) want 32 KB, wider rows are best at 16 KB
-	const int64_t win_bytes = (env_win_kb > 0 ? env_win_kb : (sh.nt == 1 ? 32 : 16)) * 1024;
+	// (small p: y and the flags are tiny copies) want 32 KB, wider rows are best at 16 KB; two-tile shapes (9 <= p <= 15
+	// and p = 16), re-swept at the end of round 2 on C3: 24 KB windows, ridge accumulate 5.99 -> 5.81 ms, wls 7.44 -> 7.21 ms
+	// (28 / 32 KB are better still for one of the two and 10 % worse for the other)
+	const int64_t win_bytes = (env_win_kb > 0 ? env_win_kb : (sh.nt == 1 ? 32 : (sh.nt == 2 ? 24 : 16))) * 1024;
 	int sr = (int)((win_bytes / row_bytes + 15) / 16 * 16);
 	if (sr < 32) sr = 32;
 	const double mean_rows = n_groups > 0 ? (double)n_rows / (double)n_groups : 1.0;
